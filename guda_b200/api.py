@@ -1,0 +1,407 @@
+"""Host-side mirror of GUDA's root-package API (package guda) above the C ABI.
+
+Same names, argument meaning and error behaviour as the reference's Go functions, so the
+parity tests read like the reference's own tests:
+  Malloc/Free/Memcpy/DevicePtr   memory.go:57-66,81-145,246-317
+  Synchronize/CreateStream       guda.go:242-305
+  AXPY/DOT/Scale/GEMM            math.go:39,64,170,98
+  FusedGEMMBiasReLU/GELU         fused.go:313, fused_gelu.go:65
+  GEMMBFloat16/GEMMFloat16       bfloat16.go:104, float16.go:201
+plus the documented aliases (docs/manual/08-blas-api.md): Saxpy/Sdot/Sscal/Sgemm/Dgemm...
+The Go shim in go/guda/ is the real drop-in; this module is the same layer for the Python
+test/bench harness (there is no Go toolchain in the build image).  Host data are numpy arrays.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import (BlasPanic, GUDAError, MEMCPY_D2D, MEMCPY_D2H, MEMCPY_DEFAULT, MEMCPY_H2D, MEMCPY_H2H)
+
+MemcpyHostToHost, MemcpyHostToDevice, MemcpyDeviceToHost, MemcpyDeviceToDevice, MemcpyDefault = range(5)
+
+
+class ErrNotSupported(GUDAError):
+    """fused.go:11-17 ErrNotSupported."""
+
+
+def _L():
+    return capi.load()
+
+
+class DevicePtr:
+    """memory.go / guda.go:95-99 DevicePtr{ptr,size,offset}.  Float32()/Float64()/Int32()/Byte() are
+    device->host SNAPSHOTS (the reference's were live host views): writes must go through Memcpy."""
+    __slots__ = ("ptr", "size", "offset")
+
+    def __init__(self, ptr=0, size=0, offset=0):
+        self.ptr, self.size, self.offset = ptr, size, offset
+
+    def Offset(self, nbytes):                      # memory.go:303-309
+        return DevicePtr(self.ptr + nbytes, self.size - nbytes, self.offset + nbytes)
+
+    def Size(self):                                # memory.go:312-314
+        return self.size
+
+    def _snapshot(self, dtype):
+        if not self.ptr:
+            return None
+        n = self.size // np.dtype(dtype).itemsize
+        out = np.empty(n, dtype=dtype)
+        if n:
+            capi.check(_L().guda_memcpy(out.ctypes.data, self.ptr, n * out.itemsize, MEMCPY_D2H, None), "Memcpy")
+        return out
+
+    def Float32(self): return self._snapshot(np.float32)
+    def Float64(self): return self._snapshot(np.float64)
+    def Int32(self): return self._snapshot(np.int32)
+    def Byte(self): return self._snapshot(np.uint8)
+    def UInt16(self): return self._snapshot(np.uint16)
+
+    def __repr__(self):
+        return "DevicePtr(0x%x, size=%d, offset=%d)" % (self.ptr, self.size, self.offset)
+
+
+class Stream:
+    """guda.go:57-62 Stream -> a CUDA stream.  Submit(fn) of the reference (a host closure queue) has no GPU meaning;
+    kernels are enqueued by passing stream=... to the BLAS calls."""
+
+    def __init__(self, handle):
+        self.handle = handle
+
+    def Synchronize(self):                         # guda.go:297-299
+        capi.check(_L().guda_stream_synchronize(self.handle), "StreamSynchronize")
+
+    def Query(self):
+        done = C.c_int(0)
+        capi.check(_L().guda_stream_query(self.handle, C.byref(done)), "StreamQuery")
+        return bool(done.value)
+
+    def WaitEvent(self, event):
+        capi.check(_L().guda_stream_wait_event(self.handle, event.handle), "StreamWaitEvent")
+
+    def Destroy(self):
+        capi.check(_L().guda_stream_destroy(self.handle), "StreamDestroy")
+        self.handle = None
+
+    def native(self):
+        out = C.c_void_p()
+        capi.check(_L().guda_stream_native(self.handle, C.byref(out)), "StreamNative")
+        return out.value or 0
+
+
+class Event:
+    def __init__(self):
+        h = C.c_void_p()
+        capi.check(_L().guda_event_create(C.byref(h)), "EventCreate")
+        self.handle = h.value
+
+    def Record(self, stream=None):
+        capi.check(_L().guda_event_record(self.handle, _sh(stream)), "EventRecord")
+
+    def Synchronize(self):
+        capi.check(_L().guda_event_synchronize(self.handle), "EventSynchronize")
+
+    def Query(self):
+        done = C.c_int(0)
+        capi.check(_L().guda_event_query(self.handle, C.byref(done)), "EventQuery")
+        return bool(done.value)
+
+    def Destroy(self):
+        capi.check(_L().guda_event_destroy(self.handle), "EventDestroy")
+        self.handle = None
+
+
+def ElapsedTime(start, stop):
+    ms = C.c_float(0)
+    capi.check(_L().guda_event_elapsed_ms(start.handle, stop.handle, C.byref(ms)), "EventElapsedTime")
+    return ms.value
+
+
+def _sh(stream):
+    return None if stream is None else stream.handle
+
+
+# ---------------------------------------------------------------- device / runtime
+def Init(device=0):
+    capi.check(_L().guda_init(device), "Init")
+
+
+def GetDeviceCount():
+    """guda.go:227-229: the single-device API always reports 1 (pinned by guda_test.go:332-335)."""
+    return 1
+
+
+def PhysicalDeviceCount():
+    n = C.c_int(0)
+    capi.check(_L().guda_device_count(C.byref(n)), "DeviceCount")
+    return n.value
+
+
+def SetDevice(dev):                                # guda.go:216-221
+    if dev != 0:
+        raise GUDAError(capi.ERR_INVALID_ARG, "SetDevice", "invalid device ID")
+
+
+def GetDeviceProperties(dev=0):                    # guda.go:232-237
+    if dev != 0:
+        raise GUDAError(capi.ERR_INVALID_ARG, "GetDeviceProperties", "invalid device ID: %d" % dev)
+    cur = C.c_int(0)
+    capi.check(_L().guda_get_device(C.byref(cur)), "GetDevice")
+    props = capi.DeviceProps()
+    capi.check(_L().guda_device_properties(cur.value, C.byref(props)), "GetDeviceProperties")
+    return props
+
+
+def Synchronize():                                 # guda.go:278-283
+    capi.check(_L().guda_device_synchronize(), "Synchronize")
+
+
+def CreateStream():                                # guda.go:242-256
+    h = C.c_void_p()
+    capi.check(_L().guda_stream_create(C.byref(h)), "StreamCreate")
+    return Stream(h.value)
+
+
+StreamCreate = CreateStream
+
+
+def MemGetInfo():
+    fr, tot = C.c_size_t(0), C.c_size_t(0)
+    capi.check(_L().guda_mem_get_info(C.byref(fr), C.byref(tot)), "MemGetInfo")
+    return fr.value, tot.value
+
+
+# ---------------------------------------------------------------- memory
+def Malloc(size):                                  # memory.go:57-59
+    p = C.c_void_p()
+    capi.check(_L().guda_malloc(C.byref(p), size), "Malloc")
+    return DevicePtr(p.value or 0, size, 0)
+
+
+def Free(ptr):                                     # memory.go:62-66
+    capi.check(_L().guda_free(ptr.ptr), "Free")
+
+
+def GetMemoryStats():                              # memory.go:230-234
+    a, p = C.c_int64(0), C.c_int64(0)
+    capi.check(_L().guda_pool_stats(C.byref(a), C.byref(p)), "GetStats")
+    return a.value, p.value
+
+
+def _addr(obj, writable):
+    if isinstance(obj, DevicePtr):
+        return obj.ptr
+    if isinstance(obj, np.ndarray):
+        if not obj.flags.c_contiguous:
+            raise GUDAError(capi.ERR_INVALID_ARG, "Memcpy", "host array must be contiguous")
+        if writable and not obj.flags.writeable:
+            raise GUDAError(capi.ERR_INVALID_ARG, "Memcpy", "destination host array is read-only")
+        return obj.ctypes.data if obj.size else 0
+    if isinstance(obj, int):
+        return obj
+    raise GUDAError(capi.ERR_INVALID_ARG, "Memcpy", "unsupported %s type: %s" % ("dst" if writable else "src", type(obj).__name__))
+
+
+def Memcpy(dst, src, size, kind=MemcpyDefault, stream=None):       # memory.go:81-145
+    capi.check(_L().guda_memcpy(_addr(dst, True), _addr(src, False), size, kind, _sh(stream)), "Memcpy")
+
+
+def MemcpyAsync(dst, src, size, kind=MemcpyDefault, stream=None):
+    capi.check(_L().guda_memcpy_async(_addr(dst, True), _addr(src, False), size, kind, _sh(stream)), "MemcpyAsync")
+
+
+def Memset(ptr, value, size, stream=None):
+    capi.check(_L().guda_memset(ptr.ptr, value, size, _sh(stream)), "Memset")
+
+
+def to_device(arr):
+    """Convenience: Malloc + H2D of a numpy array."""
+    arr = np.ascontiguousarray(arr)
+    d = Malloc(max(arr.nbytes, 1))
+    d.size = arr.nbytes
+    if arr.nbytes:
+        Memcpy(d, arr, arr.nbytes, MemcpyHostToDevice)
+    return d
+
+
+# ---------------------------------------------------------------- slice-length checks done above cgo (DevicePtr knows its size)
+def _len(p, itemsize):
+    return p.size // itemsize
+
+
+def _check_level1(n, x, incx, y, incy, item):
+    # compute/level1float32.go:226-242 (order and strings)
+    if incx == 0: raise BlasPanic("blas: zero x index increment")
+    if y is not None and incy == 0: raise BlasPanic("blas: zero y index increment")
+    if n < 1:
+        if n == 0: return False
+        raise BlasPanic("blas: n < 0")
+    lx = _len(x, item)
+    if (incx > 0 and lx <= (n - 1) * incx) or (incx < 0 and lx <= (1 - n) * incx): raise BlasPanic("blas: insufficient length of x")
+    if y is not None:
+        ly = _len(y, item)
+        if (incy > 0 and ly <= (n - 1) * incy) or (incy < 0 and ly <= (1 - n) * incy): raise BlasPanic("blas: insufficient length of y")
+    return True
+
+
+def _check_gemm_lengths(ta, tb, m, n, k, a, lda, b, ldb, c, ldc, item):
+    # compute/sgemm.go:116-136; the dimension/ld checks (:30-71) happen in the C ABI with the same strings
+    if m <= 0 or n <= 0 or k < 0: return
+    la, lb, lc = _len(a, item), _len(b, item), _len(c, item)
+    if min(lda, ldb, ldc) < 1: return
+    if (la < (k - 1) * lda + m) if ta else (la < (m - 1) * lda + k): raise BlasPanic("blas: insufficient length of a")
+    if (lb < (n - 1) * ldb + k) if tb else (lb < (k - 1) * ldb + n): raise BlasPanic("blas: insufficient length of b")
+    if lc < (m - 1) * ldc + n: raise BlasPanic("blas: insufficient length of c")
+
+
+# ---------------------------------------------------------------- Level 1
+def Saxpy(n, alpha, x, incx, y, incy, stream=None):
+    if _check_level1(n, x, incx, y, incy, 4):
+        capi.check(_L().guda_saxpy(n, alpha, x.ptr, incx, y.ptr, incy, _sh(stream)), "Saxpy")
+
+
+def Daxpy(n, alpha, x, incx, y, incy, stream=None):
+    if _check_level1(n, x, incx, y, incy, 8):
+        capi.check(_L().guda_daxpy(n, alpha, x.ptr, incx, y.ptr, incy, _sh(stream)), "Daxpy")
+
+
+def Sdot(n, x, incx, y, incy, stream=None):
+    if incx == 0: raise BlasPanic("blas: zero x index increment")
+    if incy == 0: raise BlasPanic("blas: zero y index increment")
+    if n <= 0:
+        if n == 0: return np.float32(0)
+        raise BlasPanic("blas: n < 0")
+    _check_level1(n, x, incx, y, incy, 4)
+    r = C.c_float(0)
+    capi.check(_L().guda_sdot(n, x.ptr, incx, y.ptr, incy, C.byref(r), _sh(stream)), "Sdot")
+    return np.float32(r.value)
+
+
+def Ddot(n, x, incx, y, incy, stream=None):
+    if incx == 0: raise BlasPanic("blas: zero x index increment")
+    if incy == 0: raise BlasPanic("blas: zero y index increment")
+    if n <= 0:
+        if n == 0: return 0.0
+        raise BlasPanic("blas: n < 0")
+    _check_level1(n, x, incx, y, incy, 8)
+    r = C.c_double(0)
+    capi.check(_L().guda_ddot(n, x.ptr, incx, y.ptr, incy, C.byref(r), _sh(stream)), "Ddot")
+    return r.value
+
+
+def Sscal(n, alpha, x, incx, stream=None):
+    if incx < 1:
+        if incx == 0: raise BlasPanic("blas: zero x index increment")
+        return
+    if n < 1:
+        if n == 0: return
+        raise BlasPanic("blas: n < 0")
+    if (n - 1) * incx >= _len(x, 4): raise BlasPanic("blas: insufficient length of x")
+    capi.check(_L().guda_sscal(n, alpha, x.ptr, incx, _sh(stream)), "Sscal")
+
+
+def Dscal(n, alpha, x, incx, stream=None):
+    if incx < 1:
+        if incx == 0: raise BlasPanic("blas: zero x index increment")
+        return
+    if n < 1:
+        if n == 0: return
+        raise BlasPanic("blas: n < 0")
+    if (n - 1) * incx >= _len(x, 8): raise BlasPanic("blas: insufficient length of x")
+    capi.check(_L().guda_dscal(n, alpha, x.ptr, incx, _sh(stream)), "Dscal")
+
+
+def AXPY(alpha, x, y, n, stream=None):             # math.go:39-47
+    Saxpy(n, alpha, x, 1, y, 1, stream)
+
+
+def DOT(x, y, n, stream=None):                     # math.go:64-71
+    return Sdot(n, x, 1, y, 1, stream)
+
+
+def Scale(alpha, x, n, stream=None):               # math.go:170-177
+    Sscal(n, alpha, x, 1, stream)
+
+
+# ---------------------------------------------------------------- Level 3
+def GEMM(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream=None):   # math.go:98-129
+    _dims_then_lengths(transA, transB, m, n, k, a, lda, b, ldb, c, ldc, 4)
+    capi.check(_L().guda_sgemm(int(transA), int(transB), m, n, k, alpha, a.ptr, lda, b.ptr, ldb, beta, c.ptr, ldc, _sh(stream)), "GEMM")
+
+
+def Dgemm(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream=None):  # compute/dgemm.go:25
+    _dims_then_lengths(transA, transB, m, n, k, a, lda, b, ldb, c, ldc, 8)
+    capi.check(_L().guda_dgemm(int(transA), int(transB), m, n, k, alpha, a.ptr, lda, b.ptr, ldb, beta, c.ptr, ldc, _sh(stream)), "Dgemm")
+
+
+def _dims_then_lengths(ta, tb, m, n, k, a, lda, b, ldb, c, ldc, item):
+    # compute/sgemm.go:30-71 order: m, n, k, lda, ldb, ldc -- then (:74) quick return, then (:116-136) lengths
+    if m < 0: raise BlasPanic("blas: m < 0")
+    if n < 0: raise BlasPanic("blas: n < 0")
+    if k < 0: raise BlasPanic("blas: k < 0")
+    if lda < max(1, m if ta else k): raise BlasPanic("blas: bad leading dimension of A")
+    if ldb < max(1, k if tb else n): raise BlasPanic("blas: bad leading dimension of B")
+    if ldc < max(1, n): raise BlasPanic("blas: bad leading dimension of C")
+    _check_gemm_lengths(ta, tb, m, n, k, a, lda, b, ldb, c, ldc, item)
+
+
+Sgemm = GEMM
+
+
+def FusedGEMMBiasReLU(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, bias, stream=None):   # fused.go:313
+    if transA or transB or beta != 0:
+        raise ErrNotSupported(capi.ERR_NOT_IMPLEMENTED, "FusedGEMMBiasReLU", "operation not supported")
+    _dims_then_lengths(False, False, m, n, k, a, lda, b, ldb, c, ldc, 4)
+    capi.check(_L().guda_sgemm_bias_relu(0, 0, m, n, k, alpha, a.ptr, lda, b.ptr, ldb, beta, c.ptr, ldc, bias.ptr, _sh(stream)),
+               "FusedGEMMBiasReLU")
+
+
+def FusedGEMMBiasGELU(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, bias, stream=None):   # fused_gelu.go:65
+    if transA or transB or beta != 0:
+        raise ErrNotSupported(capi.ERR_NOT_IMPLEMENTED, "FusedGEMMBiasGELU", "operation not supported")
+    _dims_then_lengths(False, False, m, n, k, a, lda, b, ldb, c, ldc, 4)
+    capi.check(_L().guda_sgemm_bias_gelu(0, 0, m, n, k, alpha, a.ptr, lda, b.ptr, ldb, beta, c.ptr, ldc, bias.ptr, _sh(stream)),
+               "FusedGEMMBiasGELU")
+
+
+def AddBiasGELU(x, bias, n, stream=None):          # fused_gelu.go:12-41
+    capi.check(_L().guda_add_bias_gelu(x.ptr, bias.ptr, n, bias.size // 4, _sh(stream)), "AddBiasGELU")
+
+
+def AddBiasReLU(x, bias, n, stream=None):          # fused.go:220
+    capi.check(_L().guda_add_bias_relu(x.ptr, bias.ptr, n, bias.size // 4, _sh(stream)), "AddBiasReLU")
+
+
+def GEMMBFloat16(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream=None):   # bfloat16.go:104
+    capi.check(_L().guda_gemm_bf16(int(transA), int(transB), m, n, k, alpha, a.ptr, lda, b.ptr, ldb, beta, c.ptr, ldc, _sh(stream)),
+               "GEMMBFloat16")
+
+
+def GEMMFloat16(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream=None):    # float16.go:201
+    capi.check(_L().guda_gemm_f16(int(transA), int(transB), m, n, k, alpha, a.ptr, lda, b.ptr, ldb, beta, c.ptr, ldc, _sh(stream)),
+               "GEMMFloat16")
+
+
+def FusedGEMMBFloat16BiasGELU(m, n, k, alpha, a, lda, b, ldb, c, ldc, bias, stream=None):
+    capi.check(_L().guda_gemm_bf16_bias_gelu(m, n, k, alpha, a.ptr, lda, b.ptr, ldb, c.ptr, ldc, bias.ptr, _sh(stream)),
+               "FusedGEMMBFloat16BiasGELU")
+
+
+def FusedGEMMBFloat16BiasReLU(m, n, k, alpha, a, lda, b, ldb, c, ldc, bias, stream=None):
+    capi.check(_L().guda_gemm_bf16_bias_relu(m, n, k, alpha, a.ptr, lda, b.ptr, ldb, c.ptr, ldc, bias.ptr, _sh(stream)),
+               "FusedGEMMBFloat16BiasReLU")
+
+
+def SetSgemmMode(mode):
+    capi.check(_L().guda_set_sgemm_mode(mode), "SetSgemmMode")
+
+
+def SetGemm16Mode(mode):
+    capi.check(_L().guda_set_gemm16_mode(mode), "SetGemm16Mode")
+
+
+def FillUniform(ptr, rows, cols, ld, seed, row0=0, col0=0, full_cols=None, lo=-1.0, hi=1.0, dtype=np.float32, stream=None):
+    full_cols = cols if full_cols is None else full_cols
+    fn = _L().guda_fill_uniform_f32 if dtype == np.float32 else _L().guda_fill_uniform_f64
+    capi.check(fn(ptr.ptr, rows, cols, ld, seed, row0, col0, full_cols, lo, hi, _sh(stream)), "FillUniform")

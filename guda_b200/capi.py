@@ -1,0 +1,128 @@
+"""ctypes binding of include/guda_b200.h -- the same C ABI the Go cgo shim binds.
+
+No fallback of any kind: if the shared library is missing, or a compute entry point is
+called without a CUDA device, an exception is raised.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libguda_b200.so")
+
+OK, ERR_MEMORY, ERR_INVALID_ARG, ERR_EXECUTION, ERR_NUMERICAL, ERR_DEVICE, ERR_NOT_IMPLEMENTED = range(7)
+ERROR_TYPE_NAMES = {1: "Memory", 2: "InvalidArgument", 3: "Execution", 4: "Numerical", 5: "Device", 6: "NotImplemented"}
+MEMCPY_H2H, MEMCPY_H2D, MEMCPY_D2H, MEMCPY_D2D, MEMCPY_DEFAULT = range(5)
+COMM_ID_BYTES = 128
+
+
+class DeviceProps(C.Structure):
+    _fields_ = [("id", C.c_int), ("name", C.c_char * 128), ("total_mem", C.c_size_t), ("sm_count", C.c_int),
+                ("max_threads", C.c_int), ("cc_major", C.c_int), ("cc_minor", C.c_int), ("l2_bytes", C.c_int)]
+
+
+# name -> (restype, argtypes); every symbol include/guda_b200.h declares
+vp, i, f, d, sz, u64 = C.c_void_p, C.c_int, C.c_float, C.c_double, C.c_size_t, C.c_uint64
+ip, fp, dp, szp, i64p = C.POINTER(C.c_int), C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_size_t), C.POINTER(C.c_int64)
+SIGNATURES = {
+    "guda_last_error": (C.c_char_p, []),
+    "guda_version": (C.c_char_p, []),
+    "guda_init": (i, [i]),
+    "guda_device_count": (i, [ip]),
+    "guda_set_device": (i, [i]),
+    "guda_get_device": (i, [ip]),
+    "guda_device_properties": (i, [i, C.POINTER(DeviceProps)]),
+    "guda_device_synchronize": (i, []),
+    "guda_mem_get_info": (i, [szp, szp]),
+    "guda_malloc": (i, [C.POINTER(vp), sz]),
+    "guda_free": (i, [vp]),
+    "guda_pool_stats": (i, [i64p, i64p]),
+    "guda_pool_trim": (i, []),
+    "guda_malloc_host": (i, [C.POINTER(vp), sz]),
+    "guda_free_host": (i, [vp]),
+    "guda_memcpy": (i, [vp, vp, sz, i, vp]),
+    "guda_memcpy_async": (i, [vp, vp, sz, i, vp]),
+    "guda_memset": (i, [vp, i, sz, vp]),
+    "guda_stream_create": (i, [C.POINTER(vp)]),
+    "guda_stream_destroy": (i, [vp]),
+    "guda_stream_synchronize": (i, [vp]),
+    "guda_stream_query": (i, [vp, ip]),
+    "guda_stream_wait_event": (i, [vp, vp]),
+    "guda_stream_native": (i, [vp, C.POINTER(vp)]),
+    "guda_event_create": (i, [C.POINTER(vp)]),
+    "guda_event_destroy": (i, [vp]),
+    "guda_event_record": (i, [vp, vp]),
+    "guda_event_synchronize": (i, [vp]),
+    "guda_event_query": (i, [vp, ip]),
+    "guda_event_elapsed_ms": (i, [vp, vp, fp]),
+    "guda_saxpy": (i, [i, f, vp, i, vp, i, vp]),
+    "guda_sscal": (i, [i, f, vp, i, vp]),
+    "guda_sdot": (i, [i, vp, i, vp, i, fp, vp]),
+    "guda_sdot_device": (i, [i, vp, i, vp, i, vp, vp]),
+    "guda_daxpy": (i, [i, d, vp, i, vp, i, vp]),
+    "guda_dscal": (i, [i, d, vp, i, vp]),
+    "guda_ddot": (i, [i, vp, i, vp, i, dp, vp]),
+    "guda_ddot_device": (i, [i, vp, i, vp, i, vp, vp]),
+    "guda_set_sgemm_mode": (i, [i]),
+    "guda_get_sgemm_mode": (i, [ip]),
+    "guda_sgemm": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
+    "guda_dgemm": (i, [i, i, i, i, i, d, vp, i, vp, i, d, vp, i, vp]),
+    "guda_gemm_bf16": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
+    "guda_gemm_f16": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
+    "guda_set_gemm16_mode": (i, [i]),
+    "guda_get_gemm16_mode": (i, [ip]),
+    "guda_sgemm_bias_relu": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp, vp]),
+    "guda_sgemm_bias_gelu": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp, vp]),
+    "guda_gemm_bf16_bias_relu": (i, [i, i, i, f, vp, i, vp, i, vp, i, vp, vp]),
+    "guda_gemm_bf16_bias_gelu": (i, [i, i, i, f, vp, i, vp, i, vp, i, vp, vp]),
+    "guda_add_bias_gelu": (i, [vp, vp, i, i, vp]),
+    "guda_add_bias_relu": (i, [vp, vp, i, i, vp]),
+    "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
+    "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),
+    "guda_f32_to_f16": (i, [vp, vp, sz, vp]),
+    "guda_f16_to_f32": (i, [vp, vp, sz, vp]),
+    "guda_fill_uniform_f32": (i, [vp, sz, sz, sz, u64, u64, u64, u64, f, f, vp]),
+    "guda_fill_uniform_f64": (i, [vp, sz, sz, sz, u64, u64, u64, u64, d, d, vp]),
+    "guda_comm_unique_id": (i, [C.POINTER(C.c_uint8)]),
+    "guda_comm_init_rank": (i, [C.POINTER(vp), i, i, C.POINTER(C.c_uint8)]),
+    "guda_comm_destroy": (i, [vp]),
+    "guda_sgemm_sharded": (i, [vp, i, i, i, i, i, f, vp, i, vp, i, vp, i, vp, i, vp]),
+    "guda_sdot_sharded": (i, [vp, i, vp, vp, fp, vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load libguda_b200.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("%s not found: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(nvcc, sm_100a). There is no CPU fallback." % LIB_PATH)
+        lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)          # AttributeError if the header and the library disagree
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+class GUDAError(Exception):
+    """errors.go:27-44 GUDAError{Type, Op, Message}."""
+
+    def __init__(self, status, op, message):
+        self.type, self.op, self.message = status, op, message
+        super().__init__("GUDA %s error in %s: %s" % (ERROR_TYPE_NAMES.get(status, "Unknown"), op, message))
+
+
+class BlasPanic(Exception):
+    """A Go panic(string) of compute/errors.go:9-35, e.g. 'blas: m < 0'."""
+
+
+def check(status, op):
+    if status == OK:
+        return
+    msg = load().guda_last_error().decode()
+    if status == ERR_INVALID_ARG and msg.startswith("blas: "):
+        raise BlasPanic(msg)
+    raise GUDAError(status, op, msg)

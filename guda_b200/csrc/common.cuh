@@ -1,0 +1,54 @@
+// common.cuh -- shared plumbing for libguda_b200: status/last-error, stream handles, launch checks.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include "../../include/guda_b200.h"
+
+namespace guda {
+
+// thread-local last error (guda_last_error)
+char* last_error_buf();
+int set_error(int status, const char* fmt, ...);
+
+// Go panic strings (compute/errors.go:9-35), returned through guda_last_error with GUDA_ERR_INVALID_ARG
+#define GUDA_PANIC(msg) return ::guda::set_error(GUDA_ERR_INVALID_ARG, "%s", msg)
+
+#define GUDA_CUDA(call)                                                                              \
+  do {                                                                                               \
+    cudaError_t _e = (call);                                                                         \
+    if (_e != cudaSuccess)                                                                           \
+      return ::guda::set_error(::guda::map_cuda_error(_e), "%s failed: %s", #call, cudaGetErrorString(_e)); \
+  } while (0)
+
+int map_cuda_error(cudaError_t e);
+
+// binds the library's device to the calling OS thread (cgo may migrate goroutines between threads)
+int bind_device();
+int current_device();
+int sm_count();
+
+struct Stream { cudaStream_t s; };
+struct Event { cudaEvent_t e; };
+
+// NULL handle = the library's default (non-blocking) stream
+cudaStream_t native(guda_stream_t h);
+
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error(GUDA_ERR_EXECUTION, "%s launch failed: %s", what, cudaGetErrorString(e));
+  return GUDA_OK;
+}
+
+// scratch that lives as long as the library: pinned host scalars + device partials for reductions
+struct Scratch {
+  void* dev_partials;      // >= 64 KiB
+  unsigned int* dev_counter;
+  void* host_scalar;       // pinned, mapped
+  void* host_scalar_dev;   // device alias of host_scalar
+};
+int get_scratch(Scratch** out);
+
+}  // namespace guda

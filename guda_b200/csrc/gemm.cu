@@ -1,0 +1,240 @@
+// gemm.cu -- SGEMM / DGEMM / fused GEMM+bias+activation entry points on the exact-order SIMT kernels.
+// Replaces compute/sgemm.go:29-350 (Sgemm), compute/dgemm.go:25-362 + dgemm_fixed.go (Dgemm),
+// fused.go:313-368 and fused_gelu.go:65-137.
+#include "gemm_simt.cuh"
+
+namespace guda {
+
+int sgemm_mode();
+// tensor-core paths (gemm_tc.cu); return GUDA_OK if they handled the call, -1 if the shape is not eligible
+int sgemm_3xtf32_try(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
+                     float beta, float* c, int ldc, cudaStream_t s);
+
+// ---------------------------------------------------------------- tiny fast paths (compute/asm/f32/gemm_small.go:12-224)
+// 4^3 / 8^3 / 16^3 contiguous NN: unfused products summed in the reference's order, then alpha*s (+ beta*c).
+template <int S>
+__global__ void sgemm_small_kernel(float alpha, const float* __restrict__ a, const float* __restrict__ b, float beta, float* __restrict__ c) {
+  int i = threadIdx.x / S, j = threadIdx.x % S;
+  float s;
+  if (S == 4) {
+    s = __fadd_rn(__fmul_rn(a[i * 4 + 0], b[0 * 4 + j]), __fmul_rn(a[i * 4 + 1], b[1 * 4 + j]));
+    s = __fadd_rn(s, __fmul_rn(a[i * 4 + 2], b[2 * 4 + j]));
+    s = __fadd_rn(s, __fmul_rn(a[i * 4 + 3], b[3 * 4 + j]));
+  } else if (S == 8) {
+    s = 0.0f;
+    for (int k = 0; k < 8; k += 2) {
+      float p = __fadd_rn(__fmul_rn(a[i * 8 + k], b[k * 8 + j]), __fmul_rn(a[i * 8 + k + 1], b[(k + 1) * 8 + j]));
+      s = __fadd_rn(s, p);
+    }
+  } else {
+    s = 0.0f;
+    for (int k = 0; k < 16; k++) s = __fadd_rn(s, __fmul_rn(a[i * 16 + k], b[k * 16 + j]));
+  }
+  float cold = c[i * S + j];
+  __syncthreads();
+  c[i * S + j] = (beta == 0.0f) ? __fmul_rn(alpha, s) : __fadd_rn(__fmul_rn(alpha, s), __fmul_rn(beta, cold));
+}
+
+// ---------------------------------------------------------------- fp64 NN alpha==1 edges (compute/dgemm_fixed.go:29-37,48-56,60-67)
+// rows >= mi4 (all columns) and columns >= ni4 (rows < mi4): sum = 0; sum += a*b unfused; c = beta-scaled c + sum
+__global__ void dgemm_edge_kernel(int m, int n, int k, const double* __restrict__ a, long long lda, const double* __restrict__ b,
+                                  long long ldb, double beta, double* __restrict__ c, long long ldc, int mi4, int ni4) {
+  long long nrow_edge = (long long)(m - mi4) * n;
+  long long ncol_edge = (long long)mi4 * (n - ni4);
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < nrow_edge + ncol_edge; e += (long long)gridDim.x * blockDim.x) {
+    int i, j;
+    if (e < nrow_edge) { i = mi4 + (int)(e / n); j = (int)(e % n); }
+    else { long long f = e - nrow_edge; j = ni4 + (int)(f / mi4); i = (int)(f % mi4); }    // consecutive threads walk down a column
+    double sum = 0.0;
+    for (int l = 0; l < k; l++) sum = __dadd_rn(sum, __dmul_rn(a[(long long)i * lda + l], b[(long long)l * ldb + j]));
+    double cv = 0.0;
+    if (beta != 0.0) { cv = c[(long long)i * ldc + j]; if (beta != 1.0) cv = __dmul_rn(cv, beta); }
+    c[(long long)i * ldc + j] = __dadd_rn(cv, sum);
+  }
+}
+
+// ---------------------------------------------------------------- dispatch
+template <typename T> struct TileCfg;
+template <> struct TileCfg<float>  { static constexpr int BK = 16, MINB_BIG = 2, MINB_SMALL = 3; };
+template <> struct TileCfg<double> { static constexpr int BK = 8,  MINB_BIG = 1, MINB_SMALL = 2; };
+
+template <typename T, bool TA, bool TB, int MODE, int EPI>
+static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
+  constexpr int BK = TileCfg<T>::BK;
+  constexpr int VN = GemmVec<T>::N;
+  const long long big_tiles = (long long)((p.m + 127) / 128) * ((p.n + 127) / 128);
+  const bool big = big_tiles >= sm_count();
+  const int BMN = big ? 128 : 64;
+  auto aligned = [&](const void* ptr, long long ld) { return ((uintptr_t)ptr % 16 == 0) && (ld % VN == 0); };
+  const bool fast = (p.m % BMN == 0) && (p.n % BMN == 0) && (p.k % BK == 0) && aligned(p.a, p.lda) && aligned(p.b, p.ldb) &&
+                    aligned(p.c, p.ldc) && p.edge_m >= p.m && p.edge_n >= p.n;
+  dim3 grid((p.n + BMN - 1) / BMN, (p.m + BMN - 1) / BMN);
+  if (grid.y > 65535) return set_error(GUDA_ERR_INVALID_ARG, "m too large for one launch");
+  if (big) {
+    if (fast) gemm_simt_kernel<T, TA, TB, 128, 128, BK, MODE, EPI, true, TileCfg<T>::MINB_BIG><<<grid, 256, 0, s>>>(p);
+    else      gemm_simt_kernel<T, TA, TB, 128, 128, BK, MODE, EPI, false, TileCfg<T>::MINB_BIG><<<grid, 256, 0, s>>>(p);
+  } else {
+    if (fast) gemm_simt_kernel<T, TA, TB, 64, 64, BK, MODE, EPI, true, TileCfg<T>::MINB_SMALL><<<grid, 256, 0, s>>>(p);
+    else      gemm_simt_kernel<T, TA, TB, 64, 64, BK, MODE, EPI, false, TileCfg<T>::MINB_SMALL><<<grid, 256, 0, s>>>(p);
+  }
+  return check_launch("gemm");
+}
+
+// argument checks of compute/sgemm.go:30-71 (same order, same panic strings).  Slice-length checks
+// (:116-136) need the DevicePtr sizes and live in the host shim.
+static int check_gemm_args(int ta, int tb, int m, int n, int k, int lda, int ldb, int ldc) {
+  if ((ta != 0 && ta != 1) || (tb != 0 && tb != 1)) GUDA_PANIC("blas: illegal transpose");
+  if (m < 0) GUDA_PANIC("blas: m < 0");
+  if (n < 0) GUDA_PANIC("blas: n < 0");
+  if (k < 0) GUDA_PANIC("blas: k < 0");
+  auto mx = [](int a, int b) { return a > b ? a : b; };
+  if (ta) { if (lda < mx(1, m)) GUDA_PANIC("blas: bad leading dimension of A"); }
+  else    { if (lda < mx(1, k)) GUDA_PANIC("blas: bad leading dimension of A"); }
+  if (tb) { if (ldb < mx(1, k)) GUDA_PANIC("blas: bad leading dimension of B"); }
+  else    { if (ldb < mx(1, n)) GUDA_PANIC("blas: bad leading dimension of B"); }
+  if (ldc < mx(1, n)) GUDA_PANIC("blas: bad leading dimension of C");
+  return GUDA_OK;
+}
+
+static int sgemm_impl(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
+                      float beta, float* c, int ldc, const float* bias, int epi, guda_stream_t stream) {
+  int rc = check_gemm_args(ta, tb, m, n, k, lda, ldb, ldc);
+  if (rc) return rc;
+  if (m == 0 || n == 0) return GUDA_OK;                                   // compute/sgemm.go:74
+  rc = bind_device();
+  if (rc) return rc;
+  if (!c || ((!a || !b) && k > 0)) return set_error(GUDA_ERR_INVALID_ARG, "GEMM: null pointer");
+  cudaStream_t s = native(stream);
+  if (epi == EPI_NONE) {
+    // compute/sgemm.go:80-96 small-matrix kernels (NN contiguous only; the bTrans branch :98-111 multiplies by
+    // B as stored, a reference defect that is deliberately NOT reproduced -- see DESIGN.md)
+    if (!ta && !tb && lda == k && ldb == n && ldc == n && m == n && n == k && (m == 4 || m == 8 || m == 16)) {
+      if (m == 4) sgemm_small_kernel<4><<<1, 16, 0, s>>>(alpha, a, b, beta, c);
+      else if (m == 8) sgemm_small_kernel<8><<<1, 64, 0, s>>>(alpha, a, b, beta, c);
+      else sgemm_small_kernel<16><<<1, 256, 0, s>>>(alpha, a, b, beta, c);
+      return check_launch("sgemm_small");
+    }
+    if ((alpha == 0.0f || k == 0) && beta == 1.0f) return GUDA_OK;        // compute/sgemm.go:139
+    if (sgemm_mode() == GUDA_SGEMM_3XTF32) {
+      rc = sgemm_3xtf32_try(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, s);
+      if (rc >= 0) return rc;
+    }
+  }
+  GemmParams<float> p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, bias, m, n};
+  if (epi == EPI_BIAS_RELU) return launch_simt<float, false, false, MODE_FMA, EPI_BIAS_RELU>(p, s);
+  if (epi == EPI_BIAS_GELU) return launch_simt<float, false, false, MODE_FMA, EPI_BIAS_GELU>(p, s);
+  if (!ta && !tb) return launch_simt<float, false, false, MODE_FMA, EPI_NONE>(p, s);
+  if (ta && !tb)  return launch_simt<float, true, false, MODE_FMA, EPI_NONE>(p, s);
+  if (!ta && tb)  return launch_simt<float, false, true, MODE_FMA, EPI_NONE>(p, s);     // DotUnitary form: tolerance, not bit-exact
+  return launch_simt<float, true, true, MODE_UNFUSED, EPI_NONE>(p, s);                  // AxpyInc: unfused chain
+}
+
+static int dgemm_impl(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb,
+                      double beta, double* c, int ldc, guda_stream_t stream) {
+  int rc = check_gemm_args(ta, tb, m, n, k, lda, ldb, ldc);
+  if (rc) return rc;
+  if (m == 0 || n == 0) return GUDA_OK;
+  rc = bind_device();
+  if (rc) return rc;
+  if (!c || ((!a || !b) && k > 0)) return set_error(GUDA_ERR_INVALID_ARG, "Dgemm: null pointer");
+  if ((alpha == 0.0 || k == 0) && beta == 1.0) return GUDA_OK;            // compute/dgemm.go:99
+  cudaStream_t s = native(stream);
+  GemmParams<double> p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, nullptr, m, n};
+  // AxpyUnitary (fp64) is all-FMA only when every C row is 32-byte aligned and n % 4 == 0
+  const bool rows_aligned = ((uintptr_t)c % 32 == 0) && (m == 1 || ((long long)ldc * 8) % 32 == 0) && (n % 4 == 0);
+  if (!ta && !tb) {
+    if (alpha == 1.0) {
+      // compute/dgemm.go:243-247 -> dgemm_fixed.go: 8x8/4x4 FMA tiles + unfused edges
+      int mi4 = m / 4 * 4, ni4 = n / 4 * 4;
+      p.edge_m = mi4; p.edge_n = ni4;
+      if (mi4 < m || ni4 < n) {
+        long long edges = (long long)(m - mi4) * n + (long long)mi4 * (n - ni4);
+        unsigned grid = (unsigned)((edges + 127) / 128);
+        if (grid > (unsigned)sm_count() * 32) grid = sm_count() * 32;
+        dgemm_edge_kernel<<<grid, 128, 0, s>>>(m, n, k, a, lda, b, ldb, beta, c, ldc, mi4, ni4);
+        rc = check_launch("dgemm_edge");
+        if (rc) return rc;
+      }
+      if (mi4 == 0 || ni4 == 0) return GUDA_OK;
+      return launch_simt<double, false, false, MODE_FMA, EPI_NONE>(p, s);
+    }
+    return rows_aligned ? launch_simt<double, false, false, MODE_FMA, EPI_NONE>(p, s)
+                        : launch_simt<double, false, false, MODE_MIXED, EPI_NONE>(p, s);
+  }
+  if (ta && !tb)
+    return rows_aligned ? launch_simt<double, true, false, MODE_FMA, EPI_NONE>(p, s)
+                        : launch_simt<double, true, false, MODE_MIXED, EPI_NONE>(p, s);
+  if (!ta && tb) return launch_simt<double, false, true, MODE_FMA, EPI_NONE>(p, s);     // DotUnitary form: tolerance
+  return launch_simt<double, true, true, MODE_UNFUSED, EPI_NONE>(p, s);
+}
+
+// fp32 GEMM with the arithmetic of bfloat16.go:136-157 (sum = beta*c; sum += (alpha*a)*b, unfused, no zero test); NN only
+int sgemm_unfused_noskip(int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
+                         float* c, int ldc, cudaStream_t s) {
+  GemmParams<float> p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, nullptr, m, n};
+  return launch_simt<float, false, false, MODE_UNFUSED_NOSKIP, EPI_NONE>(p, s);
+}
+// exact-order SGEMM on an explicit cudaStream_t (used by the fp16 path: float16.go:231)
+int sgemm_exact_on(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
+                   float* c, int ldc, cudaStream_t s);
+
+// x[i] = act(x[i] + bias[i % bias_len])   (fused_gelu.go:12-41, fused.go:220-260)
+template <int EPI>
+__global__ void add_bias_act_kernel(float* __restrict__ x, const float* __restrict__ bias, int n, int bias_len) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    x[i] = apply_epilogue<float, EPI>(x[i], bias[i % bias_len]);
+}
+
+}  // namespace guda
+
+using namespace guda;
+extern "C" {
+
+int guda_sgemm(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
+               float* c, int ldc, guda_stream_t stream) {
+  return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, stream);
+}
+int guda_dgemm(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
+               double* c, int ldc, guda_stream_t stream) {
+  return dgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream);
+}
+
+static int fused_checks(int ta, int tb, float beta, const float* bias) {
+  if (ta || tb) return set_error(GUDA_ERR_NOT_IMPLEMENTED, "operation not supported");   // fused.go:324-326
+  if (beta != 0) return set_error(GUDA_ERR_NOT_IMPLEMENTED, "operation not supported");  // fused.go:327-329
+  if (!bias) return set_error(GUDA_ERR_INVALID_ARG, "null bias");
+  return GUDA_OK;
+}
+int guda_sgemm_bias_relu(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
+                         float beta, float* c, int ldc, const float* bias, guda_stream_t stream) {
+  int rc = fused_checks(ta, tb, beta, bias);
+  if (rc) return rc;
+  return sgemm_impl(0, 0, m, n, k, alpha, a, lda, b, ldb, 0.0f, c, ldc, bias, EPI_BIAS_RELU, stream);
+}
+int guda_sgemm_bias_gelu(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
+                         float beta, float* c, int ldc, const float* bias, guda_stream_t stream) {
+  int rc = fused_checks(ta, tb, beta, bias);
+  if (rc) return rc;
+  return sgemm_impl(0, 0, m, n, k, alpha, a, lda, b, ldb, 0.0f, c, ldc, bias, EPI_BIAS_GELU, stream);
+}
+
+static int add_bias_act(float* x, const float* bias, int n, int bias_len, guda_stream_t stream, bool gelu) {
+  if (n < 0 || bias_len <= 0) return set_error(GUDA_ERR_INVALID_ARG, "AddBias: bad length");
+  if (n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x || !bias) return set_error(GUDA_ERR_INVALID_ARG, "AddBias: null pointer");
+  int grid = (n + 255) / 256;
+  if (grid > sm_count() * 16) grid = sm_count() * 16;
+  if (gelu) add_bias_act_kernel<EPI_BIAS_GELU><<<grid, 256, 0, native(stream)>>>(x, bias, n, bias_len);
+  else add_bias_act_kernel<EPI_BIAS_RELU><<<grid, 256, 0, native(stream)>>>(x, bias, n, bias_len);
+  return check_launch("add_bias_act");
+}
+int guda_add_bias_gelu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream) {
+  return add_bias_act(x, bias, n, bias_len, stream, true);
+}
+int guda_add_bias_relu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream) {
+  return add_bias_act(x, bias, n, bias_len, stream, false);
+}
+
+}  // extern "C"

@@ -1,0 +1,180 @@
+// sharded.cu -- multi-GPU forms (new, additive API): 2-D block-partitioned SGEMM + all-gather of C,
+// sharded DOT + all-reduce.  One process per GPU; NCCL over NVLink 5 / NVSwitch, loaded at run time
+// (dlopen) so the library has no link-time NCCL dependency and single-GPU users never touch it.
+// The reference has no multi-device notion at all (guda.go:227-229 GetDeviceCount() == 1).
+#include "common.cuh"
+#include <dlfcn.h>
+#include <nccl.h>
+#include <mutex>
+
+namespace guda {
+
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+static std::mutex g_nccl_mu;
+
+static int load_nccl() {
+  std::lock_guard<std::mutex> lk(g_nccl_mu);
+  if (g_nccl.handle) return GUDA_OK;
+  // prefer a copy that is already in the process (e.g. the one torch loaded), then GUDA_NCCL_LIB, then the system one
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+  if (!h) { if (const char* e = getenv("GUDA_NCCL_LIB")) h = dlopen(e, RTLD_NOW | RTLD_GLOBAL); }
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return set_error(GUDA_ERR_DEVICE, "cannot load libnccl.so.2: %s", dlerror());
+#define SYM(field, name)                                                                    \
+  *(void**)(&g_nccl.field) = dlsym(h, name);                                                \
+  if (!g_nccl.field) return set_error(GUDA_ERR_DEVICE, "libnccl is missing %s", name);
+  SYM(GetUniqueId, "ncclGetUniqueId")
+  SYM(CommInitRank, "ncclCommInitRank")
+  SYM(CommDestroy, "ncclCommDestroy")
+  SYM(AllGather, "ncclAllGather")
+  SYM(AllReduce, "ncclAllReduce")
+  SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+  g_nccl.handle = h;
+  return GUDA_OK;
+}
+
+#define GUDA_NCCL(call)                                                                                      \
+  do {                                                                                                       \
+    ncclResult_t _r = (call);                                                                                \
+    if (_r != ncclSuccess) return set_error(GUDA_ERR_EXECUTION, "%s failed: %s", #call, g_nccl.GetErrorString(_r)); \
+  } while (0)
+
+struct Comm {
+  ncclComm_t comm;
+  int nranks, rank;
+  float* staging = nullptr;      // all-gather landing zone, grown on demand
+  size_t staging_bytes = 0;
+  float* dev_scalar = nullptr;
+};
+
+// gathered [rank][m_loc][n_loc] blocks -> row-major c_full; 128-bit copies when the geometry allows
+__global__ void unpack_blocks_kernel(const float* __restrict__ staging, float* __restrict__ c_full, long long ldc_full, int pr, int pc,
+                                     int m_loc, int n_loc) {
+  const long long per_block = (long long)m_loc * n_loc;
+  const long long total = per_block * pr * pc;
+  if ((n_loc & 3) == 0 && (ldc_full & 3) == 0 && ((uintptr_t)c_full & 15) == 0 && ((uintptr_t)staging & 15) == 0) {
+    const long long nv = total / 4;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += (long long)gridDim.x * blockDim.x) {
+      long long e = v * 4;
+      int q = (int)(e / per_block);
+      long long w = e % per_block;
+      int i = (int)(w / n_loc), j = (int)(w % n_loc);
+      int r = q / pc, c = q % pc;
+      float4 val = *reinterpret_cast<const float4*>(staging + e);
+      *reinterpret_cast<float4*>(c_full + ((long long)r * m_loc + i) * ldc_full + (long long)c * n_loc + j) = val;
+    }
+  } else {
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+      int q = (int)(e / per_block);
+      long long w = e % per_block;
+      int i = (int)(w / n_loc), j = (int)(w % n_loc);
+      int r = q / pc, c = q % pc;
+      c_full[((long long)r * m_loc + i) * ldc_full + (long long)c * n_loc + j] = staging[e];
+    }
+  }
+}
+
+}  // namespace guda
+
+using namespace guda;
+extern "C" {
+
+int guda_comm_unique_id(uint8_t host_id[GUDA_COMM_ID_BYTES]) {
+  int rc = load_nccl();
+  if (rc) return rc;
+  static_assert(sizeof(ncclUniqueId) == GUDA_COMM_ID_BYTES, "ncclUniqueId size");
+  ncclUniqueId id;
+  GUDA_NCCL(g_nccl.GetUniqueId(&id));
+  memcpy(host_id, &id, sizeof(id));
+  return GUDA_OK;
+}
+
+int guda_comm_init_rank(guda_comm_t* comm, int nranks, int rank, const uint8_t host_id[GUDA_COMM_ID_BYTES]) {
+  if (!comm || nranks < 1 || rank < 0 || rank >= nranks) return set_error(GUDA_ERR_INVALID_ARG, "comm_init_rank: bad arguments");
+  int rc = load_nccl();
+  if (rc) return rc;
+  rc = bind_device();
+  if (rc) return rc;
+  ncclUniqueId id;
+  memcpy(&id, host_id, sizeof(id));
+  Comm* c = new Comm();
+  c->nranks = nranks; c->rank = rank;
+  ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+  if (r != ncclSuccess) { delete c; return set_error(GUDA_ERR_EXECUTION, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(r)); }
+  cudaError_t e = cudaMalloc((void**)&c->dev_scalar, 256);
+  if (e != cudaSuccess) { g_nccl.CommDestroy(c->comm); delete c; return set_error(GUDA_ERR_MEMORY, "cudaMalloc: %s", cudaGetErrorString(e)); }
+  *comm = reinterpret_cast<guda_comm_t>(c);
+  return GUDA_OK;
+}
+
+int guda_comm_destroy(guda_comm_t comm) {
+  if (!comm) return set_error(GUDA_ERR_INVALID_ARG, "null communicator");
+  int rc = bind_device();
+  if (rc) return rc;
+  Comm* c = reinterpret_cast<Comm*>(comm);
+  cudaDeviceSynchronize();
+  g_nccl.CommDestroy(c->comm);
+  if (c->staging) cudaFree(c->staging);
+  if (c->dev_scalar) cudaFree(c->dev_scalar);
+  delete c;
+  return GUDA_OK;
+}
+
+int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha, const float* a_panel, int lda,
+                       const float* b_panel, int ldb, float* c_block, int ldc_block, float* c_full, int ldc_full, guda_stream_t stream) {
+  if (!comm) return set_error(GUDA_ERR_INVALID_ARG, "null communicator");
+  Comm* c = reinterpret_cast<Comm*>(comm);
+  if (pr < 1 || pc < 1 || pr * pc != c->nranks) return set_error(GUDA_ERR_INVALID_ARG, "process grid %dx%d does not match %d ranks", pr, pc, c->nranks);
+  if (m_total < 0) GUDA_PANIC("blas: m < 0");
+  if (n_total < 0) GUDA_PANIC("blas: n < 0");
+  if (m_total % pr || n_total % pc) return set_error(GUDA_ERR_INVALID_ARG, "m (n) must divide evenly over the process grid");
+  const int m_loc = m_total / pr, n_loc = n_total / pc;
+  if (ldc_block != n_loc) return set_error(GUDA_ERR_INVALID_ARG, "c_block must be packed (ldc_block == n/pc) for the all-gather");
+  // local block: full K, identical per-element k-order to the 1-GPU kernel -> bit-identical results
+  int rc = guda_sgemm(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, stream);
+  if (rc) return rc;
+  if (!c_full) return GUDA_OK;             // caller only wants its block
+  if (ldc_full < n_total) GUDA_PANIC("blas: bad leading dimension of C");
+  cudaStream_t s = native(stream);
+  const size_t per_block = (size_t)m_loc * n_loc;
+  if (pc == 1 && ldc_full == n_total) {
+    // row panels are contiguous in c_full: gather straight into place
+    GUDA_NCCL(g_nccl.AllGather(c_block, c_full, per_block, ncclFloat, c->comm, s));
+    return GUDA_OK;
+  }
+  size_t need = per_block * c->nranks * sizeof(float);
+  if (need > c->staging_bytes) {
+    GUDA_CUDA(cudaStreamSynchronize(s));
+    if (c->staging) GUDA_CUDA(cudaFree(c->staging));
+    c->staging = nullptr; c->staging_bytes = 0;
+    GUDA_CUDA(cudaMalloc((void**)&c->staging, need));
+    c->staging_bytes = need;
+  }
+  GUDA_NCCL(g_nccl.AllGather(c_block, c->staging, per_block, ncclFloat, c->comm, s));
+  unpack_blocks_kernel<<<sm_count() * 8, 256, 0, s>>>(c->staging, c_full, ldc_full, pr, pc, m_loc, n_loc);
+  return check_launch("unpack_blocks");
+}
+
+int guda_sdot_sharded(guda_comm_t comm, int n_local, const float* x, const float* y, float* host_result, guda_stream_t stream) {
+  if (!comm || !host_result) return set_error(GUDA_ERR_INVALID_ARG, "sdot_sharded: null argument");
+  Comm* c = reinterpret_cast<Comm*>(comm);
+  int rc = guda_sdot_device(n_local, x, 1, y, 1, c->dev_scalar, stream);
+  if (rc) return rc;
+  cudaStream_t s = native(stream);
+  GUDA_NCCL(g_nccl.AllReduce(c->dev_scalar, c->dev_scalar, 1, ncclFloat, ncclSum, c->comm, s));
+  GUDA_CUDA(cudaMemcpyAsync(host_result, c->dev_scalar, sizeof(float), cudaMemcpyDeviceToHost, s));
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  return GUDA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,179 @@
+/*
+ * guda_b200.h -- C ABI of the B200-native replacement for GUDA's BLAS hot path.
+ *
+ * This is the drop-in boundary: exactly what a cgo shim behind GUDA's Go API
+ * (package guda, root directory of LynnColeArt/guda) binds.  Each entry point
+ * cites the reference interface it replaces (file:line in the reference).
+ * All pointers are DEVICE pointers unless the parameter name starts with host_.
+ * Every function returns a guda_status_t (0 = OK); guda_last_error() returns a
+ * thread-local message.  For BLAS argument violations the message is the exact
+ * Go panic string of compute/errors.go:9-35 (e.g. "blas: m < 0"), so the Go shim
+ * can re-panic with the reference's text.
+ *
+ * Matrices are ROW-MAJOR with ld = row stride, as in gonum/GUDA
+ * (compute/sgemm.go:51-71).  There is no CPU fallback: without a CUDA device
+ * every compute entry point fails with GUDA_ERR_DEVICE.
+ */
+#ifndef GUDA_B200_H
+#define GUDA_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* errors.go:11-24 ErrorType (+1 so that 0 is success) */
+typedef enum {
+  GUDA_OK = 0,
+  GUDA_ERR_MEMORY = 1,          /* ErrTypeMemory */
+  GUDA_ERR_INVALID_ARG = 2,     /* ErrTypeInvalidArg */
+  GUDA_ERR_EXECUTION = 3,       /* ErrTypeExecution */
+  GUDA_ERR_NUMERICAL = 4,       /* ErrTypeNumerical */
+  GUDA_ERR_DEVICE = 5,          /* ErrTypeDevice */
+  GUDA_ERR_NOT_IMPLEMENTED = 6  /* ErrTypeNotImplemented; also ErrNotSupported (fused.go:11-17) */
+} guda_status_t;
+
+/* memory.go:13-21 MemcpyKind (iota order) */
+typedef enum {
+  GUDA_MEMCPY_H2H = 0, GUDA_MEMCPY_H2D = 1, GUDA_MEMCPY_D2H = 2, GUDA_MEMCPY_D2D = 3, GUDA_MEMCPY_DEFAULT = 4
+} guda_memcpy_kind_t;
+
+typedef struct guda_stream_s* guda_stream_t;   /* NULL = the default stream (guda.go:124-127) */
+typedef struct guda_event_s*  guda_event_t;
+
+typedef struct {                /* guda.go:34-40 Device, extended with what a GPU has */
+  int    id;
+  char   name[128];
+  size_t total_mem;
+  int    sm_count;              /* Device.NumCores */
+  int    max_threads;           /* Device.MaxThreads: sm_count * max threads per SM */
+  int    cc_major, cc_minor;
+  int    l2_bytes;
+} guda_device_props_t;
+
+const char* guda_last_error(void);
+const char* guda_version(void);
+
+/* ---- device / context: guda.go:109-128 init(), :209-237 GetDevice/SetDevice/GetDeviceCount/GetDeviceProperties ---- */
+int guda_init(int device);
+int guda_device_count(int* count);
+int guda_set_device(int device);
+int guda_get_device(int* device);
+int guda_device_properties(int device, guda_device_props_t* props);
+int guda_device_synchronize(void);                        /* guda.go:278-283 Context.Synchronize */
+int guda_mem_get_info(size_t* free_bytes, size_t* total_bytes);   /* docs/manual/07-runtime-api.md MemGetInfo */
+
+/* ---- memory: memory.go:57-66 Malloc/Free, :150-234 MemoryPool, :81-145 Memcpy ----
+ * Pool semantics kept: size rounded up (here to 256 B, the cudaMalloc granule; the reference
+ * rounds to 64 B), first-fit reuse of freed blocks, unknown pointer -> MEMORY error,
+ * second free -> MEMORY error "double free detected", stats: allocated falls on free, peak never. */
+int guda_malloc(void** dptr, size_t size);
+int guda_free(void* dptr);
+int guda_pool_stats(int64_t* allocated, int64_t* peak);   /* memory.go:230-234 GetStats */
+int guda_pool_trim(void);                                 /* new: return cached blocks to the driver */
+int guda_malloc_host(void** host_ptr, size_t size);       /* pinned staging for H2D/D2H */
+int guda_free_host(void* host_ptr);
+int guda_memcpy(void* dst, const void* src, size_t size, int kind, guda_stream_t stream);       /* blocking, like the reference */
+int guda_memcpy_async(void* dst, const void* src, size_t size, int kind, guda_stream_t stream); /* manual: MemcpyAsync */
+int guda_memset(void* dptr, int value, size_t size, guda_stream_t stream);                      /* manual: Memset */
+
+/* ---- streams and events: guda.go:57-62,242-305 Stream; docs/manual/07-runtime-api.md:122,179-192 ---- */
+int guda_stream_create(guda_stream_t* stream);
+int guda_stream_destroy(guda_stream_t stream);
+int guda_stream_synchronize(guda_stream_t stream);        /* Stream.Synchronize guda.go:297-299 */
+int guda_stream_query(guda_stream_t stream, int* done);
+int guda_stream_wait_event(guda_stream_t stream, guda_event_t event);
+int guda_stream_native(guda_stream_t stream, void** cuda_stream);   /* the cudaStream_t behind a handle (for timing/interop) */
+int guda_event_create(guda_event_t* event);
+int guda_event_destroy(guda_event_t event);
+int guda_event_record(guda_event_t event, guda_stream_t stream);
+int guda_event_synchronize(guda_event_t event);
+int guda_event_query(guda_event_t event, int* done);
+int guda_event_elapsed_ms(guda_event_t start, guda_event_t stop, float* ms);
+
+/* ---- Level 1, fp32: math.go:39,64,170 AXPY/DOT/Scale -> compute/level1float32.go:225,619, level1float32_sdot.go:18 ----
+ * Stream-ordered and asynchronous, except *_dot with a host result, which blocks until the scalar is on the host. */
+int guda_saxpy(int n, float alpha, const float* x, int incx, float* y, int incy, guda_stream_t stream);
+int guda_sscal(int n, float alpha, float* x, int incx, guda_stream_t stream);
+int guda_sdot(int n, const float* x, int incx, const float* y, int incy, float* host_result, guda_stream_t stream);
+int guda_sdot_device(int n, const float* x, int incx, const float* y, int incy, float* dev_result, guda_stream_t stream);
+/* ---- Level 1, fp64: compute/level1float64.go:211,595, level1float64_ddot.go:14 ---- */
+int guda_daxpy(int n, double alpha, const double* x, int incx, double* y, int incy, guda_stream_t stream);
+int guda_dscal(int n, double alpha, double* x, int incx, guda_stream_t stream);
+int guda_ddot(int n, const double* x, int incx, const double* y, int incy, double* host_result, guda_stream_t stream);
+int guda_ddot_device(int n, const double* x, int incx, const double* y, int incy, double* dev_result, guda_stream_t stream);
+
+/* ---- Level 3: math.go:98 GEMM -> compute/sgemm.go:29 Sgemm; compute/dgemm.go:25 Dgemm ----
+ * C = alpha*op(A)*op(B) + beta*C, trans flags 0/1.  SGEMM math modes:
+ *   GUDA_SGEMM_EXACT  exact-FP32 SIMT; NN/TN/TT forms reproduce the reference's per-element
+ *                     sequential-k FMA (or unfused, TT) chain bit-for-bit
+ *   GUDA_SGEMM_3XTF32 tcgen05 tensor cores, 3xTF32 split with fp32 TMEM accumulation (stated tolerance) */
+enum { GUDA_SGEMM_EXACT = 0, GUDA_SGEMM_3XTF32 = 1 };
+int guda_set_sgemm_mode(int mode);
+int guda_get_sgemm_mode(int* mode);
+int guda_sgemm(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* a, int lda,
+               const float* b, int ldb, float beta, float* c, int ldc, guda_stream_t stream);
+int guda_dgemm(int trans_a, int trans_b, int m, int n, int k, double alpha, const double* a, int lda,
+               const double* b, int ldb, double beta, double* c, int ldc, guda_stream_t stream);
+/* bfloat16.go:104 GEMMBFloat16 (trans flags ignored by the reference -> must be 0 here), float16.go:201 GEMMFloat16.
+ * 16-bit storage, fp32 accumulation; a/b/c are uint16 bit patterns. */
+int guda_gemm_bf16(int trans_a, int trans_b, int m, int n, int k, float alpha, const uint16_t* a, int lda,
+                   const uint16_t* b, int ldb, float beta, uint16_t* c, int ldc, guda_stream_t stream);
+int guda_gemm_f16(int trans_a, int trans_b, int m, int n, int k, float alpha, const uint16_t* a, int lda,
+                  const uint16_t* b, int ldb, float beta, uint16_t* c, int ldc, guda_stream_t stream);
+
+/* 16-bit GEMM route: TENSOR = tcgen05 tensor cores when the shape is eligible (default); EXACT = upconvert +
+ * exact-order fp32 SIMT + truncate, reproducing the reference's bits */
+enum { GUDA_GEMM16_TENSOR = 0, GUDA_GEMM16_EXACT = 1 };
+int guda_set_gemm16_mode(int mode);
+int guda_get_gemm16_mode(int* mode);
+
+/* ---- fused GEMM + bias + activation: fused.go:313 FusedGEMMBiasReLU, fused_gelu.go:65 FusedGEMMBiasGELU ----
+ * C = act(alpha*A*B + bias[j]) with the epilogue applied in registers before the single store of C.
+ * trans_a/trans_b != 0 or beta != 0 -> GUDA_ERR_NOT_IMPLEMENTED (ErrNotSupported, fused.go:324-329). */
+int guda_sgemm_bias_relu(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* a, int lda,
+                         const float* b, int ldb, float beta, float* c, int ldc, const float* bias, guda_stream_t stream);
+int guda_sgemm_bias_gelu(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* a, int lda,
+                         const float* b, int ldb, float beta, float* c, int ldc, const float* bias, guda_stream_t stream);
+int guda_gemm_bf16_bias_relu(int m, int n, int k, float alpha, const uint16_t* a, int lda, const uint16_t* b, int ldb,
+                             uint16_t* c, int ldc, const float* bias, guda_stream_t stream);
+int guda_gemm_bf16_bias_gelu(int m, int n, int k, float alpha, const uint16_t* a, int lda, const uint16_t* b, int ldb,
+                             uint16_t* c, int ldc, const float* bias, guda_stream_t stream);
+/* standalone epilogue: fused_gelu.go:12 AddBiasGELU, fused.go:220 AddBiasReLU: x[i] = act(x[i] + bias[i % bias_len]) */
+int guda_add_bias_gelu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
+int guda_add_bias_relu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
+
+/* ---- conversions: bfloat16.go:12-29, float16.go:21-87 (device-side bulk convert) ---- */
+int guda_f32_to_bf16(const float* src, uint16_t* dst, size_t n, guda_stream_t stream);
+int guda_bf16_to_f32(const uint16_t* src, float* dst, size_t n, guda_stream_t stream);
+int guda_f32_to_f16(const float* src, uint16_t* dst, size_t n, guda_stream_t stream);
+int guda_f16_to_f32(const uint16_t* src, float* dst, size_t n, guda_stream_t stream);
+
+/* ---- synthetic data on the device (bench / large-config parity): counter-based, any sub-block reproducible ---- */
+int guda_fill_uniform_f32(float* dst, size_t rows, size_t cols, size_t ld, uint64_t seed, uint64_t row0, uint64_t col0,
+                          uint64_t full_cols, float lo, float hi, guda_stream_t stream);
+int guda_fill_uniform_f64(double* dst, size_t rows, size_t cols, size_t ld, uint64_t seed, uint64_t row0, uint64_t col0,
+                          uint64_t full_cols, double lo, double hi, guda_stream_t stream);
+
+/* ---- multi-GPU (new, additive: GetDeviceCount()==1 stays pinned for the single-device API, guda_test.go:332) ----
+ * One process per GPU.  The communicator wraps NCCL (loaded at run time); id bytes come from
+ * guda_comm_unique_id on rank 0 and travel out of band (the Go shim or torch.distributed). */
+typedef struct guda_comm_s* guda_comm_t;
+#define GUDA_COMM_ID_BYTES 128
+int guda_comm_unique_id(uint8_t host_id[GUDA_COMM_ID_BYTES]);
+int guda_comm_init_rank(guda_comm_t* comm, int nranks, int rank, const uint8_t host_id[GUDA_COMM_ID_BYTES]);
+int guda_comm_destroy(guda_comm_t comm);
+/* 2-D block-partitioned SGEMM: this rank owns A row panel (m_local x k), B column panel (k x n_local), computes
+ * its C block with full K locally, then all-gathers the blocks so c_full (m_total x n_total, ld = ldc_full) is
+ * complete on every rank.  grid = pr x pc, rank = r*pc + c. */
+int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha,
+                       const float* a_panel, int lda, const float* b_panel, int ldb, float* c_block, int ldc_block,
+                       float* c_full, int ldc_full, guda_stream_t stream);
+/* per-GPU partial dot products combined by ncclAllReduce(sum) */
+int guda_sdot_sharded(guda_comm_t comm, int n_local, const float* x, const float* y, float* host_result, guda_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

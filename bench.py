@@ -1,0 +1,439 @@
+#!/usr/bin/env python
+"""bench.py -- GUDA BLAS hot path on B200: throughput, roofline fraction and the CPU baseline beside it.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (N>1: launched by torchrun, one rank per GPU)
+  python bench.py --impl reference --gpus N --steps K ...  the reference's CPU path (oracle port) on the host cores
+
+Headline workload (BASELINE.json configs[4], the large-GEMM config the north star scales over 1/2/4/8 GPUs):
+SGEMM 65536^3 fp32, 2-D block-partitioned, C all-gathered over NVLink at N>1 -- STRONG scaling (total work fixed).
+A "step" is one full C = A*B.  The other BASELINE configs (C1 SGEMM 1024^3, C2 SAXPY/SDOT 16M, C3 fused FFN,
+C4 DGEMM 16384^3) run once per invocation at N=1 and are reported in the same JSON line under "suite", each with
+its own roofline.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=int(os.environ.get("GUDA_BENCH_SIZE", "65536")), help="N of the headline N^3 SGEMM")
+    ap.add_argument("--mode", default=os.environ.get("GUDA_BENCH_SGEMM_MODE", "exact"), choices=["exact", "3xtf32"])
+    ap.add_argument("--no-suite", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return {"hbm_gbs": p["hbm_gbs"], "bf16_tflops": p["bf16_tflops"], "bf16_tflops_sustained": p.get("bf16_tflops_sustained"),
+                "source": "measured"}
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ---------------------------------------------------------------- reference arm / CPU baseline (oracle port)
+CPU_SAMPLE_N = 4096
+
+
+def cpu_sgemm_sample(steps, warmup, threads):
+    """The reference's CPU SGEMM path (oracle port of compute/sgemm.go on the AVX2+FMA route, one task per 64x64
+    C block over all host threads) on a bounded sample of the headline workload: SGEMM CPU_SAMPLE_N^3."""
+    from oracle import oracle as O
+    n = CPU_SAMPLE_N
+    a = O.uniform_f32(n * n, 1); b = O.uniform_f32(n * n, 2); c = np.zeros(n * n, dtype=np.float32)
+    for _ in range(warmup):
+        O.sgemm(0, 0, n, n, n, 1.0, a, n, b, n, 0.0, c, n, threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.sgemm(0, 0, n, n, n, 1.0, a, n, b, n, 0.0, c, n, threads=threads)
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    return 2.0 * n ** 3 / dt / 1e12, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    tf, dt = cpu_sgemm_sample(args.steps, min(args.warmup, 1), cores)
+    sample = "SGEMM %d^3 fp32 per step (bounded sample of the %d^3 headline; oracle port of compute/sgemm.go, %d threads)" % (
+        CPU_SAMPLE_N, args.size, cores)
+    line = {"impl": "reference", "metric": "sgemm_tflops", "value": tf, "unit": "TFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "SGEMM %d^3 fp32 NN alpha=1 beta=0 (BASELINE configs[4])" % args.size, "sample": sample},
+            "cpu_baseline": {"value": tf, "unit": "TFLOP/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": tf, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------- device helpers
+class Dev:
+    def __init__(self, local_rank):
+        import guda_b200 as g
+        self.g = g
+        g.Init(local_rank)
+        self.L = g.load()
+        self.e0, self.e1 = g.Event(), g.Event()
+
+    def time_ms(self, fn, iters=1):
+        """CUDA events on the library's stream around `iters` calls of fn()."""
+        self.e0.Record()
+        for _ in range(iters):
+            fn()
+        self.e1.Record()
+        self.e1.Synchronize()
+        return self.g.ElapsedTime(self.e0, self.e1) / iters
+
+    def peak(self, kind):
+        v = C.c_double(0)
+        self.g.capi.check(self.L.guda_microbench_peak(kind, 3, C.byref(v)), "microbench")
+        return v.value
+
+
+def suite(dev, peaks, ffma_peak, dfma_peak):
+    """BASELINE configs C1..C4 at one GPU; inputs resident in HBM; rotating buffer sets larger than L2."""
+    g = dev.g
+    out = {}
+    # ---- C2: SAXPY / SDOT n = 2^24, alpha = 2.5 (benchmark_test.go:47); 4 rotating pairs = 512 MiB > 126 MB L2
+    n = 1 << 24
+    pairs = []
+    for i in range(4):
+        x, y = g.Malloc(n * 4), g.Malloc(n * 4)
+        g.FillUniform(x, 1, n, n, 100 + i); g.FillUniform(y, 1, n, n, 200 + i)
+        pairs.append((x, y))
+    it = [0]
+
+    def axpy():
+        x, y = pairs[it[0] % 4]; it[0] += 1
+        g.AXPY(2.5, x, y, n)
+
+    def dot():
+        x, y = pairs[it[0] % 4]; it[0] += 1
+        r = C.c_float(0)
+        dev.L.guda_sdot_device(n, x.ptr, 1, y.ptr, 1, scal.ptr, None)
+
+    scal = g.Malloc(64)
+    for _ in range(8):
+        axpy(); dot()
+    ms = dev.time_ms(axpy, 40)
+    gbs = 12.0 * n / (ms * 1e-3) / 1e9
+    out["saxpy_16M"] = {"value": gbs, "unit": "GB/s", "ms": ms, "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"],
+                        "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"]}}
+    ms = dev.time_ms(dot, 40)
+    gbs = 8.0 * n / (ms * 1e-3) / 1e9
+    out["sdot_16M"] = {"value": gbs, "unit": "GB/s", "ms": ms, "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"],
+                       "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"]}}
+    # blocking DOT through the public call (host scalar back every call)
+    t0 = time.perf_counter()
+    for _ in range(40):
+        x, y = pairs[it[0] % 4]; it[0] += 1
+        g.DOT(x, y, n)
+    out["sdot_16M"]["blocking_call_gbs"] = 8.0 * n / ((time.perf_counter() - t0) / 40) / 1e9
+    for x, y in pairs:
+        g.Free(x); g.Free(y)
+    g.Free(scal)
+
+    # ---- C1: SGEMM 1024^3 (README headline), alpha=1 beta=0; 16 rotating triples (192 MiB)
+    n = 1024
+    sets = []
+    for i in range(16):
+        a, b, c = g.Malloc(n * n * 4), g.Malloc(n * n * 4), g.Malloc(n * n * 4)
+        g.FillUniform(a, n, n, n, 300 + i); g.FillUniform(b, n, n, n, 400 + i)
+        sets.append((a, b, c))
+
+    def sg():
+        a, b, c = sets[it[0] % 16]; it[0] += 1
+        dev.L.guda_sgemm(0, 0, n, n, n, 1.0, a.ptr, n, b.ptr, n, 0.0, c.ptr, n, None)
+
+    for _ in range(5):
+        sg()
+    ms = dev.time_ms(sg, 50)
+    tf = 2.0 * n ** 3 / (ms * 1e-3) / 1e12
+    out["sgemm_1024"] = {"value": tf, "unit": "TFLOP/s", "ms": ms, "roofline": {"bound": "fp32_simt", "achieved": tf, "peak": ffma_peak,
+                         "unit": "TFLOP/s", "frac": tf / ffma_peak, "peak_source": "FFMA microbenchmark, this run"}}
+    for a, b, c in sets:
+        g.Free(a); g.Free(b); g.Free(c)
+
+    # ---- C3: fused GEMM + bias + GELU, FFN shape M=8192 K=4096 N=16384, fp32
+    M, K, N = 8192, 4096, 16384
+    a, b, c, bias = g.Malloc(M * K * 4), g.Malloc(K * N * 4), g.Malloc(M * N * 4), g.Malloc(N * 4)
+    s = 1.0 / np.sqrt(K)
+    g.FillUniform(a, M, K, K, 500); g.FillUniform(b, K, N, N, 501, lo=-3 * s, hi=3 * s); g.FillUniform(bias, 1, N, N, 502)
+
+    def fused():
+        dev.L.guda_sgemm_bias_gelu(0, 0, M, N, K, 1.0, a.ptr, K, b.ptr, N, 0.0, c.ptr, N, bias.ptr, None)
+
+    def plain():
+        dev.L.guda_sgemm(0, 0, M, N, K, 1.0, a.ptr, K, b.ptr, N, 0.0, c.ptr, N, None)
+
+    fused()
+    ms = dev.time_ms(fused, 3)
+    ms_plain = dev.time_ms(plain, 3)
+    tf = 2.0 * M * N * K / (ms * 1e-3) / 1e12
+    out["fused_gemm_bias_gelu_f32_8192x4096x16384"] = {
+        "value": tf, "unit": "TFLOP/s", "ms": ms, "ms_plain_sgemm_same_shape": ms_plain,
+        "roofline": {"bound": "fp32_simt", "achieved": tf, "peak": ffma_peak, "unit": "TFLOP/s", "frac": tf / ffma_peak,
+                     "peak_source": "FFMA microbenchmark, this run"}}
+    for p in (a, b, c, bias):
+        g.Free(p)
+
+    # ---- C4: DGEMM 16384^3, alpha=1 beta=0
+    n = 16384
+    a, b, c = g.Malloc(n * n * 8), g.Malloc(n * n * 8), g.Malloc(n * n * 8)
+    g.FillUniform(a, n, n, n, 600, dtype=np.float64); g.FillUniform(b, n, n, n, 601, dtype=np.float64)
+
+    def dg():
+        dev.L.guda_dgemm(0, 0, n, n, n, 1.0, a.ptr, n, b.ptr, n, 0.0, c.ptr, n, None)
+
+    dg()
+    ms = dev.time_ms(dg, 2)
+    tf = 2.0 * n ** 3 / (ms * 1e-3) / 1e12
+    out["dgemm_16384"] = {"value": tf, "unit": "TFLOP/s", "ms": ms, "roofline": {"bound": "fp64_simt", "achieved": tf, "peak": dfma_peak,
+                          "unit": "TFLOP/s", "frac": tf / dfma_peak, "peak_source": "DFMA microbenchmark, this run"}}
+    for p in (a, b, c):
+        g.Free(p)
+    dev.L.guda_pool_trim()
+    return out
+
+
+# ---------------------------------------------------------------- headline: SGEMM size^3, strong scaling over a pr x pc grid
+GRID = {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4)}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if rank == 0:
+            print("bench.py: --gpus %d but WORLD_SIZE=%d (launch N>1 with torchrun)" % (args.gpus, world), file=sys.stderr)
+        sys.exit(2)
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    dev = Dev(local_rank)
+    g, L = dev.g, dev.L
+    peaks = measured_peaks()
+    if args.mode == "3xtf32":
+        g.SetSgemmMode(1)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        g.Synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ffma_peak = dev.peak(0)
+    dfma_peak = dev.peak(1) if rank == 0 else 0.0
+    copy_peak = dev.peak(2) if rank == 0 else 0.0
+
+    n = args.size
+    pr, pc = GRID[world]
+    m_loc, n_loc = n // pr, n // pc
+    r, c = rank // pc, rank % pc
+    comm = None
+    if world > 1:
+        ident = (C.c_uint8 * 128)()
+        if rank == 0:
+            g.capi.check(L.guda_comm_unique_id(ident), "CommUniqueId")
+        obj = [bytes(ident)]
+        dist.broadcast_object_list(obj, src=0)
+        ident = (C.c_uint8 * 128).from_buffer_copy(obj[0])
+        h = C.c_void_p()
+        g.capi.check(L.guda_comm_init_rank(C.byref(h), world, rank, ident), "CommInitRank")
+        comm = h
+
+    # A row panel (m_loc x n), B column panel (n x n_loc), generated on the device from the same counter-based
+    # stream as the full matrices: U[-1,1), alpha = 1, beta = 0 (benchmark_test.go:124 form)
+    a_panel = g.Malloc(m_loc * n * 4); b_panel = g.Malloc(n * n_loc * 4); c_block = g.Malloc(m_loc * n_loc * 4)
+    c_full = g.Malloc(n * n * 4) if world > 1 else None
+    g.FillUniform(a_panel, m_loc, n, n, seed=11, row0=r * m_loc, col0=0, full_cols=n)
+    g.FillUniform(b_panel, n, n_loc, n_loc, seed=12, row0=0, col0=c * n_loc, full_cols=n)
+    g.Synchronize()
+
+    def step():
+        if world == 1:
+            g.capi.check(L.guda_sgemm(0, 0, n, n, n, 1.0, a_panel.ptr, n, b_panel.ptr, n, 0.0, c_block.ptr, n, None), "Sgemm")
+        else:
+            g.capi.check(L.guda_sgemm_sharded(comm, pr, pc, n, n, n, 1.0, a_panel.ptr, n, b_panel.ptr, n_loc, c_block.ptr, n_loc,
+                                              c_full.ptr, n, None), "SgemmSharded")
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    ms = dev.time_ms(step, args.steps)            # CUDA events on the launching stream, K steps back to back
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(ms)
+    flops = 2.0 * n ** 3
+    value = flops / (ms * 1e-3) / 1e12
+
+    # dominant kernel alone (the local block GEMM), for the roofline
+    def local_gemm():
+        L.guda_sgemm(0, 0, m_loc, n_loc, n, 1.0, a_panel.ptr, n, b_panel.ptr, n_loc, 0.0, c_block.ptr, n_loc, None)
+    kern_ms = dev.time_ms(local_gemm, 1) if world > 1 else ms
+    kern_tf = 2.0 * m_loc * n_loc * n / (kern_ms * 1e-3) / 1e12
+    if args.mode == "exact":
+        roof = {"bound": "fp32_simt", "achieved": kern_tf, "peak": ffma_peak, "unit": "TFLOP/s", "frac": kern_tf / ffma_peak,
+                "peak_source": "FFMA microbenchmark measured in this run (MEASURED_PEAKS.json has no fp32 SIMT figure)",
+                "frac_of_measured_bf16_tensor_peak": kern_tf / peaks["bf16_tflops_sustained"], "traffic": None}
+    else:
+        tpeak = peaks["bf16_tflops_sustained"] / 2.0 / 3.0     # TF32 = half the bf16 rate, three MMAs per product
+        roof = {"bound": "tensor", "achieved": kern_tf, "peak": tpeak, "unit": "TFLOP/s", "frac": kern_tf / tpeak,
+                "peak_source": "MEASURED_PEAKS.json bf16 sustained / 2 (tf32) / 3 (3xTF32 split), %s" % peaks["source"], "traffic": None}
+
+    # ---- e2e: the public call with HOST buffers; H2D of this rank's panels and D2H of its C block inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        import psutil
+        need = (m_loc * n + n * n_loc + m_loc * n_loc) * 4
+        avail = psutil.virtual_memory().available // max(world, 1)
+        if need * 1.2 < avail:
+            ha, hb, hc = C.c_void_p(), C.c_void_p(), C.c_void_p()
+            g.capi.check(L.guda_malloc_host(C.byref(ha), m_loc * n * 4), "MallocHost")
+            g.capi.check(L.guda_malloc_host(C.byref(hb), n * n_loc * 4), "MallocHost")
+            g.capi.check(L.guda_malloc_host(C.byref(hc), m_loc * n_loc * 4), "MallocHost")
+            L.guda_memcpy(ha, a_panel.ptr, m_loc * n * 4, 2, None); L.guda_memcpy(hb, b_panel.ptr, n * n_loc * 4, 2, None)
+
+            def e2e_step():
+                L.guda_memcpy_async(a_panel.ptr, ha, m_loc * n * 4, 1, None)
+                L.guda_memcpy_async(b_panel.ptr, hb, n * n_loc * 4, 1, None)
+                step()
+                L.guda_memcpy_async(hc, c_block.ptr, m_loc * n_loc * 4, 2, None)
+            e2e_step()
+            barrier()
+            e_ms = max_over_ranks(dev.time_ms(e2e_step, max(1, min(args.steps, 2))))
+            barrier()
+            e2e = {"value": flops / (e_ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": e_ms,
+                   "h2d_bytes_per_step": (m_loc * n + n * n_loc) * 4 * world, "d2h_bytes_per_step": m_loc * n_loc * 4 * world,
+                   "host_memory": "pinned"}
+            for hp in (ha, hb, hc):
+                L.guda_free_host(hp)
+        else:
+            e2e = {"value": None, "unit": "TFLOP/s", "skipped": "host RAM too small for %d bytes of pinned staging" % need}
+
+    for p in (a_panel, b_panel, c_block, c_full):
+        if p is not None:
+            g.Free(p)
+    L.guda_pool_trim()
+
+    suite_res, cpu = None, None
+    if rank == 0 and world == 1 and not args.no_suite:
+        suite_res = suite(dev, peaks, ffma_peak, dfma_peak)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = host_cores()
+        tf, dt = cpu_sgemm_sample(2, 1, cores)
+        cpu = {"value": tf, "unit": "TFLOP/s", "cores": cores, "kind": "port",
+               "sample": "SGEMM %d^3 fp32 (bounded sample of the %d^3 headline), oracle port of compute/sgemm.go (AVX2+FMA route, "
+                         "one task per 64x64 C block), %.2f s per pass" % (CPU_SAMPLE_N, n, dt)}
+    if comm is not None:
+        barrier()
+        L.guda_comm_destroy(comm)
+    if rank == 0:
+        launches = args.steps * (1 if world == 1 else (1 if pc == 1 else 2))
+        line = {"metric": "sgemm_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "SGEMM %d^3 fp32 NN alpha=1 beta=0 (BASELINE configs[4]); %dx%d block partition%s" % (
+                               n, pr, pc, ", C all-gathered over NCCL/NVLink inside the step" if world > 1 else ""),
+                           "math": "exact fp32 SIMT, reference k-order (bit-exact vs oracle)" if args.mode == "exact" else "3xTF32 tcgen05",
+                           "l2": "operands %.1f GiB per rank, far larger than the 126 MB L2" % ((m_loc * n + n * n_loc) * 4 / 2 ** 30)},
+                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "measured_here": {"ffma_tflops": ffma_peak, "dfma_tflops": dfma_peak, "copy_gbs": copy_peak},
+                "suite": suite_res}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

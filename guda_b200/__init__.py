@@ -8,6 +8,7 @@ There is no CPU fallback: importing works anywhere, computing needs a B200.
 """
 from .api import *          # noqa: F401,F403
 from .api import DevicePtr, Stream, Event, ErrNotSupported   # noqa: F401
+from . import capi  # noqa: F401
 from .capi import BlasPanic, GUDAError, LIB_PATH, load       # noqa: F401
 
 __version__ = "0.1.0"

@@ -87,6 +87,7 @@ SIGNATURES = {
     "guda_comm_destroy": (i, [vp]),
     "guda_sgemm_sharded": (i, [vp, i, i, i, i, i, f, vp, i, vp, i, vp, i, vp, i, vp]),
     "guda_sdot_sharded": (i, [vp, i, vp, vp, fp, vp]),
+    "guda_microbench_peak": (i, [i, i, dp]),
 }
 
 _lib = None

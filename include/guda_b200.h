@@ -156,6 +156,10 @@ int guda_fill_uniform_f32(float* dst, size_t rows, size_t cols, size_t ld, uint6
 int guda_fill_uniform_f64(double* dst, size_t rows, size_t cols, size_t ld, uint64_t seed, uint64_t row0, uint64_t col0,
                           uint64_t full_cols, double lo, double hi, guda_stream_t stream);
 
+/* ---- measured denominators for rooflines (bench.py): kind 0 = FP32 FFMA TFLOP/s, 1 = FP64 DFMA TFLOP/s,
+ * 2 = 128-bit streaming copy GB/s (read+write bytes) ---- */
+int guda_microbench_peak(int kind, int reps, double* value);
+
 /* ---- multi-GPU (new, additive: GetDeviceCount()==1 stays pinned for the single-device API, guda_test.go:332) ----
  * One process per GPU.  The communicator wraps NCCL (loaded at run time); id bytes come from
  * guda_comm_unique_id on rank 0 and travel out of band (the Go shim or torch.distributed). */

@@ -48,9 +48,11 @@ def test_sgemm_bit_exact_nn_tn_tt(g, O, m, n, k, ta, tb):
     assert np.array_equal(got, want)
 
 
-@pytest.mark.parametrize("m,n,k", [(8, 8, 8), (63, 65, 64), (128, 128, 128), (257, 129, 77), (512, 512, 300)])
+@pytest.mark.parametrize("m,n,k", [(9, 7, 8), (63, 65, 64), (128, 128, 128), (257, 129, 77), (512, 512, 300)])
 def test_sgemm_nt_within_tolerance(g, O, m, n, k):
-    """NotTrans x Trans is the DotUnitary form (32-lane blocked order): compared under the K-scaled GEMM tolerance."""
+    """NotTrans x Trans is the DotUnitary form (32-lane blocked order): compared under the K-scaled GEMM tolerance.
+    (Contiguous 4^3/8^3/16^3 with bTrans is excluded on purpose: compute/sgemm.go:98-111 multiplies by B as stored --
+    a reference defect SURVEY.md a7 says not to replicate; test_sgemm_small_btrans_is_true_transpose pins our answer.)"""
     a = O.uniform_f32(m * k, 1); b = O.uniform_f32(n * k, 2); c0 = O.uniform_f32(m * n, 3, 0.0, 1.0)
     got = _run_sgemm(g, 0, 1, m, n, k, 1.5, a, k, b, k, 0.5, c0, n)
     want = O.sgemm(0, 1, m, n, k, 1.5, a, k, b, k, 0.5, c0.copy(), n, threads=8)
@@ -88,6 +90,14 @@ def test_sgemm_small_fast_paths_bit_exact(g, O, s):
         got = _run_sgemm(g, 0, 0, s, s, s, 1.5, a, s, b, s, beta, c0, s)
         want = O.sgemm(0, 0, s, s, s, 1.5, a, s, b, s, beta, c0.copy(), s)
         assert np.array_equal(got, want)
+
+
+def test_sgemm_small_btrans_is_true_transpose(g, O):
+    s = 8
+    a = O.uniform_f32(s * s, 21); b = O.uniform_f32(s * s, 22); c0 = np.zeros(s * s, np.float32)
+    got = _run_sgemm(g, 0, 1, s, s, s, 1.0, a, s, b, s, 0.0, c0, s)
+    want = a.reshape(s, s).astype(np.float64) @ b.reshape(s, s).astype(np.float64).T
+    assert np.max(np.abs(got.reshape(s, s) - want)) <= 1e-5
 
 
 def test_sgemm_panics(g):

@@ -189,6 +189,11 @@ def GetMemoryStats():                              # memory.go:230-234
     return a.value, p.value
 
 
+def PoolTrim():
+    """Return cached (freed) blocks to the driver; new, the reference never gives memory back (memory.go:222)."""
+    capi.check(_L().guda_pool_trim(), "PoolTrim")
+
+
 def _addr(obj, writable):
     if isinstance(obj, DevicePtr):
         return obj.ptr

@@ -25,7 +25,7 @@ def _run_sgemm(g, ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc):
     g.GEMM(bool(ta), bool(tb), m, n, k, alpha, da, lda, db, ldb, beta, dc, ldc)
     g.Synchronize()
     out = dc.Float32()
-    assert np.array_equal(da.Float32(), a) and np.array_equal(db.Float32(), b)     # inputs untouched
+    assert np.array_equal(da.Float32(), a, equal_nan=True) and np.array_equal(db.Float32(), b, equal_nan=True)     # inputs untouched
     g.Free(da); g.Free(db); g.Free(dc)
     return out
 

@@ -66,6 +66,7 @@ def test_device_queries(g):
 
 def test_pool_stats_bit_exact(g):
     # guda_test.go:339-375 + memory.go:150-227: 64-byte rounding, allocated falls on Free, peak never, first-fit reuse
+    g.PoolTrim()                                       # empty free list, as in a fresh reference process
     a0, p0 = g.GetMemoryStats()
     x = g.Malloc(1000)                                 # -> 1024
     a1, p1 = g.GetMemoryStats()

@@ -1,7 +1,370 @@
-// gemm_tc.cu -- tcgen05 / TMEM / TMA tensor-core GEMM paths (bf16, fp16, 3xTF32).
+// gemm_tc.cu -- Blackwell tensor-core GEMM: TMA-fed tcgen05.mma with fp32 accumulators in TMEM.
+//
+// One persistent, warp-specialised kernel (1 CTA per SM, 192 threads):
+//   warp 0      TMA producer: cp.async.bulk.tensor tiles of A (K-major, rows of 128 B) and B (row-major [K][N] as
+//               stored by GUDA = "MN-major": boxes of BK x 128 B) into a ring of SWIZZLE_128B shared-memory stages
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma (M=128, N=BN) per 32-byte K slice; tcgen05.commit
+//               releases smem stages and signals the epilogue; owns the TMEM allocation (2 accumulator stages)
+//   warps 2..5  epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> alpha/beta, bias + ReLU/GELU in registers
+//               -> ONE store of C (subsystem 4: no second pass over C)
+// Instantiations:
+//   16-bit (bf16 / fp16 storage, fp32 accumulate)    replaces bfloat16.go:104-167, float16.go:201-244
+//   3xTF32 SGEMM: A = Ah + Al, B = Bh + Bl (fp32 planes produced by a split pre-pass); per K slice
+//                 D += Al*Bh; D += Ah*Bl; D += Ah*Bh   (kind::tf32, fp32 TMEM accumulation)      GUDA_SGEMM_3XTF32
+// Shared-memory operand layout and the 64-bit descriptors follow the canonical UMMA layouts
+// (K-major: ((8,n),2):((8,SBO),1); MN-major: ((8,n),(8,k)):((1,LBO),(8,SBO)), units of 16 bytes).
 #include "common.cuh"
+#include "gemm_simt.cuh"   // epilogue maths (apply_epilogue / gelu_f32_exact)
+#include "tc_ptx.cuh"
+#include <cudaTypedefs.h>
+#include <cuda_fp16.h>
+#include <mutex>
+
 namespace guda {
-int sgemm_3xtf32_try(int, int, int, int, int, float, const float*, int, const float*, int, float, float*, int, cudaStream_t) { return -1; }
-int gemm16_tc_try(int, int, int, int, float, const uint16_t*, int, const uint16_t*, int, float, uint16_t*, int, const float*, int,
-                  cudaStream_t) { return -1; }
+
+using namespace tc;
+
+enum { OUT_BF16 = 0, OUT_F16 = 1, OUT_F32 = 2 };
+
+struct TcParams {
+  int m, n, k;
+  float alpha, beta;
+  void* c; long long ldc;
+  const float* bias;
+  int epi;
+  int tiles_m, tiles_n;
+};
+
+template <int EB, int NSPLIT, int BN>
+struct TcCfg {
+  static constexpr int BM = 128;
+  static constexpr int BK = 128 / EB;                 // one 128-byte swizzle row of K per stage row
+  static constexpr int UMMA_K = 32 / EB;              // 32 bytes of K per tcgen05.mma
+  static constexpr int A_TILE = BM * 128;             // bytes
+  static constexpr int B_BOX_N = 128 / EB;            // elements of N per TMA box (128 bytes)
+  static constexpr int B_BOX = BK * 128;              // bytes per box
+  static constexpr int B_TILE = (BN / B_BOX_N) * B_BOX;
+  static constexpr int STAGE = NSPLIT * (A_TILE + B_TILE);
+  static constexpr int STAGES = (200 * 1024) / STAGE;
+  static constexpr int ACC_STAGES = 2;
+  static constexpr int TMEM_COLS = ACC_STAGES * BN;   // 512 (BN=256) or 256 (BN=128): powers of two
+  static constexpr int SMEM = STAGES * STAGE + 1024 /*align*/ + 256 /*barriers*/;
+  static_assert(STAGES >= 2, "pipeline too shallow");
+};
+
+__device__ __forceinline__ uint16_t tc_to_bf16(float f) {     // bfloat16.go:12-23
+  uint32_t bits = __float_as_uint(f);
+  if ((bits & 0x7FFFu) == 0x7FFFu && ((bits >> 16) & 1u)) bits += 0x10000u;
+  return (uint16_t)(bits >> 16);
+}
+__device__ __forceinline__ float tc_from_bf16(uint16_t b) { return __uint_as_float((uint32_t)b << 16); }
+__device__ __forceinline__ uint16_t tc_to_f16(float f) {      // float16.go:53-87 (truncate, flush, saturate to Inf)
+  uint32_t bits = __float_as_uint(f);
+  uint32_t sign = (bits >> 16) & 0x8000u, exponent = (bits >> 23) & 0xFFu, mant = bits & 0x7FFFFFu;
+  if (exponent == 0xFFu) return (uint16_t)(mant == 0 ? (sign | 0x7C00u) : (sign | 0x7C00u | (mant >> 13)));
+  int e = (int)exponent - 127 + 15;
+  if (e <= 0) return (uint16_t)sign;
+  if (e >= 0x1F) return (uint16_t)(sign | 0x7C00u);
+  return (uint16_t)(sign | ((uint32_t)e << 10) | (mant >> 13));
+}
+__device__ __forceinline__ float tc_from_f16(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+
+template <int EB, int NSPLIT, int BN, int OUT>
+__global__ void __launch_bounds__(192, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
+               const __grid_constant__ CUtensorMap map_b0, const __grid_constant__ CUtensorMap map_b1, TcParams p) {
+  using Cfg = TcCfg<EB, NSPLIT, BN>;
+  constexpr int BM = Cfg::BM, BK = Cfg::BK, STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + Cfg::ACC_STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + Cfg::ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int kblocks = (p.k + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_a0); prefetch_tmap(&map_b0);
+    if (NSPLIT == 2) { prefetch_tmap(&map_a1); prefetch_tmap(&map_b1); }
+    for (int s = 0; s < STAGES; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < Cfg::ACC_STAGES; s++) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_ptr, Cfg::TMEM_COLS); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  // tile order: groups of 8 M-blocks sweep N, so concurrently resident CTAs share A rows and B columns in L2
+  auto tile_coord = [&](int t, int& tm, int& tn) {
+    const int group = 8;
+    int per_group = group * p.tiles_n;
+    int g = t / per_group, r = t % per_group;
+    int rows = min(group, p.tiles_m - g * group);
+    tm = g * group + r % rows;
+    tn = r / rows;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        int tm, tn; tile_coord(t, tm, tn);
+        for (int kb = 0; kb < kblocks; kb++) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* st = smem + stage * Cfg::STAGE;
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE);
+          tma_load_2d(st, &map_a0, &full_bar[stage], kb * BK, tm * BM);
+          if (NSPLIT == 2) tma_load_2d(st + Cfg::A_TILE, &map_a1, &full_bar[stage], kb * BK, tm * BM);
+          uint8_t* sb = st + NSPLIT * Cfg::A_TILE;
+#pragma unroll
+          for (int j = 0; j < BN / Cfg::B_BOX_N; j++) {
+            tma_load_2d(sb + j * Cfg::B_BOX, &map_b0, &full_bar[stage], tn * BN + j * Cfg::B_BOX_N, kb * BK);
+            if (NSPLIT == 2) tma_load_2d(sb + Cfg::B_TILE + j * Cfg::B_BOX, &map_b1, &full_bar[stage], tn * BN + j * Cfg::B_BOX_N, kb * BK);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(EB == 2 ? (OUT == OUT_F16 ? 0u : 1u) : 2u, /*a K-major*/ 0u, /*b MN-major*/ 1u, BM, BN);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, it++) {
+        const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < kblocks; kb++) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(smem + stage * Cfg::STAGE);
+          const uint32_t b0 = a0 + NSPLIT * Cfg::A_TILE;
+#pragma unroll
+          for (int ks = 0; ks < BK / Cfg::UMMA_K; ks++) {
+            // A: K-major, 128-byte rows, 8-row groups 1024 B apart; K slice = +32 B inside the swizzled row
+            // B: MN-major, boxes (LBO) of BK rows x 128 B, 8-row groups (SBO) 1024 B apart; K slice = UMMA_K rows
+            const uint64_t da = make_smem_desc(a0 + ks * 32, 16, 1024);
+            const uint64_t db = make_smem_desc(b0 + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, 1024);
+            const uint32_t first = (kb | ks) != 0;
+            if (NSPLIT == 1) {
+              if (EB == 2) mma_f16(d_tmem, da, db, idesc, first); else mma_tf32(d_tmem, da, db, idesc, first);
+            } else {
+              const uint64_t da_lo = make_smem_desc(a0 + Cfg::A_TILE + ks * 32, 16, 1024);
+              const uint64_t db_lo = make_smem_desc(b0 + Cfg::B_TILE + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, 1024);
+              mma_tf32(d_tmem, da_lo, db, idesc, first);      // small terms first
+              mma_tf32(d_tmem, da, db_lo, idesc, 1u);
+              mma_tf32(d_tmem, da, db, idesc, 1u);
+            }
+          }
+          mma_commit(&empty_bar[stage]);                      // smem stage reusable once these MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(&tmem_full[as]);                           // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5; TMEM lane quarter = warp % 4) =====================
+    const int q = warp & 3;
+    int it = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, it++) {
+      int tm, tn; tile_coord(t, tm, tn);
+      const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const int row = tm * BM + q * 32 + lane;
+      const bool row_ok = row < p.m;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+        tmem_ld_wait();
+        const int col0 = tn * BN + c0;
+        if (row_ok && col0 < p.n) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; j++) v[j] = __fmul_rn(p.alpha, __uint_as_float(r[j]));
+          const bool full = (col0 + 32 <= p.n);
+          if (OUT == OUT_F32) {
+            float* dst = reinterpret_cast<float*>(p.c) + (long long)row * p.ldc + col0;
+            if (p.beta != 0.0f) {
+#pragma unroll
+              for (int j = 0; j < 32; j++) if (full || col0 + j < p.n) v[j] = __fadd_rn(v[j], __fmul_rn(p.beta, dst[j]));
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j++) v[j] = p.epi == 0 ? v[j] : (p.epi == 1 ? apply_epilogue<float, EPI_BIAS_RELU>(v[j], (full || col0 + j < p.n) ? p.bias[col0 + j] : 0.f)
+                                                                              : apply_epilogue<float, EPI_BIAS_GELU>(v[j], (full || col0 + j < p.n) ? p.bias[col0 + j] : 0.f));
+            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; j++) if (col0 + j < p.n) dst[j] = v[j];
+            }
+          } else {
+            uint16_t* dst = reinterpret_cast<uint16_t*>(p.c) + (long long)row * p.ldc + col0;
+            if (p.beta != 0.0f) {
+#pragma unroll
+              for (int j = 0; j < 32; j++)
+                if (full || col0 + j < p.n) v[j] = __fadd_rn(v[j], __fmul_rn(p.beta, OUT == OUT_BF16 ? tc_from_bf16(dst[j]) : tc_from_f16(dst[j])));
+            }
+            if (p.epi != 0) {
+#pragma unroll
+              for (int j = 0; j < 32; j++) {
+                float b = (full || col0 + j < p.n) ? p.bias[col0 + j] : 0.f;
+                v[j] = p.epi == 1 ? apply_epilogue<float, EPI_BIAS_RELU>(v[j], b) : apply_epilogue<float, EPI_BIAS_GELU>(v[j], b);
+              }
+            }
+            uint32_t packed[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              uint32_t lo = OUT == OUT_BF16 ? tc_to_bf16(v[2 * j]) : tc_to_f16(v[2 * j]);
+              uint32_t hi = OUT == OUT_BF16 ? tc_to_bf16(v[2 * j + 1]) : tc_to_f16(v[2 * j + 1]);
+              packed[j] = lo | (hi << 16);
+            }
+            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 4) *reinterpret_cast<uint4*>(dst + 2 * j) = make_uint4(packed[j], packed[j + 1], packed[j + 2], packed[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; j++) if (col0 + j < p.n) dst[j] = (uint16_t)(packed[j >> 1] >> ((j & 1) * 16));
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, Cfg::TMEM_COLS); }
+}
+
+// ---------------------------------------------------------------- host side
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+
+static int get_encode() {
+  static std::once_flag once;
+  static int status = GUDA_OK;
+  std::call_once(once, [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) status = GUDA_ERR_DEVICE;
+    else g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+  });
+  if (status) return set_error(GUDA_ERR_DEVICE, "cuTensorMapEncodeTiled is not available from this driver");
+  return GUDA_OK;
+}
+
+// 2-D row-major tensor [rows][cols] (cols contiguous, leading dimension ld elements), box = box_cols x box_rows, SWIZZLE_128B
+static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int eb, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                    uint32_t box_cols, uint32_t box_rows) {
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * (uint64_t)eb};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(GUDA_ERR_INVALID_ARG, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return GUDA_OK;
+}
+
+template <int EB, int NSPLIT, int BN, int OUT>
+static int launch_tc(CUtensorMapDataType dt, int m, int n, int k, float alpha, const void* a0, const void* a1, long long lda,
+                     const void* b0, const void* b1, long long ldb, float beta, void* c, long long ldc, const float* bias, int epi,
+                     cudaStream_t s) {
+  using Cfg = TcCfg<EB, NSPLIT, BN>;
+  int rc = get_encode();
+  if (rc) return rc;
+  CUtensorMap ma0, ma1, mb0, mb1;
+  if ((rc = make_map(&ma0, dt, EB, a0, m, k, lda, Cfg::BK, Cfg::BM))) return rc;
+  if ((rc = make_map(&mb0, dt, EB, b0, k, n, ldb, Cfg::B_BOX_N, Cfg::BK))) return rc;
+  ma1 = ma0; mb1 = mb0;
+  if (NSPLIT == 2) {
+    if ((rc = make_map(&ma1, dt, EB, a1, m, k, lda, Cfg::BK, Cfg::BM))) return rc;
+    if ((rc = make_map(&mb1, dt, EB, b1, k, n, ldb, Cfg::B_BOX_N, Cfg::BK))) return rc;
+  }
+  TcParams p{m, n, k, alpha, beta, c, ldc, bias, epi, (m + Cfg::BM - 1) / Cfg::BM, (n + BN - 1) / BN};
+  auto kern = gemm_tc_kernel<EB, NSPLIT, BN, OUT>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GUDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    attr_set = true;
+  }
+  int grid = p.tiles_m * p.tiles_n;
+  if (grid > sm_count()) grid = sm_count();
+  kern<<<grid, 192, Cfg::SMEM, s>>>(ma0, ma1, mb0, mb1, p);
+  return check_launch("gemm_tc");
+}
+
+static bool tma_ok(const void* p, long long ld, int eb) { return ((uintptr_t)p % 16 == 0) && ((ld * eb) % 16 == 0); }
+
+// 16-bit GEMM on tensor cores; -1 = not eligible (caller falls back to the exact route)
+int gemm16_tc_try(int is_bf16, int m, int n, int k, float alpha, const uint16_t* a, int lda, const uint16_t* b, int ldb, float beta,
+                  uint16_t* c, int ldc, const float* bias, int epi, cudaStream_t s) {
+  if (m < 128 || n < 128 || k < 64) return -1;                // tiny problems: the exact SIMT route is faster and bit-exact
+  if (!tma_ok(a, lda, 2) || !tma_ok(b, ldb, 2)) return -1;
+  if (is_bf16)
+    return launch_tc<2, 1, 256, OUT_BF16>(CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, epi, s);
+  return launch_tc<2, 1, 256, OUT_F16>(CU_TENSOR_MAP_DATA_TYPE_FLOAT16, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, epi, s);
+}
+
+// fp32 -> (hi, lo) planes for the 3xTF32 split: hi = x rounded to tf32 (10-bit mantissa, round-to-nearest-even on the
+// 13 dropped bits), lo = x - hi (exact in fp32; the tensor core reads its top 10 mantissa bits)
+__global__ void split_tf32_kernel(const float* __restrict__ src, long long lds, float* __restrict__ hi, float* __restrict__ lo,
+                                  long long ldd, long long rows, long long cols) {
+  const long long total = rows * cols;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long r = i / cols, c = i % cols;
+    float x = src[r * lds + c];
+    uint32_t u = __float_as_uint(x);
+    float h = x;
+    if ((u & 0x7F800000u) != 0x7F800000u) {            // finite: RNE to 10 mantissa bits
+      uint32_t rb = u + 0x0FFFu + ((u >> 13) & 1u);
+      h = __uint_as_float(rb & 0xFFFFE000u);
+    }
+    hi[r * ldd + c] = h;
+    lo[r * ldd + c] = __fsub_rn(x, h);
+  }
+}
+
+struct TcTemp {
+  void* p = nullptr;
+  ~TcTemp() { if (p) guda_free(p); }
+};
+
+int sgemm_3xtf32_try(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
+                     float* c, int ldc, cudaStream_t s) {
+  if (ta || tb) return -1;
+  if (m < 128 || n < 128 || k < 32) return -1;
+  auto pad4 = [](long long x) { return (x + 3) & ~3ll; };
+  const long long lda2 = pad4(k), ldb2 = pad4(n);
+  TcTemp ah, al, bh, bl;
+  int rc;
+  if ((rc = guda_malloc(&ah.p, (size_t)m * lda2 * 4))) return rc;
+  if ((rc = guda_malloc(&al.p, (size_t)m * lda2 * 4))) return rc;
+  if ((rc = guda_malloc(&bh.p, (size_t)k * ldb2 * 4))) return rc;
+  if ((rc = guda_malloc(&bl.p, (size_t)k * ldb2 * 4))) return rc;
+  const int blocks = sm_count() * 16;
+  split_tf32_kernel<<<blocks, 256, 0, s>>>(a, lda, (float*)ah.p, (float*)al.p, lda2, m, k);
+  split_tf32_kernel<<<blocks, 256, 0, s>>>(b, ldb, (float*)bh.p, (float*)bl.p, ldb2, k, n);
+  if ((rc = check_launch("split_tf32"))) return rc;
+  rc = launch_tc<4, 2, 128, OUT_F32>(CU_TENSOR_MAP_DATA_TYPE_FLOAT32, m, n, k, alpha, ah.p, al.p, lda2, bh.p, bl.p, ldb2, beta, c, ldc,
+                                     nullptr, 0, s);
+  if (rc) return rc;
+  GUDA_CUDA(cudaStreamSynchronize(s));      // the planes return to the pool when this function exits
+  return GUDA_OK;
+}
+
 }  // namespace guda

@@ -175,7 +175,7 @@ __device__ __forceinline__ T warp_sum(T v) {
 // walk of 128-bit vectors; warp shuffle tree -> smem -> one partial per CTA; the last CTA to finish
 // (atomic ticket) sums the partials in index order, so the result is deterministic for a given n.
 template <typename T>
-__global__ void __launch_bounds__(L1_THREADS) dot_kernel(size_t n, const T* __restrict__ x, long long incx, const T* __restrict__ y,
+__global__ void __launch_bounds__(L1_THREADS, 4) dot_kernel(size_t n, const T* __restrict__ x, long long incx, const T* __restrict__ y,
                                                          long long incy, size_t head, T* __restrict__ partials,
                                                          unsigned int* __restrict__ counter, T* __restrict__ out0, T* __restrict__ out1) {
   using V = typename Vec<T>::type;
@@ -391,7 +391,14 @@ static int dot_impl(int n, const T* x, int incx, const T* y, int incy, T* host_r
   size_t work = unit ? (N / Vec<T>::N + (size_t)L1_THREADS * L1_UNROLL - 1) / ((size_t)L1_THREADS * L1_UNROLL)
                      : (N + L1_THREADS - 1) / L1_THREADS;
   unsigned grid = (unsigned)work;
-  unsigned wave = (unsigned)sm_count() * 4;
+  static int occ = 0;       // resident CTAs per SM for this kernel: the grid must be exactly one full wave
+  if (occ == 0) {
+    int o = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dot_kernel<float>, L1_THREADS, 0) != cudaSuccess || o < 1) o = 2;
+    if (o > 4) o = 4;
+    occ = o;
+  }
+  unsigned wave = (unsigned)sm_count() * (unsigned)occ;
   if (grid > wave) grid = wave;
   if (grid == 0) grid = 1;
   // 8 scratch slots of 8 KiB (>= 592 partials of 8 bytes) + one ticket counter each

@@ -248,6 +248,53 @@ def suite(dev, peaks, ffma_peak, dfma_peak):
     for p in (a, b, c, bias):
         g.Free(p)
 
+    # ---- C3 bf16: same FFN shape, bf16 storage / fp32 TMEM accumulation, tcgen05 + fused bias+GELU epilogue
+    a, b, c, bias = g.Malloc(M * K * 2), g.Malloc(K * N * 2), g.Malloc(M * N * 2), g.Malloc(N * 4)
+    tmp = g.Malloc(K * N * 4)
+    g.FillUniform(tmp, M, K, K, 510); dev.L.guda_f32_to_bf16(tmp.ptr, a.ptr, M * K, None)
+    g.FillUniform(tmp, K, N, N, 511, lo=-3 * s, hi=3 * s); dev.L.guda_f32_to_bf16(tmp.ptr, b.ptr, K * N, None)
+    g.FillUniform(bias, 1, N, N, 512)
+    g.Synchronize(); g.Free(tmp)
+
+    def fused16():
+        dev.L.guda_gemm_bf16_bias_gelu(M, N, K, 1.0, a.ptr, K, b.ptr, N, c.ptr, N, bias.ptr, None)
+
+    def plain16():
+        dev.L.guda_gemm_bf16(0, 0, M, N, K, 1.0, a.ptr, K, b.ptr, N, 0.0, c.ptr, N, None)
+
+    fused16(); plain16()
+    ms = dev.time_ms(fused16, 10)
+    ms_plain = dev.time_ms(plain16, 10)
+    tf = 2.0 * M * N * K / (ms * 1e-3) / 1e12
+    out["fused_gemm_bias_gelu_bf16_8192x4096x16384"] = {
+        "value": tf, "unit": "TFLOP/s", "ms": ms, "ms_plain_gemm_same_shape": ms_plain, "tflops_plain": 2.0 * M * N * K / (ms_plain * 1e-3) / 1e12,
+        "roofline": {"bound": "tensor", "achieved": tf, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": tf / peaks["bf16_tflops"],
+                     "peak_source": "MEASURED_PEAKS.json bf16 burst (%s)" % peaks["source"]}}
+    for p in (a, b, c, bias):
+        g.Free(p)
+
+    # ---- SGEMM 8192^3 on the 3xTF32 tensor-core route (opt-in math mode; stated tolerance, see tests/test_gpu_tensor.py)
+    n = 8192
+    a, b, c = g.Malloc(n * n * 4), g.Malloc(n * n * 4), g.Malloc(n * n * 4)
+    g.FillUniform(a, n, n, n, 520); g.FillUniform(b, n, n, n, 521)
+    g.SetSgemmMode(1)
+
+    def sg3():
+        dev.L.guda_sgemm(0, 0, n, n, n, 1.0, a.ptr, n, b.ptr, n, 0.0, c.ptr, n, None)
+
+    try:
+        sg3()
+        ms = dev.time_ms(sg3, 3)
+    finally:
+        g.SetSgemmMode(0)
+    tf = 2.0 * n ** 3 / (ms * 1e-3) / 1e12
+    tpeak = peaks["bf16_tflops"] / 2.0 / 3.0
+    out["sgemm_3xtf32_8192"] = {"value": tf, "unit": "TFLOP/s", "ms": ms, "includes": "hi/lo split pre-pass + pool traffic",
+                                "roofline": {"bound": "tensor", "achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak,
+                                             "peak_source": "MEASURED_PEAKS.json bf16 burst / 2 (tf32 rate) / 3 (three MMAs per product)"}}
+    for p in (a, b, c):
+        g.Free(p)
+
     # ---- C4: DGEMM 16384^3, alpha=1 beta=0
     n = 16384
     a, b, c = g.Malloc(n * n * 8), g.Malloc(n * n * 8), g.Malloc(n * n * 8)

@@ -153,13 +153,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
             // A: K-major, 128-byte rows, 8-row groups 1024 B apart; K slice = +32 B inside the swizzled row
             // B: MN-major, boxes (LBO) of BK rows x 128 B, 8-row groups (SBO) 1024 B apart; K slice = UMMA_K rows
             const uint64_t da = make_smem_desc(a0 + ks * 32, 16, 1024);
-            const uint64_t db = make_smem_desc(b0 + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, 1024);
+            // (fp32/tf32 MN-major operands only exist as SWIZZLE_128B_BASE32B: 32-byte swizzle atoms, 4-row groups 512 B apart)
+            constexpr uint32_t B_LAYOUT = EB == 4 ? 1u : 2u, B_SBO = EB == 4 ? 512u : 1024u;
+            const uint64_t db = make_smem_desc(b0 + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, B_SBO, B_LAYOUT);
             const uint32_t first = (kb | ks) != 0;
             if (NSPLIT == 1) {
               if (EB == 2) mma_f16(d_tmem, da, db, idesc, first); else mma_tf32(d_tmem, da, db, idesc, first);
             } else {
               const uint64_t da_lo = make_smem_desc(a0 + Cfg::A_TILE + ks * 32, 16, 1024);
-              const uint64_t db_lo = make_smem_desc(b0 + Cfg::B_TILE + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, 1024);
+              const uint64_t db_lo = make_smem_desc(b0 + Cfg::B_TILE + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, B_SBO, B_LAYOUT);
               mma_tf32(d_tmem, da_lo, db, idesc, first);      // small terms first
               mma_tf32(d_tmem, da, db_lo, idesc, 1u);
               mma_tf32(d_tmem, da, db, idesc, 1u);
@@ -269,13 +271,13 @@ static int get_encode() {
 
 // 2-D row-major tensor [rows][cols] (cols contiguous, leading dimension ld elements), box = box_cols x box_rows, SWIZZLE_128B
 static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int eb, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                    uint32_t box_cols, uint32_t box_rows) {
+                    uint32_t box_cols, uint32_t box_rows, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {ld * (uint64_t)eb};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(GUDA_ERR_INVALID_ARG, "cuTensorMapEncodeTiled failed (%d)", (int)r);
   return GUDA_OK;
 }
@@ -289,11 +291,12 @@ static int launch_tc(CUtensorMapDataType dt, int m, int n, int k, float alpha, c
   if (rc) return rc;
   CUtensorMap ma0, ma1, mb0, mb1;
   if ((rc = make_map(&ma0, dt, EB, a0, m, k, lda, Cfg::BK, Cfg::BM))) return rc;
-  if ((rc = make_map(&mb0, dt, EB, b0, k, n, ldb, Cfg::B_BOX_N, Cfg::BK))) return rc;
+  const CUtensorMapSwizzle bswz = EB == 4 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  if ((rc = make_map(&mb0, dt, EB, b0, k, n, ldb, Cfg::B_BOX_N, Cfg::BK, bswz))) return rc;
   ma1 = ma0; mb1 = mb0;
   if (NSPLIT == 2) {
     if ((rc = make_map(&ma1, dt, EB, a1, m, k, lda, Cfg::BK, Cfg::BM))) return rc;
-    if ((rc = make_map(&mb1, dt, EB, b1, k, n, ldb, Cfg::B_BOX_N, Cfg::BK))) return rc;
+    if ((rc = make_map(&mb1, dt, EB, b1, k, n, ldb, Cfg::B_BOX_N, Cfg::BK, bswz))) return rc;
   }
   TcParams p{m, n, k, alpha, beta, c, ldc, bias, epi, (m + Cfg::BM - 1) / Cfg::BM, (n + BN - 1) / BN};
   auto kern = gemm_tc_kernel<EB, NSPLIT, BN, OUT>;

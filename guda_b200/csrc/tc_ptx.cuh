@@ -120,13 +120,14 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 // ---------------------------------------------------------------- UMMA descriptors (cute/arch/mma_sm100_desc.hpp bit layout)
 // shared-memory matrix descriptor, SWIZZLE_128B, version 1 (Blackwell)
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout_type: 2 = SWIZZLE_128B (16-byte atoms), 1 = SWIZZLE_128B_BASE32B (32-byte atoms; the only MN-major layout for 32-bit operands)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);            // [0,14)  start address >> 4
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;      // [16,30) leading-dimension byte offset >> 4
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;      // [32,46) stride-dimension byte offset >> 4
   d |= (uint64_t)1 << 46;                                // [46,48) descriptor version = 1
-  d |= (uint64_t)2 << 61;                                // [61,64) layout type: SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;                      // [61,64) layout type
   return d;
 }
 // instruction descriptor: fp32 accumulate, dense, no negate; formats: 0 = f16, 1 = bf16, 2 = tf32; majors: 0 = K, 1 = MN

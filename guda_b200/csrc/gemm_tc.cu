@@ -69,6 +69,16 @@ __device__ __forceinline__ uint16_t tc_to_f16(float f) {      // float16.go:53-8
 }
 __device__ __forceinline__ float tc_from_f16(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 
+// GELU_tanh for the 16-bit tensor route: tanh(u) = 1 - 2/(exp(2u)+1) with ex2.approx / rcp.approx (abs error ~1e-6,
+// two orders below the bf16/fp16 output spacing); the fp32 routes keep the reference's exact geluFloat32.
+__device__ __forceinline__ float gelu_fast(float x) {
+  float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  float e = __expf(2.0f * u);
+  float t = 1.0f - __fdividef(2.0f, e + 1.0f);
+  t = u > 10.0f ? 1.0f : t;
+  return 0.5f * x * (1.0f + t);
+}
+
 template <int EB, int NSPLIT, int BN, int OUT>
 __global__ void __launch_bounds__(192, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
@@ -86,6 +96,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int kblocks = (p.k + BK - 1) / BK;
+  // The tensor core adds into TMEM with truncation, so a long-K fp32 sum drifts (measured: ~K/8 ulps for 3xTF32).
+  // The 3xTF32 route therefore accumulates at most CHUNK_K = 256 of K in TMEM and promotes each chunk into fp32
+  // registers (round-to-nearest adds) in the epilogue warps, as block-scaled FP8 GEMMs do; 16-bit outputs do not need it.
+  const int chunk_blocks = (NSPLIT == 2) ? 8 : (kblocks > 0 ? kblocks : 1);
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_a0); prefetch_tmap(&map_b0);
@@ -137,58 +151,91 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(EB == 2 ? (OUT == OUT_F16 ? 0u : 1u) : 2u, /*a K-major*/ 0u, /*b MN-major*/ 1u, BM, BN);
       int stage = 0; uint32_t phase = 0;
-      int it = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, it++) {
-        const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(&tmem_empty[as], aphase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < kblocks; kb++) {
-          mbar_wait(&full_bar[stage], phase);
+      int ci = 0;                                             // running accumulation-chunk index (2 TMEM stages)
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        for (int kb0 = 0; kb0 < kblocks; kb0 += chunk_blocks, ci++) {
+          const int as = ci & 1; const uint32_t aphase = (ci >> 1) & 1;
+          mbar_wait(&tmem_empty[as], aphase ^ 1);
           tc_fence_after();
-          const uint32_t a0 = smem_u32(smem + stage * Cfg::STAGE);
-          const uint32_t b0 = a0 + NSPLIT * Cfg::A_TILE;
+          const uint32_t d_tmem = tmem_base + as * BN;
+          const int kb1 = min(kb0 + chunk_blocks, kblocks);
+          for (int kb = kb0; kb < kb1; kb++) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t a0 = smem_u32(smem + stage * Cfg::STAGE);
+            const uint32_t b0 = a0 + NSPLIT * Cfg::A_TILE;
 #pragma unroll
-          for (int ks = 0; ks < BK / Cfg::UMMA_K; ks++) {
-            // A: K-major, 128-byte rows, 8-row groups 1024 B apart; K slice = +32 B inside the swizzled row
-            // B: MN-major, boxes (LBO) of BK rows x 128 B, 8-row groups (SBO) 1024 B apart; K slice = UMMA_K rows
-            const uint64_t da = make_smem_desc(a0 + ks * 32, 16, 1024);
-            // (fp32/tf32 MN-major operands only exist as SWIZZLE_128B_BASE32B: 32-byte swizzle atoms, 4-row groups 512 B apart)
-            constexpr uint32_t B_LAYOUT = EB == 4 ? 1u : 2u, B_SBO = EB == 4 ? 512u : 1024u;
-            const uint64_t db = make_smem_desc(b0 + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, B_SBO, B_LAYOUT);
-            const uint32_t first = (kb | ks) != 0;
-            if (NSPLIT == 1) {
-              if (EB == 2) mma_f16(d_tmem, da, db, idesc, first); else mma_tf32(d_tmem, da, db, idesc, first);
-            } else {
-              const uint64_t da_lo = make_smem_desc(a0 + Cfg::A_TILE + ks * 32, 16, 1024);
-              const uint64_t db_lo = make_smem_desc(b0 + Cfg::B_TILE + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, B_SBO, B_LAYOUT);
-              mma_tf32(d_tmem, da_lo, db, idesc, first);      // small terms first
-              mma_tf32(d_tmem, da, db_lo, idesc, 1u);
-              mma_tf32(d_tmem, da, db, idesc, 1u);
+            for (int ks = 0; ks < BK / Cfg::UMMA_K; ks++) {
+              // A: K-major, 128-byte rows, 8-row groups 1024 B apart; K slice = +32 B inside the swizzled row
+              // B: MN-major, boxes (LBO) of BK rows x 128 B, row groups (SBO) apart; K slice = UMMA_K rows
+              // (fp32/tf32 MN-major operands only exist as SWIZZLE_128B_BASE32B: 32-byte swizzle atoms, 4-row groups 512 B apart)
+              constexpr uint32_t B_LAYOUT = EB == 4 ? 1u : 2u, B_SBO = EB == 4 ? 512u : 1024u;
+              const uint64_t da = make_smem_desc(a0 + ks * 32, 16, 1024);
+              const uint64_t db = make_smem_desc(b0 + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, B_SBO, B_LAYOUT);
+              const uint32_t first = ((kb - kb0) | ks) != 0;
+              if (NSPLIT == 1) {
+                if (EB == 2) mma_f16(d_tmem, da, db, idesc, first); else mma_tf32(d_tmem, da, db, idesc, first);
+              } else {
+                const uint64_t da_lo = make_smem_desc(a0 + Cfg::A_TILE + ks * 32, 16, 1024);
+                const uint64_t db_lo = make_smem_desc(b0 + Cfg::B_TILE + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, B_SBO, B_LAYOUT);
+                mma_tf32(d_tmem, da_lo, db, idesc, first);      // small terms first
+                mma_tf32(d_tmem, da, db_lo, idesc, 1u);
+                mma_tf32(d_tmem, da, db, idesc, 1u);
+              }
             }
+            mma_commit(&empty_bar[stage]);                      // smem stage reusable once these MMAs retire
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          mma_commit(&empty_bar[stage]);                      // smem stage reusable once these MMAs retire
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          mma_commit(&tmem_full[as]);                           // chunk accumulator complete -> epilogue
         }
-        mma_commit(&tmem_full[as]);                           // accumulator complete -> epilogue
       }
     }
   } else {
     // ===================== epilogue (warps 2..5; TMEM lane quarter = warp % 4) =====================
     const int q = warp & 3;
-    int it = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, it++) {
+    int ci = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       int tm, tn; tile_coord(t, tm, tn);
-      const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-      mbar_wait(&tmem_full[as], aphase);
-      tc_fence_after();
       const int row = tm * BM + q * 32 + lane;
       const bool row_ok = row < p.m;
-#pragma unroll 1
+      float accum[NSPLIT == 2 ? BN : 1];
+      int as = 0;
+      if (NSPLIT == 2) {
+        // promote every K chunk from TMEM into registers with round-to-nearest adds
+#pragma unroll
+        for (int j = 0; j < (NSPLIT == 2 ? BN : 1); j++) accum[j] = 0.0f;
+        for (int kb0 = 0; kb0 < kblocks; kb0 += chunk_blocks, ci++) {
+          as = ci & 1;
+          mbar_wait(&tmem_full[as], (ci >> 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int c0 = 0; c0 < (NSPLIT == 2 ? BN : 0); c0 += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; j++) accum[c0 + j] = __fadd_rn(accum[c0 + j], __uint_as_float(r[j]));
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[as]);
+        }
+      } else {
+        as = ci & 1;
+        mbar_wait(&tmem_full[as], (ci >> 1) & 1);
+        tc_fence_after();
+        ci++;
+      }
+#pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t r[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
-        tmem_ld_wait();
+        if (NSPLIT == 2) {
+#pragma unroll
+          for (int j = 0; j < 32; j++) r[j] = __float_as_uint(accum[(NSPLIT == 2 ? c0 : 0) + (NSPLIT == 2 ? j : 0)]);
+        } else {
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+          tmem_ld_wait();
+        }
         const int col0 = tn * BN + c0;
         if (row_ok && col0 < p.n) {
           float v[32];
@@ -222,7 +269,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
 #pragma unroll
               for (int j = 0; j < 32; j++) {
                 float b = (full || col0 + j < p.n) ? p.bias[col0 + j] : 0.f;
-                v[j] = p.epi == 1 ? apply_epilogue<float, EPI_BIAS_RELU>(v[j], b) : apply_epilogue<float, EPI_BIAS_GELU>(v[j], b);
+                v[j] = p.epi == 1 ? apply_epilogue<float, EPI_BIAS_RELU>(v[j], b) : gelu_fast(__fadd_rn(v[j], b));
               }
             }
             uint32_t packed[16];
@@ -242,9 +289,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      if (NSPLIT == 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      }
     }
   }
   tc_fence_before();

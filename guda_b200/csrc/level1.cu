@@ -240,14 +240,15 @@ __global__ void __launch_bounds__(L1_THREADS, 4) dot_kernel(size_t n, const T* _
     v = warp_sum(v);
     if (threadIdx.x == 0) {
       partials[blockIdx.x] = v;
-      __threadfence();
-      unsigned int ticket = atomicAdd(counter, 1u);
+      // one acq_rel ticket instead of membar + atomic: the release half publishes this CTA's partial, the acquire half
+      // (in the CTA that draws the last ticket) makes every earlier partial visible -- one L2 round trip on the tail
+      unsigned int ticket;
+      asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(counter) : "memory");
       is_last = (ticket == gridDim.x - 1);
     }
   }
   __syncthreads();
   if (is_last) {
-    __threadfence();
     // deterministic final pass: thread t sums partials t, t+256, ... then the same block tree
     T v = T(0);
     for (unsigned int i = threadIdx.x; i < gridDim.x; i += L1_THREADS) v = add_t(v, __ldcg(partials + i));
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(L1_THREADS, 4) dot_kernel(size_t n, const T* _
         if (out0) *out0 = w;
         if (out1) *out1 = w;
         *counter = 0;       // re-arm for the next launch on this slot
-        __threadfence_system();
+        if (out0) __threadfence_system();     // out0 lives in mapped pinned host memory
       }
     }
   }

@@ -20,6 +20,24 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T seed
   if (s == T(12345.678)) out[0] = s;       // never true; keeps the chain alive
 }
 
+// FP64 tensor pipe: mma.sync.m8n8k4.f64 (DMMA), 8 independent accumulator chains per warp
+__global__ void __launch_bounds__(256) dmma_peak_kernel(double* out, int iters) {
+  double a = 1.0 + threadIdx.x * 1e-3, b = 0.999;
+  double c[8][2];
+#pragma unroll
+  for (int i = 0; i < 8; i++) { c[i][0] = i; c[i][1] = -i; }
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(c[i][0]), "+d"(c[i][1]) : "d"(a), "d"(b));
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) s += c[i][0] + c[i][1];
+  if (s == 12345.678) out[0] = s;
+}
+
 __global__ void __launch_bounds__(256) copy_peak_kernel(const float4* __restrict__ src, float4* __restrict__ dst, size_t nvec) {
   size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride * 4) {
@@ -69,9 +87,31 @@ int guda_microbench_peak(int kind, int reps, double* value) {
   if (reps < 1) reps = 3;
   if (kind == 0) return fma_peak<float>(value, reps);
   if (kind == 1) return fma_peak<double>(value, reps);
-  if (kind != 2) return set_error(GUDA_ERR_INVALID_ARG, "unknown microbenchmark %d", kind);
   int rc = bind_device();
   if (rc) return rc;
+  if (kind == 3) {            // FP64 tensor pipe (DMMA m8n8k4) TFLOP/s
+    double* out;
+    GUDA_CUDA(cudaMalloc((void**)&out, 256));
+    cudaEvent_t e0, e1;
+    GUDA_CUDA(cudaEventCreate(&e0)); GUDA_CUDA(cudaEventCreate(&e1));
+    const int iters = 2048, blocks = sm_count() * 8;
+    cudaStream_t s = native(nullptr);
+    double best = 0;
+    for (int r = 0; r < reps + 1; r++) {
+      GUDA_CUDA(cudaEventRecord(e0, s));
+      dmma_peak_kernel<<<blocks, 256, 0, s>>>(out, iters);
+      GUDA_CUDA(cudaEventRecord(e1, s));
+      GUDA_CUDA(cudaEventSynchronize(e1));
+      float ms = 0;
+      GUDA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      double t = 512.0 * 8.0 * iters * 8.0 * blocks / (ms * 1e-3) / 1e12;
+      if (r > 0 && t > best) best = t;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+    *value = best;
+    return GUDA_OK;
+  }
+  if (kind != 2) return set_error(GUDA_ERR_INVALID_ARG, "unknown microbenchmark %d", kind);
   const size_t bytes = (size_t)1 << 30;
   float4 *src, *dst;
   GUDA_CUDA(cudaMalloc((void**)&src, bytes));

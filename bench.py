@@ -161,7 +161,17 @@ class Dev:
         return v.value
 
 
-def suite(dev, peaks, ffma_peak, dfma_peak):
+def ncu_traffic(key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the named kernel, from the committed ncu capture
+    (profiles/traffic.json, written by profiles/summarize.py); None when no capture covers it."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(key)
+    except Exception:
+        return None
+
+
+def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     """BASELINE configs C1..C4 at one GPU; inputs resident in HBM; rotating buffer sets larger than L2."""
     g = dev.g
     out = {}
@@ -306,8 +316,19 @@ def suite(dev, peaks, ffma_peak, dfma_peak):
     dg()
     ms = dev.time_ms(dg, 2)
     tf = 2.0 * n ** 3 / (ms * 1e-3) / 1e12
-    out["dgemm_16384"] = {"value": tf, "unit": "TFLOP/s", "ms": ms, "roofline": {"bound": "fp64_simt", "achieved": tf, "peak": dfma_peak,
-                          "unit": "TFLOP/s", "frac": tf / dfma_peak, "peak_source": "DFMA microbenchmark, this run"}}
+    fp64_peak = max(dmma_peak, dfma_peak)
+    out["dgemm_16384"] = {"value": tf, "unit": "TFLOP/s", "ms": ms, "route": "FP64 tensor pipe (DMMA m8n8k4), bit-exact vs the oracle's FMA chain",
+                          "roofline": {"bound": "tensor", "pipe": "fp64 tensor (DMMA)", "achieved": tf, "peak": fp64_peak,
+                                       "unit": "TFLOP/s", "frac": tf / fp64_peak,
+                                       "peak_source": "max(DMMA, DFMA) microbenchmarks, this run: DMMA %.1f, DFMA %.1f TFLOP/s" % (dmma_peak, dfma_peak),
+                                       "traffic": ncu_traffic("dgemm_dmma_16384")}}
+    g.SetDgemmMode(1)
+    try:
+        dg()
+        ms_simt = dev.time_ms(dg, 1)
+    finally:
+        g.SetDgemmMode(0)
+    out["dgemm_16384"]["simt_route_tflops"] = 2.0 * n ** 3 / (ms_simt * 1e-3) / 1e12
     for p in (a, b, c):
         g.Free(p)
     dev.L.guda_pool_trim()
@@ -358,6 +379,7 @@ def main():
 
     ffma_peak = dev.peak(0)
     dfma_peak = dev.peak(1) if rank == 0 else 0.0
+    dmma_peak = dev.peak(3) if rank == 0 else 0.0
     copy_peak = dev.peak(2) if rank == 0 else 0.0
 
     n = args.size
@@ -411,9 +433,11 @@ def main():
     kern_ms = dev.time_ms(local_gemm, 1) if world > 1 else ms
     kern_tf = 2.0 * m_loc * n_loc * n / (kern_ms * 1e-3) / 1e12
     if args.mode == "exact":
-        roof = {"bound": "fp32_simt", "achieved": kern_tf, "peak": ffma_peak, "unit": "TFLOP/s", "frac": kern_tf / ffma_peak,
+        roof = {"bound": "fp32_simt", "pipe": "fp32 FFMA (exact-order SIMT; tensor cores cannot reproduce the reference's per-step fp32 rounding)",
+                "achieved": kern_tf, "peak": ffma_peak, "unit": "TFLOP/s", "frac": kern_tf / ffma_peak,
                 "peak_source": "FFMA microbenchmark measured in this run (MEASURED_PEAKS.json has no fp32 SIMT figure)",
-                "frac_of_measured_bf16_tensor_peak": kern_tf / peaks["bf16_tflops_sustained"], "traffic": None}
+                "frac_of_measured_bf16_tensor_peak": kern_tf / peaks["bf16_tflops_sustained"],
+                "traffic": ncu_traffic("sgemm_simt_%d_p%d" % (n, world))}
     else:
         tpeak = peaks["bf16_tflops_sustained"] / 2.0 / 3.0     # TF32 = half the bf16 rate, three MMAs per product
         roof = {"bound": "tensor", "achieved": kern_tf, "peak": tpeak, "unit": "TFLOP/s", "frac": kern_tf / tpeak,
@@ -456,7 +480,7 @@ def main():
 
     suite_res, cpu = None, None
     if rank == 0 and world == 1 and not args.no_suite:
-        suite_res = suite(dev, peaks, ffma_peak, dfma_peak)
+        suite_res = suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak)
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = host_cores()
         tf, dt = cpu_sgemm_sample(2, 1, cores)
@@ -475,7 +499,7 @@ def main():
                            "math": "exact fp32 SIMT, reference k-order (bit-exact vs oracle)" if args.mode == "exact" else "3xTF32 tcgen05",
                            "l2": "operands %.1f GiB per rank, far larger than the 126 MB L2" % ((m_loc * n + n * n_loc) * 4 / 2 ** 30)},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-                "measured_here": {"ffma_tflops": ffma_peak, "dfma_tflops": dfma_peak, "copy_gbs": copy_peak},
+                "measured_here": {"ffma_tflops": ffma_peak, "dfma_tflops": dfma_peak, "dmma_tflops": dmma_peak, "copy_gbs": copy_peak},
                 "suite": suite_res}
         print(json.dumps(line))
     if dist is not None:

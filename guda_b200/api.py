@@ -402,6 +402,11 @@ def SetSgemmMode(mode):
     capi.check(_L().guda_set_sgemm_mode(mode), "SetSgemmMode")
 
 
+def SetDgemmMode(mode):
+    """0 = FP64 tensor pipe (DMMA) where eligible (default), 1 = SIMT DFMA kernel for every form."""
+    capi.check(_L().guda_set_dgemm_mode(mode), "SetDgemmMode")
+
+
 def SetGemm16Mode(mode):
     capi.check(_L().guda_set_gemm16_mode(mode), "SetGemm16Mode")
 

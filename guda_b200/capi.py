@@ -66,6 +66,8 @@ SIGNATURES = {
     "guda_get_sgemm_mode": (i, [ip]),
     "guda_sgemm": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_dgemm": (i, [i, i, i, i, i, d, vp, i, vp, i, d, vp, i, vp]),
+    "guda_set_dgemm_mode": (i, [i]),
+    "guda_get_dgemm_mode": (i, [ip]),
     "guda_gemm_bf16": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_gemm_f16": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_set_gemm16_mode": (i, [i]),

@@ -6,6 +6,9 @@
 namespace guda {
 
 int sgemm_mode();
+// FP64 tensor pipe (dgemm_dmma.cu); GUDA_OK / error if it took the call, -1 if the operands are not eligible
+int dgemm_dmma_try(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
+                   double* c, int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s);
 // tensor-core paths (gemm_tc.cu); return GUDA_OK if they handled the call, -1 if the shape is not eligible
 int sgemm_3xtf32_try(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
                      float beta, float* c, int ldc, cudaStream_t s);
@@ -58,26 +61,37 @@ template <typename T> struct TileCfg;
 template <> struct TileCfg<float>  { static constexpr int BK = 16, MINB_BIG = 2, MINB_SMALL = 3; };
 template <> struct TileCfg<double> { static constexpr int BK = 8,  MINB_BIG = 1, MINB_SMALL = 2; };
 
-template <typename T, bool TA, bool TB, int MODE, int EPI>
-static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
+template <typename T, bool TA, bool TB, int MODE, int EPI, int BM, int BN, int MINB>
+static int launch_simt_tile(const GemmParams<T>& p, cudaStream_t s) {
   constexpr int BK = TileCfg<T>::BK;
   constexpr int VN = GemmVec<T>::N;
-  const long long big_tiles = (long long)((p.m + 127) / 128) * ((p.n + 127) / 128);
-  const bool big = big_tiles >= sm_count();
-  const int BMN = big ? 128 : 64;
   auto aligned = [&](const void* ptr, long long ld) { return ((uintptr_t)ptr % 16 == 0) && (ld % VN == 0); };
-  const bool fast = (p.m % BMN == 0) && (p.n % BMN == 0) && (p.k % BK == 0) && aligned(p.a, p.lda) && aligned(p.b, p.ldb) &&
+  const bool fast = (p.m % BM == 0) && (p.n % BN == 0) && (p.k % BK == 0) && aligned(p.a, p.lda) && aligned(p.b, p.ldb) &&
                     aligned(p.c, p.ldc) && p.edge_m >= p.m && p.edge_n >= p.n;
-  dim3 grid((p.n + BMN - 1) / BMN, (p.m + BMN - 1) / BMN);
+  dim3 grid((p.n + BN - 1) / BN, (p.m + BM - 1) / BM);
   if (grid.y > 65535) return set_error(GUDA_ERR_INVALID_ARG, "m too large for one launch");
-  if (big) {
-    if (fast) gemm_simt_kernel<T, TA, TB, 128, 128, BK, MODE, EPI, true, TileCfg<T>::MINB_BIG><<<grid, 256, 0, s>>>(p);
-    else      gemm_simt_kernel<T, TA, TB, 128, 128, BK, MODE, EPI, false, TileCfg<T>::MINB_BIG><<<grid, 256, 0, s>>>(p);
-  } else {
-    if (fast) gemm_simt_kernel<T, TA, TB, 64, 64, BK, MODE, EPI, true, TileCfg<T>::MINB_SMALL><<<grid, 256, 0, s>>>(p);
-    else      gemm_simt_kernel<T, TA, TB, 64, 64, BK, MODE, EPI, false, TileCfg<T>::MINB_SMALL><<<grid, 256, 0, s>>>(p);
-  }
+  if (fast) gemm_simt_kernel<T, TA, TB, BM, BN, BK, MODE, EPI, true, MINB><<<grid, 256, 0, s>>>(p);
+  else      gemm_simt_kernel<T, TA, TB, BM, BN, BK, MODE, EPI, false, MINB><<<grid, 256, 0, s>>>(p);
   return check_launch("gemm");
+}
+
+// Tile choice: every C element is one thread's sequential-k chain, so there is no split-K to fill the machine with;
+// the only freedom is the CTA tile.  Pick the shape with the smallest estimated makespan
+//   ceil(tiles / SMs) * BM*BN / efficiency      (efficiency = FFMA share of the inner loop, measured: 8x8 micro-tile 1.0,
+//   8x4 0.85, 4x4 0.6), which sends 1024^3 (64 big tiles on 148 SMs) to 128x64 and anything large to 128x128.
+template <typename T, bool TA, bool TB, int MODE, int EPI>
+static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
+  const long long sms = sm_count();
+  auto makespan = [&](int bm, int bn, double eff) {
+    const long long tiles = (long long)((p.m + bm - 1) / bm) * ((p.n + bn - 1) / bn);
+    return (double)((tiles + sms - 1) / sms) * bm * bn / eff;
+  };
+  const double t_big = makespan(128, 128, 1.0), t_mid = makespan(128, 64, 0.85), t_small = makespan(64, 64, 0.6);
+  if (t_big <= t_mid && t_big <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 128, TileCfg<T>::MINB_BIG>(p, s);
+  if constexpr (sizeof(T) == 4) {
+    if (t_mid <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 64, 2>(p, s);
+  }
+  return launch_simt_tile<T, TA, TB, MODE, EPI, 64, 64, TileCfg<T>::MINB_SMALL>(p, s);
 }
 
 // argument checks of compute/sgemm.go:30-71 (same order, same panic strings).  Slice-length checks
@@ -156,14 +170,26 @@ static int dgemm_impl(int ta, int tb, int m, int n, int k, double alpha, const d
         if (rc) return rc;
       }
       if (mi4 == 0 || ni4 == 0) return GUDA_OK;
+      // dgemm_fixed.go's 8x8 / 4x4 kernels have no zero test: a plain FMA chain
+      rc = dgemm_dmma_try(0, 0, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, mi4, ni4, false, s);
+      if (rc >= 0) return rc;
       return launch_simt<double, false, false, MODE_FMA, EPI_NONE>(p, s);
+    }
+    if (rows_aligned) {
+      rc = dgemm_dmma_try(0, 0, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, m, n, true, s);
+      if (rc >= 0) return rc;
     }
     return rows_aligned ? launch_simt<double, false, false, MODE_FMA, EPI_NONE>(p, s)
                         : launch_simt<double, false, false, MODE_MIXED, EPI_NONE>(p, s);
   }
-  if (ta && !tb)
+  if (ta && !tb) {
+    if (rows_aligned) {
+      rc = dgemm_dmma_try(1, 0, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, m, n, true, s);
+      if (rc >= 0) return rc;
+    }
     return rows_aligned ? launch_simt<double, true, false, MODE_FMA, EPI_NONE>(p, s)
                         : launch_simt<double, true, false, MODE_MIXED, EPI_NONE>(p, s);
+  }
   if (!ta && tb) return launch_simt<double, false, true, MODE_FMA, EPI_NONE>(p, s);     // DotUnitary form: tolerance
   return launch_simt<double, true, true, MODE_UNFUSED, EPI_NONE>(p, s);
 }

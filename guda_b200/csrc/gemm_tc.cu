@@ -69,17 +69,88 @@ __device__ __forceinline__ uint16_t tc_to_f16(float f) {      // float16.go:53-8
 }
 __device__ __forceinline__ float tc_from_f16(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 
-// GELU_tanh for the 16-bit tensor route: tanh(u) = 1 - 2/(exp(2u)+1) with ex2.approx / rcp.approx (abs error ~1e-6,
-// two orders below the bf16/fp16 output spacing); the fp32 routes keep the reference's exact geluFloat32.
+// GELU_tanh for the 16-bit tensor route.  With e = exp(2u), 0.5*x*(1 + tanh(u)) = x - x/(e + 1): one ex2.approx and one
+// rcp.approx per element, no saturation branch (e = inf gives x, e = 0 gives 0).  Absolute error ~2e-7, three orders
+// below the bf16/fp16 output spacing; the fp32 routes keep the reference's exact geluFloat32.
 __device__ __forceinline__ float gelu_fast(float x) {
-  float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-  float e = __expf(2.0f * u);
-  float t = 1.0f - __fdividef(2.0f, e + 1.0f);
-  t = u > 10.0f ? 1.0f : t;
-  return 0.5f * x * (1.0f + t);
+  const float x2 = __fmul_rn(x, x);
+  const float inner = __fmaf_rn(__fmul_rn(0.044715f, x2), x, x);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(__fmul_rn(2.3022082f, inner)));     // 2 * sqrt(2/pi) * log2(e)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(__fadd_rn(e, 1.0f)));
+  return __fmaf_rn(-x, r, x);
 }
 
-template <int EB, int NSPLIT, int BN, int OUT>
+// bias[col0 .. col0+32) -> registers.  All lanes of a warp read the same addresses (one broadcast transaction per load).
+__device__ __forceinline__ void load_bias32(const float* __restrict__ bias, int col0, int n, float (&b)[32]) {
+  if (col0 + 32 <= n && ((reinterpret_cast<uintptr_t>(bias + col0) & 15) == 0)) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 t = __ldg(reinterpret_cast<const float4*>(bias + col0 + j));
+      b[j] = t.x; b[j + 1] = t.y; b[j + 2] = t.z; b[j + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; j++) b[j] = (col0 + j < n) ? __ldg(bias + col0 + j) : 0.0f;
+  }
+}
+
+// One thread's 32 consecutive columns of one C row: beta*C, bias + activation in registers, one store.
+template <int OUT, int EPI>
+__device__ __forceinline__ void store_chunk(const TcParams& p, float (&v)[32], int row, int col0) {
+  const bool full = (col0 + 32 <= p.n);
+  float bias[32];
+  if (EPI != EPI_NONE) load_bias32(p.bias, col0, p.n, bias);
+  if (OUT == OUT_F32) {
+    float* dst = reinterpret_cast<float*>(p.c) + (long long)row * p.ldc + col0;
+    if (p.beta != 0.0f) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) if (full || col0 + j < p.n) v[j] = __fadd_rn(v[j], __fmul_rn(p.beta, dst[j]));
+    }
+    if (EPI != EPI_NONE) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) v[j] = apply_epilogue<float, EPI>(v[j], bias[j]);
+    }
+    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; j++) if (col0 + j < p.n) dst[j] = v[j];
+    }
+  } else {
+    uint16_t* dst = reinterpret_cast<uint16_t*>(p.c) + (long long)row * p.ldc + col0;
+    if (p.beta != 0.0f) {
+#pragma unroll
+      for (int j = 0; j < 32; j++)
+        if (full || col0 + j < p.n) v[j] = __fadd_rn(v[j], __fmul_rn(p.beta, OUT == OUT_BF16 ? tc_from_bf16(dst[j]) : tc_from_f16(dst[j])));
+    }
+    if (EPI == EPI_BIAS_RELU) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) v[j] = apply_epilogue<float, EPI_BIAS_RELU>(v[j], bias[j]);
+    } else if (EPI == EPI_BIAS_GELU) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) v[j] = gelu_fast(__fadd_rn(v[j], bias[j]));
+    }
+    uint32_t packed[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+      uint32_t lo = OUT == OUT_BF16 ? tc_to_bf16(v[2 * j]) : tc_to_f16(v[2 * j]);
+      uint32_t hi = OUT == OUT_BF16 ? tc_to_bf16(v[2 * j + 1]) : tc_to_f16(v[2 * j + 1]);
+      packed[j] = lo | (hi << 16);
+    }
+    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 16; j += 4) *reinterpret_cast<uint4*>(dst + 2 * j) = make_uint4(packed[j], packed[j + 1], packed[j + 2], packed[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; j++) if (col0 + j < p.n) dst[j] = (uint16_t)(packed[j >> 1] >> ((j & 1) * 16));
+    }
+  }
+}
+
+template <int EB, int NSPLIT, int BN, int OUT, int EPI>
 __global__ void __launch_bounds__(192, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
                const __grid_constant__ CUtensorMap map_b0, const __grid_constant__ CUtensorMap map_b1, TcParams p) {
@@ -194,24 +265,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     // ===================== epilogue (warps 2..5; TMEM lane quarter = warp % 4) =====================
     const int q = warp & 3;
     int ci = 0;
+    const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       int tm, tn; tile_coord(t, tm, tn);
       const int row = tm * BM + q * 32 + lane;
       const bool row_ok = row < p.m;
-      float accum[NSPLIT == 2 ? BN : 1];
-      int as = 0;
-      if (NSPLIT == 2) {
-        // promote every K chunk from TMEM into registers with round-to-nearest adds
+      if constexpr (NSPLIT == 2) {
+        // 3xTF32: promote every K chunk from TMEM into registers with round-to-nearest adds
+        float accum[BN];
 #pragma unroll
-        for (int j = 0; j < (NSPLIT == 2 ? BN : 1); j++) accum[j] = 0.0f;
+        for (int j = 0; j < BN; j++) accum[j] = 0.0f;
         for (int kb0 = 0; kb0 < kblocks; kb0 += chunk_blocks, ci++) {
-          as = ci & 1;
+          const int as = ci & 1;
           mbar_wait(&tmem_full[as], (ci >> 1) & 1);
           tc_fence_after();
 #pragma unroll
-          for (int c0 = 0; c0 < (NSPLIT == 2 ? BN : 0); c0 += 32) {
+          for (int c0 = 0; c0 < BN; c0 += 32) {
             uint32_t r[32];
-            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+            tmem_ld_32x32(tlane + (uint32_t)(as * BN + c0), r);
             tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 32; j++) accum[c0 + j] = __fadd_rn(accum[c0 + j], __uint_as_float(r[j]));
@@ -220,79 +291,43 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
           __syncwarp();
           if (lane == 0) mbar_arrive(&tmem_empty[as]);
         }
+#pragma unroll
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          const int col0 = tn * BN + c0;
+          if (row_ok && col0 < p.n) {
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; j++) v[j] = __fmul_rn(p.alpha, accum[c0 + j]);
+            store_chunk<OUT, EPI>(p, v, row, col0);
+          }
+        }
       } else {
-        as = ci & 1;
+        // 16-bit routes: one accumulator stage per tile.  The chunk loop is NOT unrolled (the unrolled epilogue was
+        // 230 KB of SASS and ran out of the instruction cache); the TMEM load of chunk i+1 is in flight while chunk i
+        // is scaled, activated, packed and stored, and the TMEM stage is released as soon as the last chunk is in registers.
+        const int as = ci & 1;
         mbar_wait(&tmem_full[as], (ci >> 1) & 1);
         tc_fence_after();
         ci++;
-      }
-#pragma unroll
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const uint32_t tbase = tlane + (uint32_t)(as * BN);
         uint32_t r[32];
-        if (NSPLIT == 2) {
-#pragma unroll
-          for (int j = 0; j < 32; j++) r[j] = __float_as_uint(accum[(NSPLIT == 2 ? c0 : 0) + (NSPLIT == 2 ? j : 0)]);
-        } else {
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+        tmem_ld_32x32(tbase, r);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
           tmem_ld_wait();
-        }
-        const int col0 = tn * BN + c0;
-        if (row_ok && col0 < p.n) {
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; j++) v[j] = __fmul_rn(p.alpha, __uint_as_float(r[j]));
-          const bool full = (col0 + 32 <= p.n);
-          if (OUT == OUT_F32) {
-            float* dst = reinterpret_cast<float*>(p.c) + (long long)row * p.ldc + col0;
-            if (p.beta != 0.0f) {
-#pragma unroll
-              for (int j = 0; j < 32; j++) if (full || col0 + j < p.n) v[j] = __fadd_rn(v[j], __fmul_rn(p.beta, dst[j]));
-            }
-#pragma unroll
-            for (int j = 0; j < 32; j++) v[j] = p.epi == 0 ? v[j] : (p.epi == 1 ? apply_epilogue<float, EPI_BIAS_RELU>(v[j], (full || col0 + j < p.n) ? p.bias[col0 + j] : 0.f)
-                                                                              : apply_epilogue<float, EPI_BIAS_GELU>(v[j], (full || col0 + j < p.n) ? p.bias[col0 + j] : 0.f));
-            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; j++) if (col0 + j < p.n) dst[j] = v[j];
-            }
+          if (c0 + 32 < BN) {
+            tmem_ld_32x32(tbase + (uint32_t)(c0 + 32), r);
           } else {
-            uint16_t* dst = reinterpret_cast<uint16_t*>(p.c) + (long long)row * p.ldc + col0;
-            if (p.beta != 0.0f) {
-#pragma unroll
-              for (int j = 0; j < 32; j++)
-                if (full || col0 + j < p.n) v[j] = __fadd_rn(v[j], __fmul_rn(p.beta, OUT == OUT_BF16 ? tc_from_bf16(dst[j]) : tc_from_f16(dst[j])));
-            }
-            if (p.epi != 0) {
-#pragma unroll
-              for (int j = 0; j < 32; j++) {
-                float b = (full || col0 + j < p.n) ? p.bias[col0 + j] : 0.f;
-                v[j] = p.epi == 1 ? apply_epilogue<float, EPI_BIAS_RELU>(v[j], b) : gelu_fast(__fadd_rn(v[j], b));
-              }
-            }
-            uint32_t packed[16];
-#pragma unroll
-            for (int j = 0; j < 16; j++) {
-              uint32_t lo = OUT == OUT_BF16 ? tc_to_bf16(v[2 * j]) : tc_to_f16(v[2 * j]);
-              uint32_t hi = OUT == OUT_BF16 ? tc_to_bf16(v[2 * j + 1]) : tc_to_f16(v[2 * j + 1]);
-              packed[j] = lo | (hi << 16);
-            }
-            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-              for (int j = 0; j < 16; j += 4) *reinterpret_cast<uint4*>(dst + 2 * j) = make_uint4(packed[j], packed[j + 1], packed[j + 2], packed[j + 3]);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; j++) if (col0 + j < p.n) dst[j] = (uint16_t)(packed[j >> 1] >> ((j & 1) * 16));
-            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[as]);
           }
+          const int col0 = tn * BN + c0;
+          if (row_ok && col0 < p.n) store_chunk<OUT, EPI>(p, v, row, col0);
         }
-      }
-      if (NSPLIT == 1) {
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[as]);
       }
     }
   }
@@ -331,10 +366,9 @@ static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int eb, const void
   return GUDA_OK;
 }
 
-template <int EB, int NSPLIT, int BN, int OUT>
+template <int EB, int NSPLIT, int BN, int OUT, int EPI>
 static int launch_tc(CUtensorMapDataType dt, int m, int n, int k, float alpha, const void* a0, const void* a1, long long lda,
-                     const void* b0, const void* b1, long long ldb, float beta, void* c, long long ldc, const float* bias, int epi,
-                     cudaStream_t s) {
+                     const void* b0, const void* b1, long long ldb, float beta, void* c, long long ldc, const float* bias, cudaStream_t s) {
   using Cfg = TcCfg<EB, NSPLIT, BN>;
   int rc = get_encode();
   if (rc) return rc;
@@ -347,8 +381,8 @@ static int launch_tc(CUtensorMapDataType dt, int m, int n, int k, float alpha, c
     if ((rc = make_map(&ma1, dt, EB, a1, m, k, lda, Cfg::BK, Cfg::BM))) return rc;
     if ((rc = make_map(&mb1, dt, EB, b1, k, n, ldb, Cfg::B_BOX_N, Cfg::BK, bswz))) return rc;
   }
-  TcParams p{m, n, k, alpha, beta, c, ldc, bias, epi, (m + Cfg::BM - 1) / Cfg::BM, (n + BN - 1) / BN};
-  auto kern = gemm_tc_kernel<EB, NSPLIT, BN, OUT>;
+  TcParams p{m, n, k, alpha, beta, c, ldc, bias, EPI, (m + Cfg::BM - 1) / Cfg::BM, (n + BN - 1) / BN};
+  auto kern = gemm_tc_kernel<EB, NSPLIT, BN, OUT, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
     GUDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
@@ -367,9 +401,14 @@ int gemm16_tc_try(int is_bf16, int m, int n, int k, float alpha, const uint16_t*
                   uint16_t* c, int ldc, const float* bias, int epi, cudaStream_t s) {
   if (m < 128 || n < 128 || k < 64) return -1;                // tiny problems: the exact SIMT route is faster and bit-exact
   if (!tma_ok(a, lda, 2) || !tma_ok(b, ldb, 2)) return -1;
-  if (is_bf16)
-    return launch_tc<2, 1, 256, OUT_BF16>(CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, epi, s);
-  return launch_tc<2, 1, 256, OUT_F16>(CU_TENSOR_MAP_DATA_TYPE_FLOAT16, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, epi, s);
+  if (is_bf16) {
+    const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    if (epi == EPI_BIAS_RELU) return launch_tc<2, 1, 256, OUT_BF16, EPI_BIAS_RELU>(dt, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, s);
+    if (epi == EPI_BIAS_GELU) return launch_tc<2, 1, 256, OUT_BF16, EPI_BIAS_GELU>(dt, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, s);
+    return launch_tc<2, 1, 256, OUT_BF16, EPI_NONE>(dt, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, s);
+  }
+  if (epi != EPI_NONE) return -1;
+  return launch_tc<2, 1, 256, OUT_F16, EPI_NONE>(CU_TENSOR_MAP_DATA_TYPE_FLOAT16, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, s);
 }
 
 // fp32 -> (hi, lo) planes for the 3xTF32 split: hi = x rounded to tf32 (10-bit mantissa, round-to-nearest-even on the
@@ -412,8 +451,8 @@ int sgemm_3xtf32_try(int ta, int tb, int m, int n, int k, float alpha, const flo
   split_tf32_kernel<<<blocks, 256, 0, s>>>(a, lda, (float*)ah.p, (float*)al.p, lda2, m, k);
   split_tf32_kernel<<<blocks, 256, 0, s>>>(b, ldb, (float*)bh.p, (float*)bl.p, ldb2, k, n);
   if ((rc = check_launch("split_tf32"))) return rc;
-  rc = launch_tc<4, 2, 128, OUT_F32>(CU_TENSOR_MAP_DATA_TYPE_FLOAT32, m, n, k, alpha, ah.p, al.p, lda2, bh.p, bl.p, ldb2, beta, c, ldc,
-                                     nullptr, 0, s);
+  rc = launch_tc<4, 2, 128, OUT_F32, EPI_NONE>(CU_TENSOR_MAP_DATA_TYPE_FLOAT32, m, n, k, alpha, ah.p, al.p, lda2, bh.p, bl.p, ldb2, beta, c,
+                                               ldc, nullptr, s);
   if (rc) return rc;
   GUDA_CUDA(cudaStreamSynchronize(s));      // the planes return to the pool when this function exits
   return GUDA_OK;

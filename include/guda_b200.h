@@ -116,6 +116,11 @@ int guda_sgemm(int trans_a, int trans_b, int m, int n, int k, float alpha, const
                const float* b, int ldb, float beta, float* c, int ldc, guda_stream_t stream);
 int guda_dgemm(int trans_a, int trans_b, int m, int n, int k, double alpha, const double* a, int lda,
                const double* b, int ldb, double beta, double* c, int ldc, guda_stream_t stream);
+/* DGEMM route: TENSOR = FP64 tensor pipe (DMMA m8n8k4, dgemm_dmma.cu) for the NN / TN forms with 16-byte aligned operands
+ * (default; same bits as the SIMT route -- see the header of dgemm_dmma.cu); SIMT = DFMA kernel for every form */
+enum { GUDA_DGEMM_TENSOR = 0, GUDA_DGEMM_SIMT = 1 };
+int guda_set_dgemm_mode(int mode);
+int guda_get_dgemm_mode(int* mode);
 /* bfloat16.go:104 GEMMBFloat16 (trans flags ignored by the reference -> must be 0 here), float16.go:201 GEMMFloat16.
  * 16-bit storage, fp32 accumulation; a/b/c are uint16 bit patterns. */
 int guda_gemm_bf16(int trans_a, int trans_b, int m, int n, int k, float alpha, const uint16_t* a, int lda,
@@ -157,7 +162,7 @@ int guda_fill_uniform_f64(double* dst, size_t rows, size_t cols, size_t ld, uint
                           uint64_t full_cols, double lo, double hi, guda_stream_t stream);
 
 /* ---- measured denominators for rooflines (bench.py): kind 0 = FP32 FFMA TFLOP/s, 1 = FP64 DFMA TFLOP/s,
- * 2 = 128-bit streaming copy GB/s (read+write bytes) ---- */
+ * 2 = 128-bit streaming copy GB/s (read+write bytes), 3 = FP64 tensor pipe (DMMA m8n8k4) TFLOP/s ---- */
 int guda_microbench_peak(int kind, int reps, double* value);
 
 /* ---- multi-GPU (new, additive: GetDeviceCount()==1 stays pinned for the single-device API, guda_test.go:332) ----

@@ -336,7 +336,7 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
 
 
 # ---------------------------------------------------------------- headline: SGEMM size^3, strong scaling over a pr x pc grid
-GRID = {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4)}
+from guda_b200.sharding import grid_for, block_extents  # noqa: E402  (integer geometry only; no device code)
 
 
 def main():
@@ -383,9 +383,8 @@ def main():
     copy_peak = dev.peak(2) if rank == 0 else 0.0
 
     n = args.size
-    pr, pc = GRID[world]
-    m_loc, n_loc = n // pr, n // pc
-    r, c = rank // pc, rank % pc
+    pr, pc = grid_for(world)
+    row0, m_loc, col0, n_loc = block_extents(rank, pr, pc, n, n)
     comm = None
     if world > 1:
         ident = (C.c_uint8 * 128)()
@@ -402,8 +401,8 @@ def main():
     # stream as the full matrices: U[-1,1), alpha = 1, beta = 0 (benchmark_test.go:124 form)
     a_panel = g.Malloc(m_loc * n * 4); b_panel = g.Malloc(n * n_loc * 4); c_block = g.Malloc(m_loc * n_loc * 4)
     c_full = g.Malloc(n * n * 4) if world > 1 else None
-    g.FillUniform(a_panel, m_loc, n, n, seed=11, row0=r * m_loc, col0=0, full_cols=n)
-    g.FillUniform(b_panel, n, n_loc, n_loc, seed=12, row0=0, col0=c * n_loc, full_cols=n)
+    g.FillUniform(a_panel, m_loc, n, n, seed=11, row0=row0, col0=0, full_cols=n)
+    g.FillUniform(b_panel, n, n_loc, n_loc, seed=12, row0=0, col0=col0, full_cols=n)
     g.Synchronize()
 
     def step():

@@ -1,0 +1,147 @@
+// guda.hpp -- C++ host-side mirror of GUDA's root-package API (package guda) above the C ABI of include/guda_b200.h.
+//
+// The reference is compiled Go; the build image has no Go toolchain, so besides the cgo shim (go/guda) this header gives
+// compiled callers the same surface: same names, argument meaning and error behaviour.
+//   Malloc/Free/Memcpy/DevicePtr      memory.go:57-66,81-145,246-317        AXPY/DOT/Scale/GEMM     math.go:39,64,170,98
+//   Synchronize/CreateStream/Stream   guda.go:242-305                       FusedGEMMBias{ReLU,GELU} fused.go:313, fused_gelu.go:65
+// Go `error` returns become exceptions: GUDAError (errors.go:27-44), ErrNotSupported (fused.go:11-17); Go panics with the
+// fixed strings of compute/errors.go:9-35 become BlasPanic.  Header-only; link with -lguda_b200.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "../include/guda_b200.h"
+
+namespace guda {
+
+enum class ErrorType { Memory = 0, InvalidArg, Execution, Numerical, Device, NotImplemented };   // errors.go:11-24
+
+struct GUDAError : std::runtime_error {
+  ErrorType type; std::string op, message;
+  GUDAError(ErrorType t, std::string o, std::string m)
+      : std::runtime_error("GUDA error in " + o + ": " + m), type(t), op(std::move(o)), message(std::move(m)) {}
+};
+struct ErrNotSupported : GUDAError { ErrNotSupported() : GUDAError(ErrorType::NotImplemented, "Fused", "operation not supported") {} };
+struct ErrDoubleFree : GUDAError { ErrDoubleFree() : GUDAError(ErrorType::Memory, "Free", "double free detected") {} };
+struct BlasPanic : std::logic_error { using std::logic_error::logic_error; };
+
+inline void check(int rc, const char* op) {
+  if (rc == GUDA_OK) return;
+  std::string msg = guda_last_error();
+  if (rc == GUDA_ERR_INVALID_ARG && msg.rfind("blas: ", 0) == 0) throw BlasPanic(msg);
+  if (rc == GUDA_ERR_NOT_IMPLEMENTED && msg == "operation not supported") throw ErrNotSupported();
+  if (rc == GUDA_ERR_MEMORY && msg == "double free detected") throw ErrDoubleFree();
+  throw GUDAError(static_cast<ErrorType>(rc - 1), op, msg);
+}
+
+enum MemcpyKind { MemcpyHostToHost = 0, MemcpyHostToDevice, MemcpyDeviceToHost, MemcpyDeviceToDevice, MemcpyDefault };   // memory.go:15-21
+
+// guda.go:95-99.  Typed views are device->host snapshots.
+struct DevicePtr {
+  void* ptr = nullptr; size_t size = 0; size_t offset = 0;
+  DevicePtr Offset(size_t bytes) const { return DevicePtr{static_cast<char*>(ptr) + bytes, size - bytes, offset + bytes}; }
+  size_t Size() const { return size; }
+  template <typename T> std::vector<T> View() const {
+    std::vector<T> out(size / sizeof(T));
+    if (!out.empty()) check(guda_memcpy(out.data(), ptr, out.size() * sizeof(T), GUDA_MEMCPY_D2H, nullptr), "Memcpy");
+    return out;
+  }
+  std::vector<float> Float32() const { return View<float>(); }
+  std::vector<double> Float64() const { return View<double>(); }
+  std::vector<int32_t> Int32() const { return View<int32_t>(); }
+  std::vector<uint8_t> Byte() const { return View<uint8_t>(); }
+  template <typename T> void CopyFrom(const std::vector<T>& src) const {
+    if (src.size() * sizeof(T) > size) throw GUDAError(ErrorType::InvalidArg, "CopyFrom", "source larger than the device buffer");
+    if (!src.empty()) check(guda_memcpy(ptr, src.data(), src.size() * sizeof(T), GUDA_MEMCPY_H2D, nullptr), "CopyFrom");
+  }
+};
+
+inline DevicePtr Malloc(size_t size) { DevicePtr d; check(guda_malloc(&d.ptr, size), "Malloc"); d.size = size; return d; }
+inline void Free(const DevicePtr& d) { check(guda_free(d.ptr), "Free"); }
+inline void Memcpy(const DevicePtr& dst, const void* src, size_t size, MemcpyKind = MemcpyHostToDevice) {
+  if (size) check(guda_memcpy(dst.ptr, src, size, GUDA_MEMCPY_H2D, nullptr), "Memcpy");
+}
+inline void Memcpy(void* dst, const DevicePtr& src, size_t size, MemcpyKind = MemcpyDeviceToHost) {
+  if (size) check(guda_memcpy(dst, src.ptr, size, GUDA_MEMCPY_D2H, nullptr), "Memcpy");
+}
+inline void Memcpy(const DevicePtr& dst, const DevicePtr& src, size_t size, MemcpyKind = MemcpyDeviceToDevice) {
+  if (size) check(guda_memcpy(dst.ptr, src.ptr, size, GUDA_MEMCPY_D2D, nullptr), "Memcpy");
+}
+inline void GetStats(int64_t* allocated, int64_t* peak) { check(guda_pool_stats(allocated, peak), "GetStats"); }   // memory.go:230
+inline void Synchronize() { check(guda_device_synchronize(), "Synchronize"); }                                     // guda.go:200
+inline int GetDeviceCount() { return 1; }                                                                         // guda.go:227-229
+inline void SetDevice(int id) { if (id != 0) throw GUDAError(ErrorType::InvalidArg, "SetDevice", "invalid device ID"); }
+
+class Stream {                                                                                                    // guda.go:57-62
+ public:
+  Stream() { check(guda_stream_create(&h_), "CreateStream"); }
+  ~Stream() { if (h_) guda_stream_destroy(h_); }
+  Stream(const Stream&) = delete; Stream& operator=(const Stream&) = delete;
+  void Synchronize() { check(guda_stream_synchronize(h_), "StreamSynchronize"); }
+  guda_stream_t handle() const { return h_; }
+ private:
+  guda_stream_t h_ = nullptr;
+};
+
+class Event {
+ public:
+  Event() { check(guda_event_create(&h_), "EventCreate"); }
+  ~Event() { if (h_) guda_event_destroy(h_); }
+  Event(const Event&) = delete; Event& operator=(const Event&) = delete;
+  void Record(const Stream* s = nullptr) { check(guda_event_record(h_, s ? s->handle() : nullptr), "EventRecord"); }
+  void Synchronize() { check(guda_event_synchronize(h_), "EventSynchronize"); }
+  static float ElapsedTime(const Event& a, const Event& b) { float ms = 0; check(guda_event_elapsed_ms(a.h_, b.h_, &ms), "EventElapsedTime"); return ms; }
+ private:
+  guda_event_t h_ = nullptr;
+};
+
+inline float* f32(const DevicePtr& d) { return static_cast<float*>(d.ptr); }
+inline double* f64(const DevicePtr& d) { return static_cast<double*>(d.ptr); }
+
+// math.go:39,64,170
+inline void AXPY(float alpha, const DevicePtr& x, const DevicePtr& y, int n) { check(guda_saxpy(n, alpha, f32(x), 1, f32(y), 1, nullptr), "AXPY"); }
+inline float DOT(const DevicePtr& x, const DevicePtr& y, int n) { float r = 0; check(guda_sdot(n, f32(x), 1, f32(y), 1, &r, nullptr), "DOT"); return r; }
+inline void Scale(float alpha, const DevicePtr& x, int n) { check(guda_sscal(n, alpha, f32(x), 1, nullptr), "Scale"); }
+
+// compute/sgemm.go:116-136: the slice-length panics need the DevicePtr sizes, so they are raised here
+inline void check_lengths(bool ta, bool tb, int m, int n, int k, int lda, int ldb, int ldc, size_t la, size_t lb, size_t lc) {
+  if (m <= 0 || n <= 0 || k < 0) return;
+  auto need = [](long long rows, long long ld, long long cols) { return (size_t)((rows - 1) * ld + cols); };
+  if (la < (ta ? need(k, lda, m) : need(m, lda, k))) throw BlasPanic("blas: insufficient length of a");
+  if (lb < (tb ? need(n, ldb, k) : need(k, ldb, n))) throw BlasPanic("blas: insufficient length of b");
+  if (lc < need(m, ldc, n)) throw BlasPanic("blas: insufficient length of c");
+}
+
+// math.go:98
+inline void GEMM(bool transA, bool transB, int m, int n, int k, float alpha, const DevicePtr& a, int lda, const DevicePtr& b, int ldb,
+                 float beta, const DevicePtr& c, int ldc) {
+  if (m >= 0 && n >= 0 && k >= 0 && lda >= 1 && ldb >= 1 && ldc >= 1) check_lengths(transA, transB, m, n, k, lda, ldb, ldc, a.size / 4, b.size / 4, c.size / 4);
+  check(guda_sgemm(transA, transB, m, n, k, alpha, f32(a), lda, f32(b), ldb, beta, f32(c), ldc, nullptr), "GEMM");
+}
+inline void Dgemm(bool transA, bool transB, int m, int n, int k, double alpha, const DevicePtr& a, int lda, const DevicePtr& b, int ldb,
+                  double beta, const DevicePtr& c, int ldc) {
+  if (m >= 0 && n >= 0 && k >= 0 && lda >= 1 && ldb >= 1 && ldc >= 1) check_lengths(transA, transB, m, n, k, lda, ldb, ldc, a.size / 8, b.size / 8, c.size / 8);
+  check(guda_dgemm(transA, transB, m, n, k, alpha, f64(a), lda, f64(b), ldb, beta, f64(c), ldc, nullptr), "Dgemm");
+}
+// fused.go:313, fused_gelu.go:65
+inline void FusedGEMMBiasReLU(bool transA, bool transB, int m, int n, int k, float alpha, const DevicePtr& a, int lda, const DevicePtr& b,
+                              int ldb, float beta, const DevicePtr& c, int ldc, const DevicePtr& bias) {
+  check(guda_sgemm_bias_relu(transA, transB, m, n, k, alpha, f32(a), lda, f32(b), ldb, beta, f32(c), ldc, f32(bias), nullptr), "FusedGEMMBiasReLU");
+}
+inline void FusedGEMMBiasGELU(bool transA, bool transB, int m, int n, int k, float alpha, const DevicePtr& a, int lda, const DevicePtr& b,
+                              int ldb, float beta, const DevicePtr& c, int ldc, const DevicePtr& bias) {
+  check(guda_sgemm_bias_gelu(transA, transB, m, n, k, alpha, f32(a), lda, f32(b), ldb, beta, f32(c), ldc, f32(bias), nullptr), "FusedGEMMBiasGELU");
+}
+// bfloat16.go:104, float16.go:201
+inline void GEMMBFloat16(bool transA, bool transB, int m, int n, int k, float alpha, const DevicePtr& a, int lda, const DevicePtr& b, int ldb,
+                         float beta, const DevicePtr& c, int ldc) {
+  check(guda_gemm_bf16(transA, transB, m, n, k, alpha, (const uint16_t*)a.ptr, lda, (const uint16_t*)b.ptr, ldb, beta, (uint16_t*)c.ptr, ldc, nullptr), "GEMMBFloat16");
+}
+inline void GEMMFloat16(bool transA, bool transB, int m, int n, int k, float alpha, const DevicePtr& a, int lda, const DevicePtr& b, int ldb,
+                        float beta, const DevicePtr& c, int ldc) {
+  check(guda_gemm_f16(transA, transB, m, n, k, alpha, (const uint16_t*)a.ptr, lda, (const uint16_t*)b.ptr, ldb, beta, (uint16_t*)c.ptr, ldc, nullptr), "GEMMFloat16");
+}
+
+}  // namespace guda

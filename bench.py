@@ -377,7 +377,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    ffma_peak = dev.peak(0)
+    ffma_peak = max(dev.peak(0), dev.peak(4))          # scalar FFMA and packed FFMA2: the roofline uses the higher
     dfma_peak = dev.peak(1) if rank == 0 else 0.0
     dmma_peak = dev.peak(3) if rank == 0 else 0.0
     copy_peak = dev.peak(2) if rank == 0 else 0.0
@@ -434,7 +434,7 @@ def main():
     if args.mode == "exact":
         roof = {"bound": "fp32_simt", "pipe": "fp32 FFMA (exact-order SIMT; tensor cores cannot reproduce the reference's per-step fp32 rounding)",
                 "achieved": kern_tf, "peak": ffma_peak, "unit": "TFLOP/s", "frac": kern_tf / ffma_peak,
-                "peak_source": "FFMA microbenchmark measured in this run (MEASURED_PEAKS.json has no fp32 SIMT figure)",
+                "peak_source": "max(FFMA, FFMA2) microbenchmarks measured in this run (MEASURED_PEAKS.json has no fp32 SIMT figure)",
                 "frac_of_measured_bf16_tensor_peak": kern_tf / peaks["bf16_tflops_sustained"],
                 "traffic": ncu_traffic("sgemm_simt_%d_p%d" % (n, world))}
     else:

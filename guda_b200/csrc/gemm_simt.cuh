@@ -36,6 +36,22 @@ __device__ __forceinline__ double g_mul(double a, double b) { return __dmul_rn(a
 __device__ __forceinline__ float g_add(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ double g_add(double a, double b) { return __dadd_rn(a, b); }
 
+// Two independent IEEE round-to-nearest fp32 FMAs in one instruction (fma.rn.f32x2 -> FFMA2 on sm_100a): the same bits as
+// two scalar fmaf() calls, half the issue slots.  c0 = fma(a, b0, c0); c1 = fma(a, b1, c1).  ptxas keeps the accumulator
+// pair and the B pair (straight out of LDS.128) in aligned 64-bit registers, so the mov.b64 packs below cost nothing.
+__device__ __forceinline__ void fma2_f32(float& c0, float& c1, unsigned long long aa, float b0, float b1) {
+  unsigned long long c, bb;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(c0), "f"(c1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(b0), "f"(b1));
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(c) : "l"(aa), "l"(bb));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(c0), "=f"(c1) : "l"(c));
+}
+__device__ __forceinline__ unsigned long long dup_f32(float a) {
+  unsigned long long aa;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(aa) : "f"(a));
+  return aa;
+}
+
 // ---- geluFloat32 restated with explicit roundings (fused_gelu.go:44-56, activations.go:31-90) ----
 __device__ __forceinline__ float gelu_exp_f32(float x) {
   if (x > 88.7f) return 3.40282346638528859811704183484516925440e+38f;
@@ -254,10 +270,20 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p) {
         load_frag<T, HM>(af + HM, &sm.a[cur][kk][BM / 2 + ty * HM]);
         load_frag<T, HN>(bf, &sm.b[cur][kk][tx * HN]);
         load_frag<T, HN>(bf + HN, &sm.b[cur][kk][BN / 2 + tx * HN]);
+        if constexpr (sizeof(T) == 4 && TN % 2 == 0) {
 #pragma unroll
-        for (int i = 0; i < TM; i++)
+          for (int i = 0; i < TM; i++) {
+            const unsigned long long aa = dup_f32((float)af[i]);
 #pragma unroll
-          for (int j = 0; j < TN; j++) acc[i][j] = g_fma(af[i], bf[j], acc[i][j]);
+            for (int j = 0; j < TN; j += 2)
+              fma2_f32(reinterpret_cast<float&>(acc[i][j]), reinterpret_cast<float&>(acc[i][j + 1]), aa, (float)bf[j], (float)bf[j + 1]);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < TM; i++)
+#pragma unroll
+            for (int j = 0; j < TN; j++) acc[i][j] = g_fma(af[i], bf[j], acc[i][j]);
+        }
       }
     } else {
 #pragma unroll

@@ -20,6 +20,26 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T seed
   if (s == T(12345.678)) out[0] = s;       // never true; keeps the chain alive
 }
 
+// packed fp32: fma.rn.f32x2 (FFMA2), 8 independent 2-wide chains per thread
+__global__ void __launch_bounds__(256) ffma2_peak_kernel(float* out, int iters) {
+  unsigned long long a[8], x, y;
+  const float xf = 0.999f, yf = 1e-3f;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(x) : "f"(xf));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(y) : "f"(yf));
+#pragma unroll
+  for (int i = 0; i < 8; i++) { float f = 1.0f + threadIdx.x + i; asm("mov.b64 %0, {%1, %1};" : "=l"(a[i]) : "f"(f)); }
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++)
+#pragma unroll
+      for (int i = 0; i < 8; i++) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(a[i]) : "l"(x), "l"(y));
+  }
+  unsigned long long r = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) r ^= a[i];
+  if (r == 0x12345678ull) out[0] = 1.0f;
+}
+
 // FP64 tensor pipe: mma.sync.m8n8k4.f64 (DMMA), 8 independent accumulator chains per warp
 __global__ void __launch_bounds__(256) dmma_peak_kernel(double* out, int iters) {
   double a = 1.0 + threadIdx.x * 1e-3, b = 0.999;
@@ -89,6 +109,28 @@ int guda_microbench_peak(int kind, int reps, double* value) {
   if (kind == 1) return fma_peak<double>(value, reps);
   int rc = bind_device();
   if (rc) return rc;
+  if (kind == 4) {            // packed fp32 FMA (FFMA2) TFLOP/s
+    float* out;
+    GUDA_CUDA(cudaMalloc((void**)&out, 256));
+    cudaEvent_t e0, e1;
+    GUDA_CUDA(cudaEventCreate(&e0)); GUDA_CUDA(cudaEventCreate(&e1));
+    const int iters = 4096, blocks = sm_count() * 8;
+    cudaStream_t s = native(nullptr);
+    double best = 0;
+    for (int r = 0; r < reps + 1; r++) {
+      GUDA_CUDA(cudaEventRecord(e0, s));
+      ffma2_peak_kernel<<<blocks, 256, 0, s>>>(out, iters);
+      GUDA_CUDA(cudaEventRecord(e1, s));
+      GUDA_CUDA(cudaEventSynchronize(e1));
+      float ms = 0;
+      GUDA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      double t = 2.0 * 2.0 * 64.0 * iters * 256.0 * blocks / (ms * 1e-3) / 1e12;
+      if (r > 0 && t > best) best = t;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+    *value = best;
+    return GUDA_OK;
+  }
   if (kind == 3) {            // FP64 tensor pipe (DMMA m8n8k4) TFLOP/s
     double* out;
     GUDA_CUDA(cudaMalloc((void**)&out, 256));

@@ -162,7 +162,8 @@ int guda_fill_uniform_f64(double* dst, size_t rows, size_t cols, size_t ld, uint
                           uint64_t full_cols, double lo, double hi, guda_stream_t stream);
 
 /* ---- measured denominators for rooflines (bench.py): kind 0 = FP32 FFMA TFLOP/s, 1 = FP64 DFMA TFLOP/s,
- * 2 = 128-bit streaming copy GB/s (read+write bytes), 3 = FP64 tensor pipe (DMMA m8n8k4) TFLOP/s ---- */
+ * 2 = 128-bit streaming copy GB/s (read+write bytes), 3 = FP64 tensor pipe (DMMA m8n8k4) TFLOP/s,
+ * 4 = packed fp32 FMA (fma.rn.f32x2 / FFMA2) TFLOP/s ---- */
 int guda_microbench_peak(int kind, int reps, double* value);
 
 /* ---- multi-GPU (new, additive: GetDeviceCount()==1 stays pinned for the single-device API, guda_test.go:332) ----

@@ -66,6 +66,7 @@ SIGNATURES = {
     "guda_get_sgemm_mode": (i, [ip]),
     "guda_sgemm": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_dgemm": (i, [i, i, i, i, i, d, vp, i, vp, i, d, vp, i, vp]),
+    "guda_sgemm_scatter": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, C.POINTER(vp), i, i, i, i, vp]),
     "guda_set_dgemm_mode": (i, [i]),
     "guda_get_dgemm_mode": (i, [ip]),
     "guda_gemm_bf16": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
@@ -88,6 +89,8 @@ SIGNATURES = {
     "guda_comm_init_rank": (i, [C.POINTER(vp), i, i, C.POINTER(C.c_uint8)]),
     "guda_comm_destroy": (i, [vp]),
     "guda_sgemm_sharded": (i, [vp, i, i, i, i, i, f, vp, i, vp, i, vp, i, vp, i, vp]),
+    "guda_comm_set_gather_mode": (i, [vp, i]),
+    "guda_comm_get_gather_mode": (i, [vp, ip]),
     "guda_sdot_sharded": (i, [vp, i, vp, vp, fp, vp]),
     "guda_microbench_peak": (i, [i, i, dp]),
 }

@@ -254,6 +254,8 @@ static int launch_dmma(const DmmaParams& p, cudaStream_t s) {
 }
 
 static int g_dgemm_mode = GUDA_DGEMM_TENSOR;
+int dgemm_dmma_one(int ta, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta, double* c,
+                   int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s);
 int dgemm_mode() { return g_dgemm_mode; }
 
 // Returns GUDA_OK / an error if the DMMA route took the call, -1 if the operands are not eligible (caller uses the SIMT kernel).
@@ -263,8 +265,24 @@ int dgemm_dmma_try(int ta, int tb, int m, int n, int k, double alpha, const doub
   if (g_dgemm_mode != GUDA_DGEMM_TENSOR || tb) return -1;
   if (m < 32 || n < 32 || k < 4) return -1;
   if (((uintptr_t)a & 15) || ((uintptr_t)b & 15) || (lda & 1) || (ldb & 1)) return -1;
+  if ((long long)((m + dmma::BM - 1) / dmma::BM) * ((n + dmma::BN - 1) / dmma::BN) > 0x7fffffffLL) return -1;
+  // K blocking across launches keeps the co-resident CTAs' panels inside L2 (same bits: see launch_simt in gemm.cu)
+  constexpr int KC = 1024;
+  if (k >= 4 * KC && (long long)m * n >= (1ll << 22)) {
+    for (int k0 = 0; k0 < k; k0 += KC) {
+      const int kc = (k0 + KC >= k) ? k - k0 : KC;
+      int rc = dgemm_dmma_one(ta, m, n, kc, alpha, ta ? a + (long long)k0 * lda : a + k0, lda, b + (long long)k0 * ldb, ldb,
+                              k0 == 0 ? beta : 1.0, c, ldc, edge_m, edge_n, skip, s);
+      if (rc) return rc;
+    }
+    return GUDA_OK;
+  }
+  return dgemm_dmma_one(ta, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, edge_m, edge_n, skip, s);
+}
+
+int dgemm_dmma_one(int ta, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta, double* c,
+                   int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s) {
   DmmaParams p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, edge_m, edge_n, (m + dmma::BM - 1) / dmma::BM, (n + dmma::BN - 1) / dmma::BN};
-  if ((long long)p.tiles_m * p.tiles_n > 0x7fffffffLL) return -1;
   const bool scale = alpha != 1.0;
   if (ta) {
     if (scale) return skip ? launch_dmma<true, true, true>(p, s) : launch_dmma<true, true, false>(p, s);

@@ -80,7 +80,7 @@ static int launch_simt_tile(const GemmParams<T>& p, cudaStream_t s) {
 //   ceil(tiles / SMs) * BM*BN / efficiency      (efficiency = FFMA share of the inner loop, measured: 8x8 micro-tile 1.0,
 //   8x4 0.85, 4x4 0.6), which sends 1024^3 (64 big tiles on 148 SMs) to 128x64 and anything large to 128x128.
 template <typename T, bool TA, bool TB, int MODE, int EPI>
-static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
+static int launch_simt_one(const GemmParams<T>& p, cudaStream_t s) {
   const long long sms = sm_count();
   auto makespan = [&](int bm, int bn, double eff) {
     const long long tiles = (long long)((p.m + bm - 1) / bm) * ((p.n + bn - 1) / bn);
@@ -92,6 +92,33 @@ static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
     if (t_mid <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 64, 2>(p, s);
   }
   return launch_simt_tile<T, TA, TB, MODE, EPI, 64, 64, TileCfg<T>::MINB_SMALL>(p, s);
+}
+
+// K blocking across launches.  A C element is one sequential-k chain held in an fp32 (fp64) accumulator, so stopping the
+// chain at k1, storing the accumulator and resuming from it with beta = 1 gives the SAME bits (the reference itself walks
+// 64-deep k blocks this way, compute/sgemm.go:236-260).  With K far beyond what L2 can hold, the ~300 co-resident CTAs
+// drift apart in k and stop sharing A/B panels: ncu measured 11.4 TB of DRAM reads for one 65536^3 launch (L2 hit 35 %).
+// Chunks of KC keep the resident set -- (16 + ~18) tile panels x KC -- inside L2.
+template <typename T> struct KChunk { static constexpr int KC = sizeof(T) == 4 ? 2048 : 1024; };
+
+template <typename T, bool TA, bool TB, int MODE, int EPI>
+static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
+  constexpr int KC = KChunk<T>::KC;
+  const bool chunk = EPI == EPI_NONE && p.c != nullptr && p.k >= 4 * KC && (long long)p.m * p.n >= (1ll << 22) &&
+                     p.edge_m >= p.m && p.edge_n >= p.n;
+  if (!chunk) return launch_simt_one<T, TA, TB, MODE, EPI>(p, s);
+  GemmParams<T> q = p;
+  for (int k0 = 0; k0 < p.k; k0 += KC) {
+    const bool last = k0 + KC >= p.k;
+    q.k = last ? p.k - k0 : KC;
+    q.a = TA ? p.a + (long long)k0 * p.lda : p.a + k0;
+    q.b = TB ? p.b + k0 : p.b + (long long)k0 * p.ldb;
+    q.beta = k0 == 0 ? p.beta : T(1);
+    q.nscatter = last ? p.nscatter : 0;
+    int rc = launch_simt_one<T, TA, TB, MODE, EPI>(q, s);
+    if (rc) return rc;
+  }
+  return GUDA_OK;
 }
 
 // argument checks of compute/sgemm.go:30-71 (same order, same panic strings).  Slice-length checks
@@ -110,16 +137,19 @@ static int check_gemm_args(int ta, int tb, int m, int n, int k, int lda, int ldb
   return GUDA_OK;
 }
 
+struct ScatterArgs { int n; float* dst[GUDA_MAX_SCATTER]; long long ld, off; };
+
 static int sgemm_impl(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
-                      float beta, float* c, int ldc, const float* bias, int epi, guda_stream_t stream) {
+                      float beta, float* c, int ldc, const float* bias, int epi, guda_stream_t stream,
+                      const ScatterArgs* scatter = nullptr) {
   int rc = check_gemm_args(ta, tb, m, n, k, lda, ldb, ldc);
   if (rc) return rc;
   if (m == 0 || n == 0) return GUDA_OK;                                   // compute/sgemm.go:74
   rc = bind_device();
   if (rc) return rc;
-  if (!c || ((!a || !b) && k > 0)) return set_error(GUDA_ERR_INVALID_ARG, "GEMM: null pointer");
+  if ((!c && !(scatter && beta == 0.0f)) || ((!a || !b) && k > 0)) return set_error(GUDA_ERR_INVALID_ARG, "GEMM: null pointer");
   cudaStream_t s = native(stream);
-  if (epi == EPI_NONE) {
+  if (epi == EPI_NONE && !scatter) {
     // compute/sgemm.go:80-96 small-matrix kernels (NN contiguous only; the bTrans branch :98-111 multiplies by
     // B as stored, a reference defect that is deliberately NOT reproduced -- see DESIGN.md)
     if (!ta && !tb && lda == k && ldb == n && ldc == n && m == n && n == k && (m == 4 || m == 8 || m == 16)) {
@@ -135,6 +165,12 @@ static int sgemm_impl(int ta, int tb, int m, int n, int k, float alpha, const fl
     }
   }
   GemmParams<float> p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, bias, m, n};
+  if (scatter) {
+    if ((alpha == 0.0f || k == 0) && beta == 1.0f && !c) return GUDA_OK;
+    p.nscatter = scatter->n;
+    for (int i = 0; i < scatter->n; i++) p.scatter[i] = scatter->dst[i];
+    p.scatter_ld = scatter->ld; p.scatter_off = scatter->off;
+  }
   if (epi == EPI_BIAS_RELU) return launch_simt<float, false, false, MODE_FMA, EPI_BIAS_RELU>(p, s);
   if (epi == EPI_BIAS_GELU) return launch_simt<float, false, false, MODE_FMA, EPI_BIAS_GELU>(p, s);
   if (!ta && !tb) return launch_simt<float, false, false, MODE_FMA, EPI_NONE>(p, s);
@@ -223,6 +259,23 @@ int guda_sgemm(int ta, int tb, int m, int n, int k, float alpha, const float* a,
 int guda_dgemm(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
                double* c, int ldc, guda_stream_t stream) {
   return dgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream);
+}
+
+// SGEMM whose epilogue also stores the finished block at (row0, col0) of `ndest` larger row-major matrices (leading
+// dimension ld_dest) -- the building block of the fused GEMM + all-gather (sharded.cu), exact-order route only.
+int guda_sgemm_scatter(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
+                       float* c, int ldc, float* const* host_dests, int ndest, int ld_dest, int row0, int col0, guda_stream_t stream) {
+  if (ndest < 0 || ndest > GUDA_MAX_SCATTER || (ndest > 0 && !host_dests)) return set_error(GUDA_ERR_INVALID_ARG, "sgemm_scatter: bad destination list");
+  if (ndest == 0) return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, stream);
+  if (row0 < 0 || col0 < 0 || ld_dest < col0 + n) GUDA_PANIC("blas: bad leading dimension of C");
+  ScatterArgs sc{};
+  sc.n = ndest;
+  for (int i = 0; i < ndest; i++) {
+    if (!host_dests[i]) return set_error(GUDA_ERR_INVALID_ARG, "sgemm_scatter: null destination");
+    sc.dst[i] = host_dests[i];
+  }
+  sc.ld = ld_dest; sc.off = (long long)row0 * ld_dest + col0;
+  return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, stream, &sc);
 }
 
 static int fused_checks(int ta, int tb, float beta, const float* bias) {

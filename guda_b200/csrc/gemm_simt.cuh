@@ -24,6 +24,7 @@ namespace guda {
 
 enum { MODE_FMA = 0, MODE_UNFUSED = 1, MODE_MIXED = 2, MODE_UNFUSED_NOSKIP = 3 };   // NOSKIP: bfloat16.go:152 has no zero test
 enum { EPI_NONE = 0, EPI_BIAS_RELU = 1, EPI_BIAS_GELU = 2 };
+#define GUDA_MAX_SCATTER 8
 
 template <typename T> struct GemmVec;
 template <> struct GemmVec<float> { using V = float4; static constexpr int N = 4; };
@@ -108,6 +109,11 @@ struct GemmParams {
   T* c; long long ldc;
   const T* bias;
   int edge_m, edge_n;      // elements with i >= edge_m or j >= edge_n are NOT stored (fp64 NN alpha==1 edges)
+  // fused all-gather (sharded.cu): besides c, the finished tile is stored at (row, col) + scatter_off of every matrix in
+  // scatter[] -- the gathered C of each rank, peers reached through NVLink-mapped (CUDA IPC) pointers.  c may be null.
+  int nscatter;
+  T* scatter[GUDA_MAX_SCATTER];
+  long long scatter_ld, scatter_off;
 };
 
 template <typename T, int BM, int BN, int BK>
@@ -332,14 +338,29 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p) {
         if (EPI != EPI_NONE) bias = (col0 + j < p.n) ? p.bias[col0 + j] : T(0);
         out[j] = apply_epilogue<T, EPI>(acc[i][jh * HN + j], bias);
       }
-      T* dst = p.c + (long long)row * p.ldc + col0;
       int lim = p.n < p.edge_n ? p.n : p.edge_n;
-      if (FAST && HN % VN == 0) {
+      if (p.c) {
+        T* dst = p.c + (long long)row * p.ldc + col0;
+        if (FAST && HN % VN == 0) {
 #pragma unroll
-        for (int j = 0; j < HN; j += VN) *reinterpret_cast<V*>(dst + j) = *reinterpret_cast<V*>(out + j);
-      } else {
+          for (int j = 0; j < HN; j += VN) *reinterpret_cast<V*>(dst + j) = *reinterpret_cast<V*>(out + j);
+        } else {
 #pragma unroll
-        for (int j = 0; j < HN; j++) if (col0 + j < lim) dst[j] = out[j];
+          for (int j = 0; j < HN; j++) if (col0 + j < lim) dst[j] = out[j];
+        }
+      }
+      if (p.nscatter) {
+        const bool vec = (HN % VN == 0) && (p.scatter_ld % VN == 0) && (p.scatter_off % VN == 0) && (col0 + HN <= lim);
+        for (int s = 0; s < p.nscatter; s++) {
+          T* dst = p.scatter[s] + (long long)row * p.scatter_ld + p.scatter_off + col0;
+          if (vec && (reinterpret_cast<uintptr_t>(p.scatter[s]) & 15) == 0) {
+#pragma unroll
+            for (int j = 0; j < HN; j += VN) *reinterpret_cast<V*>(dst + j) = *reinterpret_cast<V*>(out + j);
+          } else {
+#pragma unroll
+            for (int j = 0; j < HN; j++) if (col0 + j < lim) dst[j] = out[j];
+          }
+        }
       }
     }
   }

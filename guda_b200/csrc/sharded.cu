@@ -3,11 +3,16 @@
 // (dlopen) so the library has no link-time NCCL dependency and single-GPU users never touch it.
 // The reference has no multi-device notion at all (guda.go:227-229 GetDeviceCount() == 1).
 #include "common.cuh"
+#include <cuda.h>
 #include <dlfcn.h>
 #include <nccl.h>
 #include <mutex>
+#include <vector>
 
 namespace guda {
+
+int sgemm_mode();
+constexpr int GUDA_MAX_SCATTER_RANKS = 8;     // == GUDA_MAX_SCATTER of gemm_simt.cuh
 
 struct NcclApi {
   void* handle = nullptr;
@@ -49,13 +54,74 @@ static int load_nccl() {
     if (_r != ncclSuccess) return set_error(GUDA_ERR_EXECUTION, "%s failed: %s", #call, g_nccl.GetErrorString(_r)); \
   } while (0)
 
+// what a rank publishes about its gathered-C buffer: the IPC handle of the allocation that holds it + the offset inside it
+struct PeerRecord {
+  cudaIpcMemHandle_t handle;     // 64 bytes
+  unsigned long long offset;
+  unsigned long long ok;
+};
+struct PeerMapping { cudaIpcMemHandle_t handle; void* base; };
+
 struct Comm {
   ncclComm_t comm;
   int nranks, rank;
-  float* staging = nullptr;      // all-gather landing zone, grown on demand
+  float* staging = nullptr;      // all-gather landing zone (NCCL mode), grown on demand
   size_t staging_bytes = 0;
   float* dev_scalar = nullptr;
+  int gather_mode = GUDA_GATHER_P2P;
+  bool p2p_failed = false;       // agreed by all ranks: peer mapping is not available here
+  PeerRecord* dev_records = nullptr;            // [nranks + 1]: slot nranks is this rank's send buffer
+  PeerRecord* host_records = nullptr;           // pinned, [nranks + 1]
+  std::vector<std::vector<PeerMapping>> opened; // per peer rank: allocations already mapped into this process
 };
+
+// Collective: every rank publishes where its c_full lives; returns device-usable pointers to every rank's c_full.
+// The NCCL all-gather + stream synchronise also acts as the entry barrier: when it returns, every rank has finished
+// whatever preceded this call on its stream, so peers may overwrite its c_full.
+static int resolve_peers(Comm* c, float* c_full, cudaStream_t s, float** out, bool* all_ok) {
+  PeerRecord mine{};
+  CUdeviceptr base = 0; size_t range = 0;
+  // the driver entry point is resolved at run time so that the library has no link-time dependency on libcuda.so.1
+  typedef CUresult (*AddressRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+  static AddressRangeFn address_range = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) fn = nullptr;
+    return reinterpret_cast<AddressRangeFn>(fn);
+  }();
+  bool ok = address_range && address_range(&base, &range, (CUdeviceptr)c_full) == CUDA_SUCCESS &&
+            cudaIpcGetMemHandle(&mine.handle, (void*)base) == cudaSuccess;
+  cudaGetLastError();
+  mine.offset = ok ? (unsigned long long)((CUdeviceptr)c_full - base) : 0;
+  mine.ok = ok ? 1 : 0;
+  c->host_records[c->nranks] = mine;
+  GUDA_CUDA(cudaMemcpyAsync(c->dev_records + c->nranks, c->host_records + c->nranks, sizeof(PeerRecord), cudaMemcpyHostToDevice, s));
+  GUDA_NCCL(g_nccl.AllGather(c->dev_records + c->nranks, c->dev_records, sizeof(PeerRecord), ncclChar, c->comm, s));
+  GUDA_CUDA(cudaMemcpyAsync(c->host_records, c->dev_records, sizeof(PeerRecord) * c->nranks, cudaMemcpyDeviceToHost, s));
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  bool good = true;
+  for (int r = 0; r < c->nranks; r++) good = good && c->host_records[r].ok;
+  for (int r = 0; r < c->nranks && good; r++) {
+    if (r == c->rank) { out[r] = c_full; continue; }
+    const PeerRecord& rec = c->host_records[r];
+    void* mapped = nullptr;
+    for (const PeerMapping& pm : c->opened[r])
+      if (memcmp(&pm.handle, &rec.handle, sizeof(cudaIpcMemHandle_t)) == 0) { mapped = pm.base; break; }
+    if (!mapped) {
+      if (cudaIpcOpenMemHandle(&mapped, rec.handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); good = false; break; }
+      c->opened[r].push_back(PeerMapping{rec.handle, mapped});
+    }
+    out[r] = reinterpret_cast<float*>(static_cast<char*>(mapped) + rec.offset);
+  }
+  // every rank must take the same route: agree on the outcome (a rank that could not map a peer vetoes P2P for all)
+  float flag = good ? 1.0f : 0.0f;
+  GUDA_CUDA(cudaMemcpyAsync(c->dev_scalar, &flag, sizeof(float), cudaMemcpyHostToDevice, s));
+  GUDA_NCCL(g_nccl.AllReduce(c->dev_scalar, c->dev_scalar, 1, ncclFloat, ncclMin, c->comm, s));
+  GUDA_CUDA(cudaMemcpyAsync(&flag, c->dev_scalar, sizeof(float), cudaMemcpyDeviceToHost, s));
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  *all_ok = flag > 0.5f;
+  return GUDA_OK;
+}
 
 // gathered [rank][m_loc][n_loc] blocks -> row-major c_full; 128-bit copies when the geometry allows
 __global__ void unpack_blocks_kernel(const float* __restrict__ staging, float* __restrict__ c_full, long long ldc_full, int pr, int pc,
@@ -112,7 +178,12 @@ int guda_comm_init_rank(guda_comm_t* comm, int nranks, int rank, const uint8_t h
   ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
   if (r != ncclSuccess) { delete c; return set_error(GUDA_ERR_EXECUTION, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(r)); }
   cudaError_t e = cudaMalloc((void**)&c->dev_scalar, 256);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&c->dev_records, sizeof(PeerRecord) * (nranks + 1));
+  if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->host_records, sizeof(PeerRecord) * (nranks + 1), cudaHostAllocDefault);
   if (e != cudaSuccess) { g_nccl.CommDestroy(c->comm); delete c; return set_error(GUDA_ERR_MEMORY, "cudaMalloc: %s", cudaGetErrorString(e)); }
+  c->opened.resize(nranks);
+  if (const char* m = getenv("GUDA_SHARDED_GATHER")) c->gather_mode = (strcmp(m, "nccl") == 0) ? GUDA_GATHER_NCCL : GUDA_GATHER_P2P;
+  if (nranks > GUDA_MAX_SCATTER_RANKS) c->gather_mode = GUDA_GATHER_NCCL;
   *comm = reinterpret_cast<guda_comm_t>(c);
   return GUDA_OK;
 }
@@ -123,7 +194,11 @@ int guda_comm_destroy(guda_comm_t comm) {
   if (rc) return rc;
   Comm* c = reinterpret_cast<Comm*>(comm);
   cudaDeviceSynchronize();
+  for (auto& per_rank : c->opened)
+    for (PeerMapping& pm : per_rank) cudaIpcCloseMemHandle(pm.base);
   g_nccl.CommDestroy(c->comm);
+  if (c->dev_records) cudaFree(c->dev_records);
+  if (c->host_records) cudaFreeHost(c->host_records);
   if (c->staging) cudaFree(c->staging);
   if (c->dev_scalar) cudaFree(c->dev_scalar);
   delete c;
@@ -140,12 +215,32 @@ int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_tota
   if (m_total % pr || n_total % pc) return set_error(GUDA_ERR_INVALID_ARG, "m (n) must divide evenly over the process grid");
   const int m_loc = m_total / pr, n_loc = n_total / pc;
   if (ldc_block != n_loc) return set_error(GUDA_ERR_INVALID_ARG, "c_block must be packed (ldc_block == n/pc) for the all-gather");
-  // local block: full K, identical per-element k-order to the 1-GPU kernel -> bit-identical results
-  int rc = guda_sgemm(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, stream);
+  int rc = bind_device();
+  if (rc) return rc;
+  cudaStream_t s = native(stream);
+  if (c_full && ldc_full < n_total) GUDA_PANIC("blas: bad leading dimension of C");
+  // ---- fused route: ONE kernel computes the block (full K locally: the same per-element k-order as on one GPU, so the
+  // bits are identical) and its epilogue stores every finished tile into every rank's c_full over NVLink ----
+  if (c_full && c->gather_mode == GUDA_GATHER_P2P && !c->p2p_failed && sgemm_mode() == GUDA_SGEMM_EXACT) {
+    float* peers[GUDA_MAX_SCATTER_RANKS];
+    bool ok = false;
+    if ((rc = resolve_peers(c, c_full, s, peers, &ok))) return rc;
+    if (ok) {
+      const int r = c->rank / pc, q = c->rank % pc;
+      rc = guda_sgemm_scatter(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, peers, c->nranks,
+                              ldc_full, r * m_loc, q * n_loc, stream);
+      if (rc) return rc;
+      // exit barrier: the one-float all-reduce completes on this stream only after every rank's kernel has finished
+      // storing into this rank's c_full
+      GUDA_NCCL(g_nccl.AllReduce(c->dev_scalar, c->dev_scalar, 1, ncclFloat, ncclSum, c->comm, s));
+      return GUDA_OK;
+    }
+    c->p2p_failed = true;                  // agreed by all ranks (resolve_peers reduces the flag): use NCCL from now on
+  }
+  // ---- NCCL route: local block, then all-gather ----
+  rc = guda_sgemm(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, stream);
   if (rc) return rc;
   if (!c_full) return GUDA_OK;             // caller only wants its block
-  if (ldc_full < n_total) GUDA_PANIC("blas: bad leading dimension of C");
-  cudaStream_t s = native(stream);
   const size_t per_block = (size_t)m_loc * n_loc;
   if (pc == 1 && ldc_full == n_total) {
     // row panels are contiguous in c_full: gather straight into place
@@ -163,6 +258,18 @@ int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_tota
   GUDA_NCCL(g_nccl.AllGather(c_block, c->staging, per_block, ncclFloat, c->comm, s));
   unpack_blocks_kernel<<<sm_count() * 8, 256, 0, s>>>(c->staging, c_full, ldc_full, pr, pc, m_loc, n_loc);
   return check_launch("unpack_blocks");
+}
+
+int guda_comm_set_gather_mode(guda_comm_t comm, int mode) {
+  if (!comm || (mode != GUDA_GATHER_P2P && mode != GUDA_GATHER_NCCL)) return set_error(GUDA_ERR_INVALID_ARG, "comm_set_gather_mode: bad arguments");
+  reinterpret_cast<Comm*>(comm)->gather_mode = mode;
+  return GUDA_OK;
+}
+int guda_comm_get_gather_mode(guda_comm_t comm, int* mode_in_effect) {
+  if (!comm || !mode_in_effect) return set_error(GUDA_ERR_INVALID_ARG, "comm_get_gather_mode: bad arguments");
+  Comm* c = reinterpret_cast<Comm*>(comm);
+  *mode_in_effect = (c->gather_mode == GUDA_GATHER_P2P && !c->p2p_failed) ? GUDA_GATHER_P2P : GUDA_GATHER_NCCL;
+  return GUDA_OK;
 }
 
 int guda_sdot_sharded(guda_comm_t comm, int n_local, const float* x, const float* y, float* host_result, guda_stream_t stream) {

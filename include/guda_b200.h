@@ -121,6 +121,12 @@ int guda_dgemm(int trans_a, int trans_b, int m, int n, int k, double alpha, cons
 enum { GUDA_DGEMM_TENSOR = 0, GUDA_DGEMM_SIMT = 1 };
 int guda_set_dgemm_mode(int mode);
 int guda_get_dgemm_mode(int* mode);
+/* SGEMM (exact route) whose epilogue stores the finished m x n block to c (may be NULL when beta == 0) AND at (row0, col0)
+ * of each of the ndest <= 8 row-major matrices host_dests[i] (leading dimension ld_dest).  The destinations may be peer-GPU
+ * memory mapped through CUDA IPC: this is the kernel behind the fused GEMM + all-gather of guda_sgemm_sharded. */
+int guda_sgemm_scatter(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
+                       float beta, float* c, int ldc, float* const* host_dests, int ndest, int ld_dest, int row0, int col0,
+                       guda_stream_t stream);
 /* bfloat16.go:104 GEMMBFloat16 (trans flags ignored by the reference -> must be 0 here), float16.go:201 GEMMFloat16.
  * 16-bit storage, fp32 accumulation; a/b/c are uint16 bit patterns. */
 int guda_gemm_bf16(int trans_a, int trans_b, int m, int n, int k, float alpha, const uint16_t* a, int lda,
@@ -181,6 +187,12 @@ int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_tota
                        const float* a_panel, int lda, const float* b_panel, int ldb, float* c_block, int ldc_block,
                        float* c_full, int ldc_full, guda_stream_t stream);
 /* per-GPU partial dot products combined by ncclAllReduce(sum) */
+/* how guda_sgemm_sharded gathers C: P2P (default) = ONE kernel, the GEMM epilogue stores each finished tile straight into every
+ * rank's c_full through NVLink-mapped peer pointers (CUDA IPC), no staging copy, no unpack pass; NCCL = local GEMM, then
+ * ncclAllGather (+ unpack).  If peer mapping is unavailable on every rank's agreement the call falls back to NCCL. */
+enum { GUDA_GATHER_P2P = 0, GUDA_GATHER_NCCL = 1 };
+int guda_comm_set_gather_mode(guda_comm_t comm, int mode);
+int guda_comm_get_gather_mode(guda_comm_t comm, int* mode_in_effect);
 int guda_sdot_sharded(guda_comm_t comm, int n_local, const float* x, const float* y, float* host_result, guda_stream_t stream);
 
 #ifdef __cplusplus

@@ -135,3 +135,20 @@ def test_dgemm_2048_sampled_and_modes_identical(g, O):
     sub_a = np.ascontiguousarray(a.reshape(n, n)[rows, :]).ravel()
     want = O.dgemm(0, 0, len(rows), n, n, 1.0, sub_a, n, b, n, 0.0, _aligned_copy(np.zeros(len(rows) * n)), n)
     assert np.array_equal(tensor.reshape(n, n)[rows, :].ravel(), want)
+
+
+def test_dgemm_k_blocked_launches_same_bits(g, O):
+    """K >= 4096 with a large C is run as K-blocked launches (L2 residency): resuming the chain from the stored fp64
+    accumulator must not change a bit.  Oracle on a row subset; tensor vs SIMT on everything."""
+    m = n = 2048
+    k = 4100
+    a = O.uniform_f64(m * k, 61); b = O.uniform_f64(k * n, 62); c0 = O.uniform_f64(m * n, 63)
+    tensor = _gpu_dgemm(g, 0, 0, 0, m, n, k, 1.0, a, k, b, n, 0.5, c0, n)
+    simt = _gpu_dgemm(g, 1, 0, 0, m, n, k, 1.0, a, k, b, n, 0.5, c0, n)
+    assert np.array_equal(tensor, simt)
+    rows = [0, 4, 1023, 2044]                      # whole 4-row groups so that dgemm_fixed.go's 4x4 tiling applies
+    rows = [r + d for r in rows for d in range(4)]
+    sub_a = np.ascontiguousarray(a.reshape(m, k)[rows, :]).ravel()
+    sub_c = np.ascontiguousarray(c0.reshape(m, n)[rows, :]).ravel()
+    want = O.dgemm(0, 0, len(rows), n, k, 1.0, sub_a, k, b, n, 0.5, _aligned_copy(sub_c), n)
+    assert np.array_equal(tensor.reshape(m, n)[rows, :].ravel(), want)

@@ -299,3 +299,52 @@ def test_gemm_f16_exact_route_bit_exact(g, O, m, n, k):
         g.Free(da); g.Free(db); g.Free(dc)
     finally:
         g.SetGemm16Mode(0)
+
+
+# ------------------------------------------------------------------ K-blocked launches, fused all-gather building block
+def test_sgemm_k_blocked_launches_bit_exact(g, O):
+    """K >= 8192 with a large C runs as 2048-deep launches that resume the chain from the stored fp32 accumulator
+    (gemm.cu launch_simt): the bits must equal the oracle's single chain."""
+    m, n, k = 2048, 2048, 8200
+    a = O.uniform_f32(m * k, 71); b = O.uniform_f32(k * n, 72); c0 = O.uniform_f32(m * n, 73)
+    got = _run_sgemm(g, 0, 0, m, n, k, 1.5, a, k, b, n, 0.5, c0, n)
+    want = O.sgemm(0, 0, m, n, k, 1.5, a, k, b, n, 0.5, c0.copy(), n, threads=16)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("pr,pc,m,n,k", [(2, 2, 256, 384, 100), (1, 2, 128, 520, 64), (2, 4, 512, 1024, 33)])
+def test_sgemm_scatter_places_blocks_like_an_all_gather(g, O, pr, pc, m, n, k):
+    """guda_sgemm_scatter is the kernel behind the fused GEMM + all-gather: every emulated rank computes its block and its
+    epilogue stores it into EVERY rank's gathered matrix.  With the ranks emulated on one GPU (one call per rank, P
+    destination buffers) each buffer must end up equal to the single-GPU product, bit for bit."""
+    import ctypes as C
+    from guda_b200 import sharding
+    L = g.load()
+    world = pr * pc
+    a = O.uniform_f32(m * k, 81); b = O.uniform_f32(k * n, 82)
+    da, db = g.to_device(a), g.to_device(b)
+    fulls = [g.Malloc(m * n * 4) for _ in range(world)]
+    for f in fulls:
+        g.Memset(f, 0xFF, m * n * 4)
+    dests = (C.c_void_p * world)(*[f.ptr for f in fulls])
+    blocks = []
+    for rank in range(world):
+        r0, rows, c0, cols = sharding.block_extents(rank, pr, pc, m, n)
+        blk = g.Malloc(rows * cols * 4)
+        blocks.append((blk, r0, rows, c0, cols))
+        g.capi.check(L.guda_sgemm_scatter(0, 0, rows, cols, k, 1.25, da.ptr + r0 * k * 4, k, db.ptr + c0 * 4, n, 0.0, blk.ptr, cols,
+                                          dests, world, n, r0, c0, None), "SgemmScatter")
+    g.Synchronize()
+    want = O.sgemm(0, 0, m, n, k, 1.25, a, k, b, n, 0.0, np.zeros(m * n, np.float32), n)
+    for f in fulls:
+        assert np.array_equal(f.Float32(), want)
+    for blk, r0, rows, c0, cols in blocks:
+        assert np.array_equal(blk.Float32().reshape(rows, cols), want.reshape(m, n)[r0:r0 + rows, c0:c0 + cols])
+    # c may be NULL when only the gathered copies are wanted
+    g.Memset(fulls[0], 0, m * n * 4)
+    one = (C.c_void_p * 1)(fulls[0].ptr)
+    g.capi.check(L.guda_sgemm_scatter(0, 0, m, n, k, 1.25, da.ptr, k, db.ptr, n, 0.0, None, n, one, 1, n, 0, 0, None), "SgemmScatter")
+    g.Synchronize()
+    assert np.array_equal(fulls[0].Float32(), want)
+    for p in [da, db] + fulls + [b_[0] for b_ in blocks]:
+        g.Free(p)

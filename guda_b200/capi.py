@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libguda_b200.so")
+# GUDA_B200_LIB: load another build of the same library (A/B timing of kernel variants); the default is the in-tree build
+LIB_PATH = os.environ.get("GUDA_B200_LIB") or os.path.join(_HERE, "lib", "libguda_b200.so")
 
 OK, ERR_MEMORY, ERR_INVALID_ARG, ERR_EXECUTION, ERR_NUMERICAL, ERR_DEVICE, ERR_NOT_IMPLEMENTED = range(7)
 ERROR_TYPE_NAMES = {1: "Memory", 2: "InvalidArgument", 3: "Execution", 4: "Numerical", 5: "Device", 6: "NotImplemented"}
@@ -107,6 +108,8 @@ def load():
                               "(nvcc, sm_100a). There is no CPU fallback." % LIB_PATH)
         lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
         for name, (res, args) in SIGNATURES.items():
+            if not hasattr(lib, name) and os.environ.get("GUDA_B200_LIB_PARTIAL") == "1":
+                continue                     # A/B timing against an older build of the library (scratch/build_variant.sh)
             fn = getattr(lib, name)          # AttributeError if the header and the library disagree
             fn.restype, fn.argtypes = res, args
         _lib = lib

@@ -267,8 +267,8 @@ int dgemm_dmma_try(int ta, int tb, int m, int n, int k, double alpha, const doub
   if (((uintptr_t)a & 15) || ((uintptr_t)b & 15) || (lda & 1) || (ldb & 1)) return -1;
   if ((long long)((m + dmma::BM - 1) / dmma::BM) * ((n + dmma::BN - 1) / dmma::BN) > 0x7fffffffLL) return -1;
   // K blocking across launches keeps the co-resident CTAs' panels inside L2 (same bits: see launch_simt in gemm.cu)
-  constexpr int KC = 1024;
-  if (k >= 4 * KC && (long long)m * n >= (1ll << 22)) {
+  constexpr int KC = 4096;
+  if (k >= 2 * KC && (long long)m * n >= (1ll << 22)) {
     for (int k0 = 0; k0 < k; k0 += KC) {
       const int kc = (k0 + KC >= k) ? k - k0 : KC;
       int rc = dgemm_dmma_one(ta, m, n, kc, alpha, ta ? a + (long long)k0 * lda : a + k0, lda, b + (long long)k0 * ldb, ldb,

@@ -61,8 +61,8 @@ template <typename T> struct TileCfg;
 template <> struct TileCfg<float>  { static constexpr int BK = 16, MINB_BIG = 2, MINB_SMALL = 3; };
 template <> struct TileCfg<double> { static constexpr int BK = 8,  MINB_BIG = 1, MINB_SMALL = 2; };
 
-template <typename T, bool TA, bool TB, int MODE, int EPI, int BM, int BN, int MINB>
-static int launch_simt_tile(const GemmParams<T>& p, cudaStream_t s) {
+template <typename T, bool TA, bool TB, int MODE, int EPI, int BM, int BN, int MINB, bool SCAT = false>
+static int launch_simt_tile(const GemmParams<T>& p, cudaStream_t s, const ScatterParams<T, SCAT>& sp) {
   constexpr int BK = TileCfg<T>::BK;
   constexpr int VN = GemmVec<T>::N;
   auto aligned = [&](const void* ptr, long long ld) { return ((uintptr_t)ptr % 16 == 0) && (ld % VN == 0); };
@@ -70,8 +70,8 @@ static int launch_simt_tile(const GemmParams<T>& p, cudaStream_t s) {
                     aligned(p.c, p.ldc) && p.edge_m >= p.m && p.edge_n >= p.n;
   dim3 grid((p.n + BN - 1) / BN, (p.m + BM - 1) / BM);
   if (grid.y > 65535) return set_error(GUDA_ERR_INVALID_ARG, "m too large for one launch");
-  if (fast) gemm_simt_kernel<T, TA, TB, BM, BN, BK, MODE, EPI, true, MINB><<<grid, 256, 0, s>>>(p);
-  else      gemm_simt_kernel<T, TA, TB, BM, BN, BK, MODE, EPI, false, MINB><<<grid, 256, 0, s>>>(p);
+  if (fast) gemm_simt_kernel<T, TA, TB, BM, BN, BK, MODE, EPI, true, MINB, SCAT><<<grid, 256, 0, s>>>(p, sp);
+  else      gemm_simt_kernel<T, TA, TB, BM, BN, BK, MODE, EPI, false, MINB, SCAT><<<grid, 256, 0, s>>>(p, sp);
   return check_launch("gemm");
 }
 
@@ -79,19 +79,19 @@ static int launch_simt_tile(const GemmParams<T>& p, cudaStream_t s) {
 // the only freedom is the CTA tile.  Pick the shape with the smallest estimated makespan
 //   ceil(tiles / SMs) * BM*BN / efficiency      (efficiency = FFMA share of the inner loop, measured: 8x8 micro-tile 1.0,
 //   8x4 0.85, 4x4 0.6), which sends 1024^3 (64 big tiles on 148 SMs) to 128x64 and anything large to 128x128.
-template <typename T, bool TA, bool TB, int MODE, int EPI>
-static int launch_simt_one(const GemmParams<T>& p, cudaStream_t s) {
+template <typename T, bool TA, bool TB, int MODE, int EPI, bool SCAT = false>
+static int launch_simt_one(const GemmParams<T>& p, cudaStream_t s, const ScatterParams<T, SCAT>& sp = {}) {
   const long long sms = sm_count();
   auto makespan = [&](int bm, int bn, double eff) {
     const long long tiles = (long long)((p.m + bm - 1) / bm) * ((p.n + bn - 1) / bn);
     return (double)((tiles + sms - 1) / sms) * bm * bn / eff;
   };
   const double t_big = makespan(128, 128, 1.0), t_mid = makespan(128, 64, 0.85), t_small = makespan(64, 64, 0.6);
-  if (t_big <= t_mid && t_big <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 128, TileCfg<T>::MINB_BIG>(p, s);
+  if (t_big <= t_mid && t_big <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 128, TileCfg<T>::MINB_BIG, SCAT>(p, s, sp);
   if constexpr (sizeof(T) == 4) {
-    if (t_mid <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 64, 2>(p, s);
+    if (t_mid <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 64, 2, SCAT>(p, s, sp);
   }
-  return launch_simt_tile<T, TA, TB, MODE, EPI, 64, 64, TileCfg<T>::MINB_SMALL>(p, s);
+  return launch_simt_tile<T, TA, TB, MODE, EPI, 64, 64, TileCfg<T>::MINB_SMALL, SCAT>(p, s, sp);
 }
 
 // K blocking across launches.  A C element is one sequential-k chain held in an fp32 (fp64) accumulator, so stopping the
@@ -99,14 +99,16 @@ static int launch_simt_one(const GemmParams<T>& p, cudaStream_t s) {
 // 64-deep k blocks this way, compute/sgemm.go:236-260).  With K far beyond what L2 can hold, the ~300 co-resident CTAs
 // drift apart in k and stop sharing A/B panels: ncu measured 11.4 TB of DRAM reads for one 65536^3 launch (L2 hit 35 %).
 // Chunks of KC keep the resident set -- (16 + ~18) tile panels x KC -- inside L2.
-template <typename T> struct KChunk { static constexpr int KC = sizeof(T) == 4 ? 2048 : 1024; };
+// KC = 8192 (fp32): a launch boundary is a grid-wide barrier, so the drift is bounded by one chunk while the extra C
+// round trip (2 x |C| per chunk) and the pipeline refill stay near 1 % of the work (KC = 2048 cut traffic to 1.7 TB but cost 5 %).
+template <typename T> struct KChunk { static constexpr int KC = sizeof(T) == 4 ? 8192 : 4096; };
 
-template <typename T, bool TA, bool TB, int MODE, int EPI>
-static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
+template <typename T, bool TA, bool TB, int MODE, int EPI, bool SCAT = false>
+static int launch_simt(const GemmParams<T>& p, cudaStream_t s, const ScatterParams<T, SCAT>& sp = {}) {
   constexpr int KC = KChunk<T>::KC;
-  const bool chunk = EPI == EPI_NONE && p.c != nullptr && p.k >= 4 * KC && (long long)p.m * p.n >= (1ll << 22) &&
+  const bool chunk = EPI == EPI_NONE && p.c != nullptr && p.k >= 2 * KC && (long long)p.m * p.n >= (1ll << 22) &&
                      p.edge_m >= p.m && p.edge_n >= p.n;
-  if (!chunk) return launch_simt_one<T, TA, TB, MODE, EPI>(p, s);
+  if (!chunk) return launch_simt_one<T, TA, TB, MODE, EPI, SCAT>(p, s, sp);
   GemmParams<T> q = p;
   for (int k0 = 0; k0 < p.k; k0 += KC) {
     const bool last = k0 + KC >= p.k;
@@ -114,8 +116,7 @@ static int launch_simt(const GemmParams<T>& p, cudaStream_t s) {
     q.a = TA ? p.a + (long long)k0 * p.lda : p.a + k0;
     q.b = TB ? p.b + k0 : p.b + (long long)k0 * p.ldb;
     q.beta = k0 == 0 ? p.beta : T(1);
-    q.nscatter = last ? p.nscatter : 0;
-    int rc = launch_simt_one<T, TA, TB, MODE, EPI>(q, s);
+    int rc = (SCAT && last) ? launch_simt_one<T, TA, TB, MODE, EPI, SCAT>(q, s, sp) : launch_simt_one<T, TA, TB, MODE, EPI, false>(q, s);
     if (rc) return rc;
   }
   return GUDA_OK;
@@ -166,10 +167,12 @@ static int sgemm_impl(int ta, int tb, int m, int n, int k, float alpha, const fl
   }
   GemmParams<float> p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, bias, m, n};
   if (scatter) {
-    if ((alpha == 0.0f || k == 0) && beta == 1.0f && !c) return GUDA_OK;
-    p.nscatter = scatter->n;
-    for (int i = 0; i < scatter->n; i++) p.scatter[i] = scatter->dst[i];
-    p.scatter_ld = scatter->ld; p.scatter_off = scatter->off;
+    if (ta || tb) return set_error(GUDA_ERR_NOT_IMPLEMENTED, "sgemm_scatter: only the NN form is implemented");
+    ScatterParams<float, true> sp;
+    sp.n = scatter->n;
+    for (int i = 0; i < GUDA_MAX_SCATTER; i++) sp.dst[i] = i < scatter->n ? scatter->dst[i] : nullptr;
+    sp.ld = scatter->ld; sp.off = scatter->off;
+    return launch_simt<float, false, false, MODE_FMA, EPI_NONE, true>(p, s, sp);
   }
   if (epi == EPI_BIAS_RELU) return launch_simt<float, false, false, MODE_FMA, EPI_BIAS_RELU>(p, s);
   if (epi == EPI_BIAS_GELU) return launch_simt<float, false, false, MODE_FMA, EPI_BIAS_GELU>(p, s);

@@ -19,6 +19,7 @@
 // and fused_gelu.go:107-125).
 #pragma once
 #include "common.cuh"
+#include <type_traits>
 
 namespace guda {
 
@@ -109,11 +110,17 @@ struct GemmParams {
   T* c; long long ldc;
   const T* bias;
   int edge_m, edge_n;      // elements with i >= edge_m or j >= edge_n are NOT stored (fp64 NN alpha==1 edges)
-  // fused all-gather (sharded.cu): besides c, the finished tile is stored at (row, col) + scatter_off of every matrix in
-  // scatter[] -- the gathered C of each rank, peers reached through NVLink-mapped (CUDA IPC) pointers.  c may be null.
-  int nscatter;
-  T* scatter[GUDA_MAX_SCATTER];
-  long long scatter_ld, scatter_off;
+};
+
+// fused all-gather (sharded.cu): besides c, the finished tile is stored at (row, col) + off of every matrix in dst[] -- the
+// gathered C of each rank, peers reached through NVLink-mapped (CUDA IPC) pointers; c may then be null.  A separate kernel
+// parameter (empty for the ordinary kernels) so that the hot kernels' parameter block and code are untouched: ptxas'
+// schedule of the main loop proved sensitive to it (57.4 -> 54.6 TFLOP/s at 8192^3 when these fields lived in GemmParams).
+template <typename T, bool SCAT> struct ScatterParams {};
+template <typename T> struct ScatterParams<T, true> {
+  int n;
+  T* dst[GUDA_MAX_SCATTER];
+  long long ld, off;
 };
 
 template <typename T, int BM, int BN, int BK>
@@ -198,8 +205,8 @@ __device__ __forceinline__ void load_frag(T* dst, const T* src) {
   }
 }
 
-template <typename T, bool TA, bool TB, int BM, int BN, int BK, int MODE, int EPI, bool FAST, int MINB>
-__global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p) {
+template <typename T, bool TA, bool TB, int BM, int BN, int BK, int MODE, int EPI, bool FAST, int MINB, bool SCAT = false>
+__global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p, ScatterParams<T, SCAT> sp) {
   constexpr int TM = BM / 16, TN = BN / 16;       // micro-tile
   constexpr int HM = TM / 2, HN = TN / 2;         // halves, BM/2 (BN/2) apart
   using Smem = GemmSmem<T, BM, BN, BK>;
@@ -339,7 +346,7 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p) {
         out[j] = apply_epilogue<T, EPI>(acc[i][jh * HN + j], bias);
       }
       int lim = p.n < p.edge_n ? p.n : p.edge_n;
-      if (p.c) {
+      if (!SCAT || p.c) {
         T* dst = p.c + (long long)row * p.ldc + col0;
         if (FAST && HN % VN == 0) {
 #pragma unroll
@@ -349,11 +356,11 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p) {
           for (int j = 0; j < HN; j++) if (col0 + j < lim) dst[j] = out[j];
         }
       }
-      if (p.nscatter) {
-        const bool vec = (HN % VN == 0) && (p.scatter_ld % VN == 0) && (p.scatter_off % VN == 0) && (col0 + HN <= lim);
-        for (int s = 0; s < p.nscatter; s++) {
-          T* dst = p.scatter[s] + (long long)row * p.scatter_ld + p.scatter_off + col0;
-          if (vec && (reinterpret_cast<uintptr_t>(p.scatter[s]) & 15) == 0) {
+      if constexpr (SCAT) {
+        const bool vec = (HN % VN == 0) && (sp.ld % VN == 0) && (sp.off % VN == 0) && (col0 + HN <= lim);
+        for (int s = 0; s < sp.n; s++) {
+          T* dst = sp.dst[s] + (long long)row * sp.ld + sp.off + col0;
+          if (vec && (reinterpret_cast<uintptr_t>(sp.dst[s]) & 15) == 0) {
 #pragma unroll
             for (int j = 0; j < HN; j += VN) *reinterpret_cast<V*>(dst + j) = *reinterpret_cast<V*>(out + j);
           } else {

@@ -138,10 +138,10 @@ def test_dgemm_2048_sampled_and_modes_identical(g, O):
 
 
 def test_dgemm_k_blocked_launches_same_bits(g, O):
-    """K >= 4096 with a large C is run as K-blocked launches (L2 residency): resuming the chain from the stored fp64
+    """K >= 8192 with a large C is run as 4096-deep K-blocked launches (L2 residency): resuming the chain from the stored fp64
     accumulator must not change a bit.  Oracle on a row subset; tensor vs SIMT on everything."""
     m = n = 2048
-    k = 4100
+    k = 8200
     a = O.uniform_f64(m * k, 61); b = O.uniform_f64(k * n, 62); c0 = O.uniform_f64(m * n, 63)
     tensor = _gpu_dgemm(g, 0, 0, 0, m, n, k, 1.0, a, k, b, n, 0.5, c0, n)
     simt = _gpu_dgemm(g, 1, 0, 0, m, n, k, 1.0, a, k, b, n, 0.5, c0, n)

@@ -303,9 +303,9 @@ def test_gemm_f16_exact_route_bit_exact(g, O, m, n, k):
 
 # ------------------------------------------------------------------ K-blocked launches, fused all-gather building block
 def test_sgemm_k_blocked_launches_bit_exact(g, O):
-    """K >= 8192 with a large C runs as 2048-deep launches that resume the chain from the stored fp32 accumulator
+    """K >= 16384 with a large C runs as 8192-deep launches that resume the chain from the stored fp32 accumulator
     (gemm.cu launch_simt): the bits must equal the oracle's single chain."""
-    m, n, k = 2048, 2048, 8200
+    m, n, k = 2048, 2048, 16500
     a = O.uniform_f32(m * k, 71); b = O.uniform_f32(k * n, 72); c0 = O.uniform_f32(m * n, 73)
     got = _run_sgemm(g, 0, 0, m, n, k, 1.5, a, k, b, n, 0.5, c0, n)
     want = O.sgemm(0, 0, m, n, k, 1.5, a, k, b, n, 0.5, c0.copy(), n, threads=16)

@@ -486,15 +486,22 @@ def main():
         cpu = {"value": tf, "unit": "TFLOP/s", "cores": cores, "kind": "port",
                "sample": "SGEMM %d^3 fp32 (bounded sample of the %d^3 headline), oracle port of compute/sgemm.go (AVX2+FMA route, "
                          "one task per 64x64 C block), %.2f s per pass" % (CPU_SAMPLE_N, n, dt)}
+    gather = None
     if comm is not None:
+        eff = C.c_int(-1)
+        L.guda_comm_get_gather_mode(comm, C.byref(eff))
+        gather = {0: "fused: GEMM epilogue stores tiles into every rank's C over NVLink peer pointers (CUDA IPC), one kernel",
+                  1: "local GEMM, then ncclAllGather (+ unpack kernel)"}.get(eff.value, "?")
         barrier()
         L.guda_comm_destroy(comm)
     if rank == 0:
-        launches = args.steps * (1 if world == 1 else (1 if pc == 1 else 2))
+        # exact mode: K >= 16384 runs as 8192-deep launches resuming the same fp32 chains (gemm.cu launch_simt)
+        kchunks = (n + 8191) // 8192 if (args.mode == "exact" and n >= 16384) else 1
+        launches = args.steps * (kchunks + (0 if (world == 1 or gather.startswith("fused") or pc == 1) else 1))
         line = {"metric": "sgemm_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "SGEMM %d^3 fp32 NN alpha=1 beta=0 (BASELINE configs[4]); %dx%d block partition%s" % (
-                               n, pr, pc, ", C all-gathered over NCCL/NVLink inside the step" if world > 1 else ""),
+                               n, pr, pc, ", C gathered on every rank inside the step (%s)" % gather if world > 1 else ""),
                            "math": "exact fp32 SIMT, reference k-order (bit-exact vs oracle)" if args.mode == "exact" else "3xTF32 tcgen05",
                            "l2": "operands %.1f GiB per rank, far larger than the 126 MB L2" % ((m_loc * n + n * n_loc) * 4 / 2 ** 30)},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

@@ -96,8 +96,27 @@ def full(rep_path, out_path, pairs):
     json.dump(traffic, open(traffic_path, "w"), indent=1, sort_keys=True)
 
 
+def traffic(csv_path, key, steps):
+    """Sum dram read+write bytes over every launch in an `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --csv`
+    log that covers `steps` steps of the hot path; stores bytes per step under `key` in profiles/traffic.json."""
+    rows = [r for r in csv.reader(open(csv_path)) if len(r) > 10 and r[0].isdigit()]
+    total = sum(float(r[-1].replace(",", "")) for r in rows if r[-3].startswith("dram__bytes_"))
+    n_launch = len({r[0] for r in rows})
+    path = os.path.join(HERE, "traffic.json")
+    try:
+        t = json.load(open(path))
+    except Exception:
+        t = {}
+    t[key] = total / steps
+    t[key + "_launches_per_step"] = n_launch / steps
+    json.dump(t, open(path, "w"), indent=1, sort_keys=True)
+    print(key, "%.4g bytes per step over %d launches" % (total / steps, n_launch / steps))
+
+
 if __name__ == "__main__":
-    if sys.argv[1] == "launches":
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3], int(sys.argv[4]) if len(sys.argv) > 4 else 1)
+    elif sys.argv[1] == "launches":
         launches(sys.argv[2], sys.argv[3])
     else:
         full(sys.argv[2], sys.argv[3], sys.argv[4:])

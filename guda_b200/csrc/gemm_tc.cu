@@ -336,6 +336,151 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, Cfg::TMEM_COLS); }
 }
 
+// ---------------------------------------------------------------- CTA-pair (cta_group::2) variant, 16-bit operands
+// One cluster of two CTAs (two SMs of a TPC) owns a 256 x 256 tile of C: tcgen05.mma.cta_group::2 with M = 256, N = 256.
+// Each CTA stages its own 128 rows of A and HALF of the B tile (128 columns); the pair's tensor cores read both halves of B,
+// so per SM and per 16-deep MMA step shared memory sees 8 KB of TMA writes + 8 KB of operand reads instead of 12 + 12 KB --
+// the single-CTA kernel was shared-memory-bandwidth bound (tensor pipe 74 % active, ncu profiles/r01).
+// Roles per CTA: warp 0 TMA producer (bytes counted on the LEADER's full barrier), warp 1 MMA issuer (leader CTA only; its
+// tcgen05.commit is multicast to both CTAs' empty / tmem_full barriers), warps 2..5 epilogue on the CTA's own 128 TMEM lanes
+// (the non-leader's epilogue warps release the accumulator stage on the leader's tmem_empty barrier).
+struct TcPairCfg {
+  static constexpr int BM = 128, BN = 256, BN_HALF = 128, BK = 64, UMMA_K = 16;
+  static constexpr int A_TILE = BM * 128;                 // bytes: 128 rows x 128 B
+  static constexpr int B_BOX = BK * 128;                  // 64 k-rows x 128 B (64 columns)
+  static constexpr int B_TILE = (BN_HALF / 64) * B_BOX;   // this CTA's half of B
+  static constexpr int STAGE = A_TILE + B_TILE;           // 32 KB
+  static constexpr int STAGES = 6;
+  static constexpr int ACC_STAGES = 2;
+  static constexpr int TMEM_COLS = ACC_STAGES * BN;       // 512
+  static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
+};
+
+template <int OUT, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
+gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, TcParams p) {
+  using Cfg = TcPairCfg;
+  constexpr int BM = Cfg::BM, BN = Cfg::BN, BK = Cfg::BK, STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + Cfg::ACC_STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + Cfg::ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();                 // 0 = leader
+  const int num_tiles = p.tiles_m * p.tiles_n;             // tiles_m counts 256-row blocks
+  const int kblocks = (p.k + BK - 1) / BK;
+  const int first_tile = (int)cluster_id_x(), tile_step = (int)cluster_count_x();
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_a); prefetch_tmap(&map_b);
+    for (int s = 0; s < STAGES; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < Cfg::ACC_STAGES; s++) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 8); }
+    fence_barrier_init();
+  }
+  if (warp == 1) { tmem_alloc_pair(tmem_ptr, Cfg::TMEM_COLS); tmem_relinquish_pair(); }
+  tc_fence_before();
+  cluster_sync_all();                                      // barriers of both CTAs initialised before any remote arrive
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  auto tile_coord = [&](int t, int& tm, int& tn) {
+    const int group = 4;                                   // 4 x 256 rows
+    int per_group = group * p.tiles_n;
+    int g = t / per_group, r = t % per_group;
+    int rows = min(group, p.tiles_m - g * group);
+    tm = g * group + r % rows;
+    tn = r / rows;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = first_tile; t < num_tiles; t += tile_step) {
+        int tm, tn; tile_coord(t, tm, tn);
+        const int row0 = tm * 2 * BM + (int)rank * BM;
+        const int col0 = tn * BN + (int)rank * Cfg::BN_HALF;
+        for (int kb = 0; kb < kblocks; kb++) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* st = smem + stage * Cfg::STAGE;
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE);     // both CTAs' bytes land on the leader's barrier
+          tma_load_2d_pair(st, &map_a, &full_bar[stage], kb * BK, row0);
+          tma_load_2d_pair(st + Cfg::A_TILE, &map_b, &full_bar[stage], col0, kb * BK);
+          tma_load_2d_pair(st + Cfg::A_TILE + Cfg::B_BOX, &map_b, &full_bar[stage], col0 + 64, kb * BK);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc(OUT == OUT_F16 ? 0u : 1u, /*a K-major*/ 0u, /*b MN-major*/ 1u, 2 * BM, BN);
+      int stage = 0; uint32_t phase = 0;
+      int ci = 0;
+      for (int t = first_tile; t < num_tiles; t += tile_step, ci++) {
+        const int as = ci & 1; const uint32_t aphase = (ci >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < kblocks; kb++) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(smem + stage * Cfg::STAGE);
+          const uint32_t b0 = a0 + Cfg::A_TILE;
+#pragma unroll
+          for (int ks = 0; ks < BK / Cfg::UMMA_K; ks++) {
+            const uint64_t da = make_smem_desc(a0 + ks * 32, 16, 1024);
+            const uint64_t db = make_smem_desc(b0 + ks * Cfg::UMMA_K * 128, Cfg::B_BOX, 1024, 2u);
+            mma_f16_pair(d_tmem, da, db, idesc, (uint32_t)((kb | ks) != 0));
+          }
+          mma_commit_pair(&empty_bar[stage]);                // the stage is reusable in BOTH CTAs once these MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit_pair(&tmem_full[as]);                     // accumulator complete -> both CTAs' epilogues
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5 of both CTAs; TMEM lane quarter = warp % 4) =====================
+    const int q = warp & 3;
+    int ci = 0;
+    const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+    for (int t = first_tile; t < num_tiles; t += tile_step, ci++) {
+      int tm, tn; tile_coord(t, tm, tn);
+      const int row = tm * 2 * BM + (int)rank * BM + q * 32 + lane;
+      const bool row_ok = row < p.m;
+      const int as = ci & 1;
+      mbar_wait(&tmem_full[as], (ci >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tbase = tlane + (uint32_t)(as * BN);
+      uint32_t r[32];
+      tmem_ld_32x32(tbase, r);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) v[j] = __fmul_rn(p.alpha, __uint_as_float(r[j]));
+        if (c0 + 32 < BN) {
+          tmem_ld_32x32(tbase + (uint32_t)(c0 + 32), r);
+        } else {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_leader(&tmem_empty[as]);
+        }
+        const int col0 = tn * BN + c0;
+        if (row_ok && col0 < p.n) store_chunk<OUT, EPI>(p, v, row, col0);
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();                                      // both CTAs done with TMEM and with each other's barriers
+  if (warp == 1) { tc_fence_after(); tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS); }
+}
+
 // ---------------------------------------------------------------- host side
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 
@@ -394,6 +539,30 @@ static int launch_tc(CUtensorMapDataType dt, int m, int n, int k, float alpha, c
   return check_launch("gemm_tc");
 }
 
+template <int OUT, int EPI>
+static int launch_tc_pair(CUtensorMapDataType dt, int m, int n, int k, float alpha, const void* a, long long lda, const void* b,
+                          long long ldb, float beta, void* c, long long ldc, const float* bias, cudaStream_t s) {
+  using Cfg = TcPairCfg;
+  int rc = get_encode();
+  if (rc) return rc;
+  CUtensorMap ma, mb;
+  if ((rc = make_map(&ma, dt, 2, a, m, k, lda, Cfg::BK, Cfg::BM))) return rc;
+  if ((rc = make_map(&mb, dt, 2, b, k, n, ldb, 64, Cfg::BK))) return rc;
+  TcParams p{m, n, k, alpha, beta, c, ldc, bias, EPI, (m + 2 * Cfg::BM - 1) / (2 * Cfg::BM), (n + Cfg::BN - 1) / Cfg::BN};
+  auto kern = gemm_tc_pair_kernel<OUT, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GUDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    attr_set = true;
+  }
+  int clusters = p.tiles_m * p.tiles_n;
+  if (clusters > sm_count() / 2) clusters = sm_count() / 2;
+  kern<<<2 * clusters, 192, Cfg::SMEM, s>>>(ma, mb, p);      // __cluster_dims__(2,1,1): consecutive CTAs form a pair
+  return check_launch("gemm_tc_pair");
+}
+
+static int g_tc_pair = 1;       // GUDA_TC_PAIR=0 selects the single-CTA kernel (A/B timing)
+
 static bool tma_ok(const void* p, long long ld, int eb) { return ((uintptr_t)p % 16 == 0) && ((ld * eb) % 16 == 0); }
 
 // 16-bit GEMM on tensor cores; -1 = not eligible (caller falls back to the exact route)
@@ -401,6 +570,17 @@ int gemm16_tc_try(int is_bf16, int m, int n, int k, float alpha, const uint16_t*
                   uint16_t* c, int ldc, const float* bias, int epi, cudaStream_t s) {
   if (m < 128 || n < 128 || k < 64) return -1;                // tiny problems: the exact SIMT route is faster and bit-exact
   if (!tma_ok(a, lda, 2) || !tma_ok(b, ldb, 2)) return -1;
+  static bool env_read = false;
+  if (!env_read) { if (const char* e = getenv("GUDA_TC_PAIR")) g_tc_pair = atoi(e); env_read = true; }
+  if (g_tc_pair && m >= 256 && n >= 256) {
+    if (is_bf16) {
+      const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+      if (epi == EPI_BIAS_RELU) return launch_tc_pair<OUT_BF16, EPI_BIAS_RELU>(dt, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, bias, s);
+      if (epi == EPI_BIAS_GELU) return launch_tc_pair<OUT_BF16, EPI_BIAS_GELU>(dt, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, bias, s);
+      return launch_tc_pair<OUT_BF16, EPI_NONE>(dt, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, bias, s);
+    }
+    if (epi == EPI_NONE) return launch_tc_pair<OUT_F16, EPI_NONE>(CU_TENSOR_MAP_DATA_TYPE_FLOAT16, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, bias, s);
+  }
   if (is_bf16) {
     const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     if (epi == EPI_BIAS_RELU) return launch_tc<2, 1, 256, OUT_BF16, EPI_BIAS_RELU>(dt, m, n, k, alpha, a, a, lda, b, b, ldb, beta, c, ldc, bias, s);

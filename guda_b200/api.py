@@ -398,6 +398,32 @@ def FusedGEMMBFloat16BiasReLU(m, n, k, alpha, a, lda, b, ldb, c, ldc, bias, stre
                "FusedGEMMBFloat16BiasReLU")
 
 
+class ConvParams:
+    """conv.go:9-31 ConvParams with the reference's field names."""
+    FIELDS = ("BatchSize", "InChannels", "InHeight", "InWidth", "OutChannels", "KernelHeight", "KernelWidth",
+              "StrideH", "StrideW", "PadH", "PadW", "DilationH", "DilationW", "UseBias")
+
+    def __init__(self, **kw):
+        for f in self.FIELDS:
+            setattr(self, f, kw.get(f, 1 if f.startswith(("Stride", "Dilation")) else 0))
+
+    def OutputHeight(self):                        # conv.go:54-57
+        return (self.InHeight + 2 * self.PadH - ((self.KernelHeight - 1) * self.DilationH + 1)) // self.StrideH + 1
+
+    def OutputWidth(self):                         # conv.go:60-63
+        return (self.InWidth + 2 * self.PadW - ((self.KernelWidth - 1) * self.DilationW + 1)) // self.StrideW + 1
+
+    def _c(self):
+        return capi.ConvParams(*[int(getattr(self, f)) for f in self.FIELDS])
+
+
+def Conv2D(input, kernel, bias, output, params, stream=None):          # conv.go:69
+    """bias may be None / a zero DevicePtr (conv_test.go passes DevicePtr{})."""
+    cp = params._c()
+    bptr = bias.ptr if (bias is not None and bias.ptr) else None
+    capi.check(_L().guda_conv2d(input.ptr, kernel.ptr, bptr, output.ptr, C.byref(cp), _sh(stream)), "Conv2D")
+
+
 def SetSgemmMode(mode):
     capi.check(_L().guda_set_sgemm_mode(mode), "SetSgemmMode")
 

@@ -16,6 +16,12 @@ MEMCPY_H2H, MEMCPY_H2D, MEMCPY_D2H, MEMCPY_D2D, MEMCPY_DEFAULT = range(5)
 COMM_ID_BYTES = 128
 
 
+class ConvParams(C.Structure):
+    """conv.go:9-31 ConvParams, field for field (guda_conv_params_t)."""
+    _fields_ = [(n, C.c_int) for n in ("batch_size", "in_channels", "in_height", "in_width", "out_channels", "kernel_height",
+                                       "kernel_width", "stride_h", "stride_w", "pad_h", "pad_w", "dilation_h", "dilation_w", "use_bias")]
+
+
 class DeviceProps(C.Structure):
     _fields_ = [("id", C.c_int), ("name", C.c_char * 128), ("total_mem", C.c_size_t), ("sm_count", C.c_int),
                 ("max_threads", C.c_int), ("cc_major", C.c_int), ("cc_minor", C.c_int), ("l2_bytes", C.c_int)]
@@ -80,6 +86,7 @@ SIGNATURES = {
     "guda_gemm_bf16_bias_gelu": (i, [i, i, i, f, vp, i, vp, i, vp, i, vp, vp]),
     "guda_add_bias_gelu": (i, [vp, vp, i, i, vp]),
     "guda_add_bias_relu": (i, [vp, vp, i, i, vp]),
+    "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
     "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
     "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),
     "guda_f32_to_f16": (i, [vp, vp, sz, vp]),

@@ -144,4 +144,18 @@ inline void GEMMFloat16(bool transA, bool transB, int m, int n, int k, float alp
   check(guda_gemm_f16(transA, transB, m, n, k, alpha, (const uint16_t*)a.ptr, lda, (const uint16_t*)b.ptr, ldb, beta, (uint16_t*)c.ptr, ldc, nullptr), "GEMMFloat16");
 }
 
+// conv.go:9-31 ConvParams, :69 Conv2D
+struct ConvParams {
+  int BatchSize = 0, InChannels = 0, InHeight = 0, InWidth = 0, OutChannels = 0, KernelHeight = 0, KernelWidth = 0;
+  int StrideH = 1, StrideW = 1, PadH = 0, PadW = 0, DilationH = 1, DilationW = 1;
+  bool UseBias = false;
+  int OutputHeight() const { return (InHeight + 2 * PadH - ((KernelHeight - 1) * DilationH + 1)) / StrideH + 1; }
+  int OutputWidth() const { return (InWidth + 2 * PadW - ((KernelWidth - 1) * DilationW + 1)) / StrideW + 1; }
+};
+inline void Conv2D(const DevicePtr& input, const DevicePtr& kernel, const DevicePtr& bias, const DevicePtr& output, const ConvParams& p) {
+  guda_conv_params_t cp{p.BatchSize, p.InChannels, p.InHeight, p.InWidth, p.OutChannels, p.KernelHeight, p.KernelWidth,
+                        p.StrideH, p.StrideW, p.PadH, p.PadW, p.DilationH, p.DilationW, p.UseBias ? 1 : 0};
+  check(guda_conv2d(f32(input), f32(kernel), f32(bias), f32(output), &cp, nullptr), "Conv2D");
+}
+
 }  // namespace guda

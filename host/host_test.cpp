@@ -85,6 +85,19 @@ int main() {
     EXPECT(pan, "m < 0 must panic with the reference's string");
     Free(da); Free(db); Free(dc); Free(dbias);
   }
+  // ---- conv_test.go:8-76 TestConv2DBasic (3x3 edge detector, pad 1)
+  {
+    ConvParams p; p.BatchSize = 1; p.InChannels = 1; p.InHeight = 4; p.InWidth = 4; p.OutChannels = 1; p.KernelHeight = 3; p.KernelWidth = 3;
+    p.PadH = p.PadW = 1;
+    std::vector<float> in(16), ker{-1, -1, -1, -1, 8, -1, -1, -1, -1};
+    for (int i = 0; i < 16; i++) in[i] = (float)(i + 1);
+    const std::vector<float> expected{-5, -6, -3, 14, 12, 0, 0, 27, 24, 0, 0, 39, 71, 54, 57, 90};
+    DevicePtr di = Malloc(64), dk = Malloc(36), dout = Malloc(64);
+    di.CopyFrom(in); dk.CopyFrom(ker);
+    Conv2D(di, dk, DevicePtr{}, dout, p);
+    EXPECT(dout.Float32() == expected, "Conv2D basic");
+    Free(di); Free(dk); Free(dout);
+  }
   std::printf(failures ? "host_test: %d FAILED\n" : "host_test: all checks passed\n", failures);
   return failures ? 1 : 0;
 }

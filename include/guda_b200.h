@@ -155,6 +155,18 @@ int guda_gemm_bf16_bias_gelu(int m, int n, int k, float alpha, const uint16_t* a
 int guda_add_bias_gelu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
 int guda_add_bias_relu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
 
+/* ---- Conv2D: conv.go:9-31 ConvParams, :69 Conv2D = im2col -> Sgemm -> NCHW placement + bias.
+ * input [B][IC][H][W], kernel [OC][IC][KH][KW], bias [OC] (used when use_bias != 0 and bias != NULL), output [B][OC][OH][OW].
+ * Blocks until done (it owns a pooled workspace, like the reference's `defer Free(workspace)`). */
+typedef struct {
+  int batch_size, in_channels, in_height, in_width;
+  int out_channels, kernel_height, kernel_width;
+  int stride_h, stride_w, pad_h, pad_w, dilation_h, dilation_w;
+  int use_bias;
+} guda_conv_params_t;
+int guda_conv2d(const float* input, const float* kernel, const float* bias, float* output, const guda_conv_params_t* params,
+                guda_stream_t stream);
+
 /* ---- conversions: bfloat16.go:12-29, float16.go:21-87 (device-side bulk convert) ---- */
 int guda_f32_to_bf16(const float* src, uint16_t* dst, size_t n, guda_stream_t stream);
 int guda_bf16_to_f32(const uint16_t* src, float* dst, size_t n, guda_stream_t stream);

@@ -30,7 +30,8 @@ enum {
   ORC_ZERO_INCX = 1, ORC_ZERO_INCY = 2, ORC_N_LT0 = 3, ORC_M_LT0 = 4, ORC_K_LT0 = 5,
   ORC_BAD_LDA = 6, ORC_BAD_LDB = 7, ORC_BAD_LDC = 8,
   ORC_SHORT_X = 9, ORC_SHORT_Y = 10, ORC_SHORT_A = 11, ORC_SHORT_B = 12, ORC_SHORT_C = 13,
-  ORC_NOT_SUPPORTED = 14
+  ORC_NOT_SUPPORTED = 14,
+  ORC_BAD_CONV = 15        /* ConvParams.Validate (conv.go:34-51) */
 };
 const char* orc_panic_string(int code);
 
@@ -85,6 +86,16 @@ int orc_fused_gemm_bias_gelu(int ta, int tb, int m, int n, int k, float alpha, c
                              const float* b, int ldb, float beta, float* c, int ldc, const float* bias,
                              int gelu_route, int threads);
 void orc_add_bias_gelu(float* x, const float* bias, int n, int bias_len);     /* fused_gelu.go:12-41 */
+
+/* ---- Conv2D via im2col -> Sgemm (conv.go:69-226) and the direct form (conv.go:231-300); NCHW, kernel [OC][IC][KH][KW] ---- */
+void orc_im2col(const float* input, int channels, int height, int width, int kh, int kw, int pad_h, int pad_w,
+                int stride_h, int stride_w, int dil_h, int dil_w, float* output, size_t ld_out);
+int orc_conv2d(const float* input, const float* kernel, const float* bias, float* output, int batch, int in_c, int in_h, int in_w,
+               int out_c, int kh, int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int use_bias,
+               int threads);
+int orc_conv2d_direct(const float* input, const float* kernel, const float* bias, float* output, int batch, int in_c, int in_h,
+                      int in_w, int out_c, int kh, int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                      int use_bias);
 
 /* ---- bf16 / fp16 (bfloat16.go:12-29,104-167; float16.go:21-87,201-244) ---- */
 uint16_t orc_to_bf16(float f);

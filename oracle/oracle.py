@@ -217,6 +217,34 @@ def fused_gemm_bias_gelu(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, b
     return c
 
 
+# ---------------------------------------------------------------- Conv2D (conv.go)
+CONV_KEYS = ("BatchSize", "InChannels", "InHeight", "InWidth", "OutChannels", "KernelHeight", "KernelWidth",
+             "StrideH", "StrideW", "PadH", "PadW", "DilationH", "DilationW")
+
+
+def conv_out_hw(p):
+    """ConvParams.OutputHeight/OutputWidth (conv.go:54-63)."""
+    if p["StrideH"] <= 0 or p["StrideW"] <= 0:
+        return 0, 0
+    oh = (p["InHeight"] + 2 * p["PadH"] - ((p["KernelHeight"] - 1) * p["DilationH"] + 1)) // p["StrideH"] + 1
+    ow = (p["InWidth"] + 2 * p["PadW"] - ((p["KernelWidth"] - 1) * p["DilationW"] + 1)) // p["StrideW"] + 1
+    return oh, ow
+
+
+def conv2d(inp, kernel, bias, p, direct=False, threads=1):
+    """p: dict with the ConvParams field names.  Returns the NCHW output as a flat float32 array."""
+    inp, kernel = _f32(inp), _f32(kernel)
+    oh, ow = conv_out_hw(p)
+    out = np.zeros(max(p["BatchSize"] * p["OutChannels"] * oh * ow, 1), dtype=np.float32)
+    use_bias = int(bool(p.get("UseBias")) and bias is not None)
+    b = _f32(bias) if bias is not None else np.zeros(1, dtype=np.float32)
+    args = [_p(inp, C.c_float), _p(kernel, C.c_float), _p(b, C.c_float), _p(out, C.c_float)] + [int(p[k]) for k in CONV_KEYS] + [use_bias]
+    rc = lib().orc_conv2d_direct(*args) if direct else lib().orc_conv2d(*(args + [threads]))
+    if rc:
+        raise OraclePanic("conv2d: invalid parameters (code %d)" % rc)
+    return out[:p["BatchSize"] * p["OutChannels"] * oh * ow]
+
+
 # ---------------------------------------------------------------- bf16 / fp16
 def to_bf16(x):
     x = _f32(x)

@@ -136,6 +136,26 @@ def extract_var(path, varname):
     return Parser(tokenize(src[start:j + 1])).composite()
 
 
+def extract_conv_cases(path):
+    """conv_test.go: each TestConv2D* holds a ConvParams literal, input/kernel[/bias] float32 literals and `expected`."""
+    src = open(path).read()
+    src = src[:src.index("func BenchmarkConv2D")]
+    cases = []
+    for name, body in re.findall(r"func (TestConv2D\w+)\(t \*testing\.T\) \{(.*?)\n\}\n", src, flags=re.S):
+        body = re.sub(r"//[^\n]*", "", body)
+        params = {k: (v == "true" if v in ("true", "false") else int(v))
+                  for k, v in re.findall(r"(\w+):\s*(\d+|true|false),", body[body.index("&ConvParams{"):body.index("}", body.index("&ConvParams{"))])}
+        def floats(var):
+            m = re.search(var + r"\s*:=\s*\[\]float32\{(.*?)\}", body, flags=re.S)
+            return [float(x) for x in re.findall(r"-?\d+\.?\d*", m.group(1))] if m else None
+        exp = floats("expected")
+        if exp is None:
+            exp = [float(re.search(r"expected\s*:=\s*float32\((-?\d+\.?\d*)\)", body).group(1))]
+        cases.append({"name": name, "params": params, "input": floats("input"), "kernel": floats("kernel"), "bias": floats("bias"),
+                      "expected": exp})
+    return cases
+
+
 def main():
     dg = extract_var(os.path.join(REF, "blas/testblas/dgemm.go"), "DgemmCases")
     assert len(dg) == 7, len(dg)
@@ -159,6 +179,10 @@ def main():
     pts = re.findall(r"\{\s*(-?\d+\.?\d*)\s*,\s*(-?\d+\.?\d*)\s*,\s*([-\d.e]+)\s*\}", src[:src.index("func TestAddBiasGELU")])
     json.dump({"source": "fused_gelu_test.go:10-22 (input, expected, tol)", "points": [[float(a), float(b), float(c)] for a, b, c in pts]},
               open(os.path.join(OUT, "gelu_kat.json"), "w"), indent=1)
+    conv = extract_conv_cases(os.path.join(REF, "conv_test.go"))
+    assert len(conv) == 4, len(conv)
+    json.dump({"source": "conv_test.go:8-260 (TestConv2DBasic/WithBias/Stride/MultiChannel: params, inputs, expected, tol 1e-5)",
+               "cases": conv}, open(os.path.join(OUT, "conv_cases.json"), "w"), indent=1)
     print("dgemm cases:", len(dg), "one-vector:", len(keep1), "two-vector:", len(keep2), "gelu points:", len(pts))
 
 

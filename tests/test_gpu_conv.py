@@ -1,0 +1,80 @@
+"""GPU parity for Conv2D (guda_b200/csrc/conv.cu) through the C ABI: the reference's own conv tests (conv_test.go:8-260) and
+random shapes against the oracle's restatement of conv.go -- bit for bit, since both run the same im2col -> Sgemm FMA chain."""
+import numpy as np
+import pytest
+
+from tests.helpers import golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def g():
+    import guda_b200 as G
+    G.Init(0)
+    return G
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle
+    return oracle
+
+
+def _run(g, p, x, w, b):
+    cp = g.ConvParams(**p)
+    oh, ow = cp.OutputHeight(), cp.OutputWidth()
+    n_out = p["BatchSize"] * p["OutChannels"] * oh * ow
+    dx, dw, dout = g.to_device(x), g.to_device(w), g.Malloc(n_out * 4)
+    g.Memset(dout, 0xFF, n_out * 4)
+    db = g.to_device(b) if b is not None else g.DevicePtr()
+    g.Conv2D(dx, dw, db, dout, cp)
+    out = dout.Float32()
+    assert np.array_equal(dx.Float32(), x) and np.array_equal(dw.Float32(), w)
+    for d in (dx, dw, dout) + ((db,) if b is not None else ()):
+        g.Free(d)
+    return out
+
+
+@pytest.mark.parametrize("idx", range(4))
+def test_reference_conv_cases_on_gpu(g, idx):
+    case = golden("conv_cases.json")["cases"][idx]
+    bias = np.array(case["bias"], dtype=np.float32) if case["bias"] else None
+    out = _run(g, case["params"], np.array(case["input"], np.float32), np.array(case["kernel"], np.float32), bias)
+    exp = np.array(case["expected"], dtype=np.float32)
+    assert np.all(np.abs(out[:exp.size] - exp) <= 1e-5)
+
+
+def _params(B, C_, H, W, OC, KH, KW, s=1, p=0, d=1, bias=True):
+    return {"BatchSize": B, "InChannels": C_, "InHeight": H, "InWidth": W, "OutChannels": OC, "KernelHeight": KH, "KernelWidth": KW,
+            "StrideH": s, "StrideW": s, "PadH": p, "PadW": p, "DilationH": d, "DilationW": d, "UseBias": bias}
+
+
+# conv_test.go:262-300 benchmark shapes (32x32x32 3x3, 64x56x56 3x3 -> 64, 3x224x224 7x7 s2) + ragged / dilated / batched ones
+SHAPES = [_params(1, 32, 32, 32, 64, 3, 3, 1, 1), _params(1, 64, 56, 56, 64, 3, 3, 1, 1), _params(1, 3, 224, 224, 64, 7, 7, 2, 3),
+          _params(1, 3, 9, 11, 5, 3, 3, 1, 1, bias=False), _params(2, 4, 8, 8, 6, 3, 3, 2, 1), _params(3, 2, 10, 7, 4, 2, 3, 1, 0, 2),
+          _params(4, 16, 14, 14, 32, 1, 1), _params(1, 1, 5, 5, 1, 5, 5)]
+
+
+@pytest.mark.parametrize("p", SHAPES)
+def test_conv2d_bit_exact_vs_oracle(g, O, p):
+    x = O.uniform_f32(p["BatchSize"] * p["InChannels"] * p["InHeight"] * p["InWidth"], 1)
+    w = O.uniform_f32(p["OutChannels"] * p["InChannels"] * p["KernelHeight"] * p["KernelWidth"], 2)
+    w[::7] = 0.0                                    # the Sgemm zero test acts on the weights
+    b = O.uniform_f32(p["OutChannels"], 3) if p["UseBias"] else None
+    got = _run(g, p, x, w, b)
+    want = O.conv2d(x, w, b, p, threads=8)
+    assert np.array_equal(got, want)
+    direct = O.conv2d(x, w, b, p, direct=True)
+    assert np.max(np.abs(got - direct)) <= 2e-5 * max(1.0, float(np.max(np.abs(direct))))
+
+
+def test_conv2d_validation_errors(g):
+    p = _params(1, 1, 4, 4, 1, 3, 3)
+    z = g.Malloc(64)
+    for field, val in (("StrideH", 0), ("DilationW", 0), ("PadH", -1), ("OutChannels", 0), ("BatchSize", 0)):
+        bad = dict(p); bad[field] = val
+        with pytest.raises(g.GUDAError) as e:
+            g.Conv2D(z, z, None, z, g.ConvParams(**bad))
+        assert e.value.type == 2 and "invalid" in e.value.message           # InvalidArgument, conv.go:34-51
+    g.Free(z)

@@ -214,6 +214,33 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
         g.Free(x); g.Free(y)
     g.Free(scal)
 
+    # ---- level 2: SGEMV N / T and SGER on a 16384 x 16384 matrix (1 GiB, 2 rotating copies > L2)
+    m2 = n2 = 16384
+    mats = []
+    for i in range(2):
+        a = g.Malloc(m2 * n2 * 4); g.FillUniform(a, m2, n2, n2, 250 + i); mats.append(a)
+    vx, vy = g.Malloc(n2 * 4), g.Malloc(n2 * 4)
+    g.FillUniform(vx, 1, n2, n2, 252); g.FillUniform(vy, 1, n2, n2, 253)
+
+    def l2(fn, nbytes, key):
+        def call():
+            a = mats[it[0] % 2]; it[0] += 1
+            fn(a)
+        for _ in range(3):
+            call()
+        ms = dev.time_ms(call, 20)
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out[key] = {"value": gbs, "unit": "GB/s", "ms": ms, "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"],
+                    "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"],
+                    "algorithmic_bytes": nbytes}}
+
+    l2(lambda a: dev.L.guda_sgemv(0, m2, n2, 1.0, a.ptr, n2, vx.ptr, 1, 0.5, vy.ptr, 1, None), 4.0 * m2 * n2, "sgemv_n_16384")
+    l2(lambda a: dev.L.guda_sgemv(1, m2, n2, 1.0, a.ptr, n2, vx.ptr, 1, 0.5, vy.ptr, 1, None), 4.0 * m2 * n2, "sgemv_t_16384")
+    l2(lambda a: dev.L.guda_sger(m2, n2, 1e-6, vx.ptr, 1, vy.ptr, 1, a.ptr, n2, None), 8.0 * m2 * n2, "sger_16384")
+    for a in mats:
+        g.Free(a)
+    g.Free(vx); g.Free(vy)
+
     # ---- C1: SGEMM 1024^3 (README headline), alpha=1 beta=0; 16 rotating triples (192 MiB)
     n = 1024
     sets = []

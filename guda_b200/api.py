@@ -317,6 +317,31 @@ def Dscal(n, alpha, x, incx, stream=None):
     capi.check(_L().guda_dscal(n, alpha, x.ptr, incx, _sh(stream)), "Dscal")
 
 
+# ---------------------------------------------------------------- Level 2
+def Sgemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy, stream=None):    # compute/level2float32.go:244-308
+    """Slice-length panics (which need len()) are raised here in the reference's order; the dimension / ld / increment panics
+    come back from the C ABI with the same strings."""
+    if m >= 0 and n >= 0 and lda >= max(1, n) and incx != 0 and incy != 0 and m > 0 and n > 0:
+        lenx, leny = (m, n) if trans else (n, m)
+        lx, ly = _len(x, 4), _len(y, 4)
+        if (incx > 0 and (lenx - 1) * incx >= lx) or (incx < 0 and (1 - lenx) * incx >= lx): raise BlasPanic("blas: insufficient length of x")
+        if (incy > 0 and (leny - 1) * incy >= ly) or (incy < 0 and (1 - leny) * incy >= ly): raise BlasPanic("blas: insufficient length of y")
+        if _len(a, 4) < lda * (m - 1) + n: raise BlasPanic("blas: insufficient length of a")
+    capi.check(_L().guda_sgemv(int(bool(trans)), m, n, alpha, a.ptr, lda, x.ptr, incx, beta, y.ptr, incy, _sh(stream)), "Sgemv")
+    if trans and m > 0 and n > 0 and alpha != 0 and beta == 0 and incy == 1 and _len(y, 4) > n:
+        # compute/asm/f32/gemv.go:61-64: `for i := range y { y[i] = 0 }` clears the whole slice, not only y[:n]
+        capi.check(_L().guda_memset(y.ptr + 4 * n, 0, 4 * (_len(y, 4) - n), _sh(stream)), "Sgemv")
+
+
+def Sger(m, n, alpha, x, incx, y, incy, a, lda, stream=None):                  # compute/level2float32.go:24-65
+    if m >= 0 and n >= 0 and lda >= max(1, n) and incx != 0 and incy != 0 and m > 0 and n > 0:
+        lx, ly = _len(x, 4), _len(y, 4)
+        if (incx > 0 and lx <= (m - 1) * incx) or (incx < 0 and lx <= (1 - m) * incx): raise BlasPanic("blas: insufficient length of x")
+        if (incy > 0 and ly <= (n - 1) * incy) or (incy < 0 and ly <= (1 - n) * incy): raise BlasPanic("blas: insufficient length of y")
+        if _len(a, 4) < lda * (m - 1) + n: raise BlasPanic("blas: insufficient length of a")
+    capi.check(_L().guda_sger(m, n, alpha, x.ptr, incx, y.ptr, incy, a.ptr, lda, _sh(stream)), "Sger")
+
+
 def AXPY(alpha, x, y, n, stream=None):             # math.go:39-47
     Saxpy(n, alpha, x, 1, y, 1, stream)
 

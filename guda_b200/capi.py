@@ -86,6 +86,8 @@ SIGNATURES = {
     "guda_gemm_bf16_bias_gelu": (i, [i, i, i, f, vp, i, vp, i, vp, i, vp, vp]),
     "guda_add_bias_gelu": (i, [vp, vp, i, i, vp]),
     "guda_add_bias_relu": (i, [vp, vp, i, i, vp]),
+    "guda_sgemv": (i, [i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
+    "guda_sger": (i, [i, i, f, vp, i, vp, i, vp, i, vp]),
     "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
     "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
     "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),

@@ -144,6 +144,31 @@ inline void GEMMFloat16(bool transA, bool transB, int m, int n, int k, float alp
   check(guda_gemm_f16(transA, transB, m, n, k, alpha, (const uint16_t*)a.ptr, lda, (const uint16_t*)b.ptr, ldb, beta, (uint16_t*)c.ptr, ldc, nullptr), "GEMMFloat16");
 }
 
+// compute/level2float32.go:244-308 Sgemv (row-major); slice-length panics here, the rest from the C ABI with the same strings
+inline void Sgemv(bool trans, int m, int n, float alpha, const DevicePtr& a, int lda, const DevicePtr& x, int incX, float beta,
+                  const DevicePtr& y, int incY) {
+  if (m > 0 && n > 0 && lda >= (n > 1 ? n : 1) && incX != 0 && incY != 0) {
+    const long long lenX = trans ? m : n, lenY = trans ? n : m, lx = (long long)(x.size / 4), ly = (long long)(y.size / 4);
+    if ((incX > 0 && (lenX - 1) * incX >= lx) || (incX < 0 && (1 - lenX) * incX >= lx)) throw BlasPanic("blas: insufficient length of x");
+    if ((incY > 0 && (lenY - 1) * incY >= ly) || (incY < 0 && (1 - lenY) * incY >= ly)) throw BlasPanic("blas: insufficient length of y");
+    if ((long long)(a.size / 4) < (long long)lda * (m - 1) + n) throw BlasPanic("blas: insufficient length of a");
+  }
+  check(guda_sgemv(trans, m, n, alpha, f32(a), lda, f32(x), incX, beta, f32(y), incY, nullptr), "Sgemv");
+  // compute/asm/f32/gemv.go:61-64: GemvT with beta == 0 and incY == 1 clears the whole y slice
+  if (trans && m > 0 && n > 0 && alpha != 0 && beta == 0 && incY == 1 && y.size / 4 > (size_t)n)
+    check(guda_memset(static_cast<char*>(y.ptr) + 4 * (size_t)n, 0, (y.size / 4 - n) * 4, nullptr), "Sgemv");
+}
+// compute/level2float32.go:24-65 Sger
+inline void Sger(int m, int n, float alpha, const DevicePtr& x, int incX, const DevicePtr& y, int incY, const DevicePtr& a, int lda) {
+  if (m > 0 && n > 0 && lda >= (n > 1 ? n : 1) && incX != 0 && incY != 0) {
+    const long long lx = (long long)(x.size / 4), ly = (long long)(y.size / 4);
+    if ((incX > 0 && lx <= (long long)(m - 1) * incX) || (incX < 0 && lx <= (long long)(1 - m) * incX)) throw BlasPanic("blas: insufficient length of x");
+    if ((incY > 0 && ly <= (long long)(n - 1) * incY) || (incY < 0 && ly <= (long long)(1 - n) * incY)) throw BlasPanic("blas: insufficient length of y");
+    if ((long long)(a.size / 4) < (long long)lda * (m - 1) + n) throw BlasPanic("blas: insufficient length of a");
+  }
+  check(guda_sger(m, n, alpha, f32(x), incX, f32(y), incY, f32(a), lda, nullptr), "Sger");
+}
+
 // conv.go:9-31 ConvParams, :69 Conv2D
 struct ConvParams {
   int BatchSize = 0, InChannels = 0, InHeight = 0, InWidth = 0, OutChannels = 0, KernelHeight = 0, KernelWidth = 0;

@@ -98,6 +98,29 @@ int main() {
     EXPECT(dout.Float32() == expected, "Conv2D basic");
     Free(di); Free(dk); Free(dout);
   }
+  // ---- Sgemv N / T and Sger (compute/level2float32.go:244-308, :24-65): bit-exact against the oracle
+  {
+    const int m = 37, n = 75;
+    std::vector<float> a = uniform(m * n, 71), xn = uniform(n, 72), xt = uniform(m, 73), yn = uniform(m, 74), yt = uniform(n, 75);
+    DevicePtr da = Malloc(a.size() * 4), dxn = Malloc(n * 4), dxt = Malloc(m * 4), dyn = Malloc(m * 4), dyt = Malloc(n * 4);
+    da.CopyFrom(a); dxn.CopyFrom(xn); dxt.CopyFrom(xt); dyn.CopyFrom(yn); dyt.CopyFrom(yt);
+    Sgemv(false, m, n, 1.5f, da, n, dxn, 1, 0.25f, dyn, 1);
+    Sgemv(true, m, n, 1.5f, da, n, dxt, 1, 0.25f, dyt, 1);
+    Synchronize();
+    orc_sgemv(0, m, n, 1.5f, a.data(), a.size(), n, xn.data(), n, 1, 0.25f, yn.data(), m, 1);
+    orc_sgemv(1, m, n, 1.5f, a.data(), a.size(), n, xt.data(), m, 1, 0.25f, yt.data(), n, 1);
+    EXPECT(dyn.Float32() == yn, "Sgemv NoTrans bit-exact");
+    EXPECT(dyt.Float32() == yt, "Sgemv Trans bit-exact");
+    Sger(m, n, -0.75f, dxt, 1, dxn, 1, da, n);
+    Synchronize();
+    orc_sger(m, n, -0.75f, xt.data(), m, 1, xn.data(), n, 1, a.data(), a.size(), n);
+    EXPECT(da.Float32() == a, "Sger bit-exact");
+    bool pan = false; try { Sgemv(false, m, n, 1.0f, da, n - 1, dxn, 1, 0.0f, dyn, 1); } catch (const BlasPanic& e) { pan = std::string(e.what()) == "blas: bad leading dimension of A"; }
+    EXPECT(pan, "bad lda must panic with the reference's string");
+    pan = false; try { Sgemv(false, m, n, 1.0f, da, n, dxt, 1, 0.0f, dyn, 1); } catch (const BlasPanic& e) { pan = std::string(e.what()) == "blas: insufficient length of x"; }
+    EXPECT(pan, "short x must panic with the reference's string");
+    Free(da); Free(dxn); Free(dxt); Free(dyn); Free(dyt);
+  }
   std::printf(failures ? "host_test: %d FAILED\n" : "host_test: all checks passed\n", failures);
   return failures ? 1 : 0;
 }

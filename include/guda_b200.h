@@ -155,6 +155,16 @@ int guda_gemm_bf16_bias_gelu(int m, int n, int k, float alpha, const uint16_t* a
 int guda_add_bias_gelu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
 int guda_add_bias_relu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
 
+/* ---- Level 2: compute/level2float32.go:244-308 Sgemv, :24-65 Sger (row-major; lda = row stride);
+ * kernels compute/asm/f32/gemv.go:12-91 (GemvN / GemvT) and compute/asm/f32/ge_amd64.s (Ger).  trans: 0 = NoTrans,
+ * non-zero = Trans / ConjTrans.  Dimension, ld and zero-increment panics come back as GUDA_ERR_INVALID_ARG with the
+ * reference's strings; slice-length panics are the host shim's (it knows len()).  Results are bit-identical to the reference's
+ * AVX2 route for every increment sign.  One reference quirk lives in the host shim because it needs len(y): GemvT with
+ * beta == 0 and incY == 1 clears y[n:len(y)] too (gemv.go:61-64). */
+int guda_sgemv(int trans, int m, int n, float alpha, const float* a, int lda, const float* x, int incx, float beta, float* y, int incy,
+               guda_stream_t stream);
+int guda_sger(int m, int n, float alpha, const float* x, int incx, const float* y, int incy, float* a, int lda, guda_stream_t stream);
+
 /* ---- Conv2D: conv.go:9-31 ConvParams, :69 Conv2D = im2col -> Sgemm -> NCHW placement + bias.
  * input [B][IC][H][W], kernel [OC][IC][KH][KW], bias [OC] (used when use_bias != 0 and bias != NULL), output [B][OC][OH][OW].
  * Blocks until done (it owns a pooled workspace, like the reference's `defer Free(workspace)`). */

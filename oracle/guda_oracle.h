@@ -87,6 +87,14 @@ int orc_fused_gemm_bias_gelu(int ta, int tb, int m, int n, int k, float alpha, c
                              int gelu_route, int threads);
 void orc_add_bias_gelu(float* x, const float* bias, int n, int bias_len);     /* fused_gelu.go:12-41 */
 
+/* ---- Level 2 (compute/level2float32.go:244-308 Sgemv, :24-65 Sger; compute/asm/f32/gemv.go, ge_noasm.go); row-major ---- */
+void orc_f32_gemv(int trans, int m, int n, float alpha, const float* a, int lda, const float* x, int incx,
+                  float beta, float* y, size_t leny, int incy);   /* package f32's GemvN/GemvT: no checks, no alpha == 0 shortcut */
+int orc_sgemv(int trans, int m, int n, float alpha, const float* a, size_t lena, int lda, const float* x, size_t lenx, int incx,
+              float beta, float* y, size_t leny, int incy);
+int orc_sger(int m, int n, float alpha, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy,
+             float* a, size_t lena, int lda);
+
 /* ---- Conv2D via im2col -> Sgemm (conv.go:69-226) and the direct form (conv.go:231-300); NCHW, kernel [OC][IC][KH][KW] ---- */
 void orc_im2col(const float* input, int channels, int height, int width, int kh, int kw, int pad_h, int pad_w,
                 int stride_h, int stride_w, int dil_h, int dil_w, float* output, size_t ld_out);

@@ -67,6 +67,9 @@ def lib():
         L.orc_f16_to_f32.argtypes = [C.c_uint16]; L.orc_f16_to_f32.restype = f
         L.orc_gemm_bf16.argtypes = [i, i, i, f, u16p, i, u16p, i, f, u16p, i]; L.orc_gemm_bf16.restype = None
         L.orc_gemm_f16.argtypes = [i, i, i, i, i, f, u16p, i, u16p, i, f, u16p, i, i]
+        L.orc_sgemv.argtypes = [i, i, i, f, fp, sz, i, fp, sz, i, f, fp, sz, i]
+        L.orc_f32_gemv.argtypes = [i, i, i, f, fp, i, fp, i, f, fp, sz, i]; L.orc_f32_gemv.restype = None
+        L.orc_sger.argtypes = [i, i, f, fp, sz, i, fp, sz, i, fp, sz, i]
         L.orc_generate_f32.argtypes = [fp, sz, C.c_uint64]; L.orc_generate_f32.restype = None
         L.orc_generate_f32_masked.argtypes = [fp, sz, C.c_uint64, f, f]; L.orc_generate_f32_masked.restype = None
         L.orc_generate_f64_masked.argtypes = [dp, sz, C.c_uint64, d, d]; L.orc_generate_f64_masked.restype = None
@@ -215,6 +218,34 @@ def fused_gemm_bias_gelu(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, b
                                         beta, _p(c, C.c_float), ldc, _p(bias, C.c_float),
                                         0 if route == "scalar" else 1, threads))
     return c
+
+
+# ---------------------------------------------------------------- Level 2
+def sgemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy):
+    """In place on y (float32 array)."""
+    assert y.dtype == np.float32 and y.flags.c_contiguous
+    a, x = _f32(a), _f32(x)
+    _chk(lib().orc_sgemv(int(trans), m, n, C.c_float(alpha), _p(a, C.c_float), C.c_size_t(a.size), lda, _p(x, C.c_float), C.c_size_t(x.size), incx,
+                         C.c_float(beta), _p(y, C.c_float), C.c_size_t(y.size), incy))
+    return y
+
+
+def f32_gemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy):
+    """package f32's GemvN / GemvT (what gemv_test.go calls): unchecked, no alpha == 0 shortcut.  In place on y."""
+    assert y.dtype == np.float32 and y.flags.c_contiguous
+    a, x = _f32(a), _f32(x)
+    lib().orc_f32_gemv(int(trans), m, n, C.c_float(alpha), _p(a, C.c_float), lda, _p(x, C.c_float), incx, C.c_float(beta),
+                       _p(y, C.c_float), C.c_size_t(y.size), incy)
+    return y
+
+
+def sger(m, n, alpha, x, incx, y, incy, a, lda):
+    """In place on a (float32 array)."""
+    assert a.dtype == np.float32 and a.flags.c_contiguous
+    x, y = _f32(x), _f32(y)
+    _chk(lib().orc_sger(m, n, C.c_float(alpha), _p(x, C.c_float), C.c_size_t(x.size), incx, _p(y, C.c_float), C.c_size_t(y.size), incy,
+                        _p(a, C.c_float), C.c_size_t(a.size), lda))
+    return a
 
 
 # ---------------------------------------------------------------- Conv2D (conv.go)

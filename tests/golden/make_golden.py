@@ -136,6 +136,26 @@ def extract_var(path, varname):
     return Parser(tokenize(src[start:j + 1])).composite()
 
 
+def extract_struct_slice(path, varname):
+    """`var name = []struct { ...fields... }{ ...elements... }`: skip the anonymous struct type, parse the element list."""
+    src = open(path).read()
+    m = re.search(r"var\s+%s\s*=\s*\[\]struct\s*\{" % varname, src)
+    j = src.index("}", m.end())                       # flat field list: the first closing brace ends the type
+    start = src.index("{", j)
+    depth, j = 0, start
+    while True:
+        ch = src[j]
+        if ch == "{":
+            depth += 1
+        elif ch == "}":
+            depth -= 1
+            if depth == 0:
+                break
+        j += 1
+    body = re.sub(r"//[^\n]*", "", src[start:j + 1])
+    return Parser(tokenize(body)).composite()
+
+
 def extract_conv_cases(path):
     """conv_test.go: each TestConv2D* holds a ConvParams literal, input/kernel[/bias] float32 literals and `expected`."""
     src = open(path).read()
@@ -183,6 +203,12 @@ def main():
     assert len(conv) == 4, len(conv)
     json.dump({"source": "conv_test.go:8-260 (TestConv2DBasic/WithBias/Stride/MultiChannel: params, inputs, expected, tol 1e-5)",
                "cases": conv}, open(os.path.join(OUT, "conv_cases.json"), "w"), indent=1)
+    gemv = extract_var(os.path.join(REF, "compute/asm/f32/gemv_test.go"), "SgemvCases")
+    ger = extract_struct_slice(os.path.join(REF, "compute/asm/f32/ge_test.go"), "gerTests")
+    assert len(gemv) == 7 and len(ger) >= 8, (len(gemv), len(ger))
+    json.dump({"source": "compute/asm/f32/gemv_test.go:35-506 (SgemvCases; harness :508-615, tol 1e-6 abs-or-rel); "
+                         "compute/asm/f32/ge_test.go:14-144 (gerTests; harness :146-219, alpha 1 unit / 3.5 strided)",
+               "gemv": gemv, "ger": ger}, open(os.path.join(OUT, "level2_cases.json"), "w"), indent=1)
     print("dgemm cases:", len(dg), "one-vector:", len(keep1), "two-vector:", len(keep2), "gelu points:", len(pts))
 
 

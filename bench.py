@@ -199,11 +199,13 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     ms = dev.time_ms(axpy, 40)
     gbs = 12.0 * n / (ms * 1e-3) / 1e9
     out["saxpy_16M"] = {"value": gbs, "unit": "GB/s", "ms": ms, "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"],
-                        "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"]}}
+                        "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"],
+                        "algorithmic_bytes": 12.0 * n, "traffic": ncu_traffic("saxpy_16M")}}
     ms = dev.time_ms(dot, 40)
     gbs = 8.0 * n / (ms * 1e-3) / 1e9
     out["sdot_16M"] = {"value": gbs, "unit": "GB/s", "ms": ms, "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"],
-                       "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"]}}
+                       "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"],
+                       "algorithmic_bytes": 8.0 * n, "traffic": ncu_traffic("sdot_16M")}}
     # blocking DOT through the public call (host scalar back every call)
     t0 = time.perf_counter()
     for _ in range(40):
@@ -232,7 +234,7 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
         gbs = nbytes / (ms * 1e-3) / 1e9
         out[key] = {"value": gbs, "unit": "GB/s", "ms": ms, "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"],
                     "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": gbs / 8000.0, "peak_source": peaks["source"],
-                    "algorithmic_bytes": nbytes}}
+                    "algorithmic_bytes": nbytes, "traffic": ncu_traffic(key)}}
 
     l2(lambda a: dev.L.guda_sgemv(0, m2, n2, 1.0, a.ptr, n2, vx.ptr, 1, 0.5, vy.ptr, 1, None), 4.0 * m2 * n2, "sgemv_n_16384")
     l2(lambda a: dev.L.guda_sgemv(1, m2, n2, 1.0, a.ptr, n2, vx.ptr, 1, 0.5, vy.ptr, 1, None), 4.0 * m2 * n2, "sgemv_t_16384")

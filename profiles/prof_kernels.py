@@ -22,6 +22,17 @@ if which in ("all", "level1"):
         g.DOT(x, y, n)
         g.Scale(0.999, x, n)
     g.Free(x); g.Free(y)
+if which in ("all", "level2"):
+    m = n = 16384
+    a, x, y = g.Malloc(m * n * 4), g.Malloc(n * 4), g.Malloc(n * 4)
+    g.FillUniform(a, m, n, n, 11); g.FillUniform(x, 1, n, n, 12); g.FillUniform(y, 1, n, n, 13)
+    for _ in range(reps):
+        g.Sgemv(False, m, n, 1.0, a, n, x, 1, 0.5, y, 1)
+        g.Sgemv(True, m, n, 1.0, a, n, x, 1, 0.5, y, 1)
+        g.Sger(m, n, 1e-6, x, 1, y, 1, a, n)
+    g.Synchronize()
+    for p in (a, x, y):
+        g.Free(p)
 if which in ("all", "sgemm"):
     n = int(os.environ.get("PROF_N", "8192"))
     a, b, c = g.Malloc(n * n * 4), g.Malloc(n * n * 4), g.Malloc(n * n * 4)

@@ -243,6 +243,26 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
         g.Free(a)
     g.Free(vx); g.Free(vy)
 
+    # ---- reductions: blocking scalar-returning calls over 2^28 floats (1 GiB, 2 rotating buffers)
+    nr = 1 << 28
+    rb = []
+    for i in range(2):
+        x = g.Malloc(nr * 4); g.FillUniform(x, 1, nr, nr, 260 + i); rb.append(x)
+    rf, ri = C.c_float(0), C.c_longlong(0)
+    for key, fn, res in (("ssum_256M", dev.L.guda_ssum, rf), ("smax_256M", dev.L.guda_smax, rf), ("sargmax_256M", dev.L.guda_sargmax, ri)):
+        def call():
+            x = rb[it[0] % 2]; it[0] += 1
+            fn(nr, x.ptr, C.byref(res), None)
+        for _ in range(3):
+            call()
+        ms = dev.time_ms(call, 10)
+        gbs = 4.0 * nr / (ms * 1e-3) / 1e9
+        out[key] = {"value": gbs, "unit": "GB/s", "ms": ms, "includes": "launch + stream sync + host read of the scalar, every call",
+                    "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                                 "peak_source": peaks["source"], "algorithmic_bytes": 4.0 * nr, "traffic": ncu_traffic(key)}}
+    for x in rb:
+        g.Free(x)
+
     # ---- C1: SGEMM 1024^3 (README headline), alpha=1 beta=0; 16 rotating triples (192 MiB)
     n = 1024
     sets = []

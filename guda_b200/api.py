@@ -58,6 +58,33 @@ class DevicePtr:
     def Byte(self): return self._snapshot(np.uint8)
     def UInt16(self): return self._snapshot(np.uint16)
 
+    # ---- reductions: reduce.go:13-56 (blocking, scalar to the host like the reference's return values)
+    def _slice_check(self, n):
+        if n < 0 or n > self.size // 4:
+            raise IndexError("slice bounds out of range")          # d.Float32()[:n] in the reference
+
+    def _red_f(self, fn, n):
+        self._slice_check(n)
+        r = C.c_float(0)
+        capi.check(getattr(_L(), fn)(n, self.ptr, C.byref(r), None), fn)
+        return np.float32(r.value)
+
+    def _red_i(self, fn, n):
+        self._slice_check(n)
+        r = C.c_longlong(0)
+        capi.check(getattr(_L(), fn)(n, self.ptr, C.byref(r), None), fn)
+        return int(r.value)
+
+    def Sum(self, n): return self._red_f("guda_ssum", n)                    # reduce.go:13
+    def Max(self, n): return self._red_f("guda_smax", n)                    # reduce.go:18
+    def Min(self, n): return self._red_f("guda_smin", n)                    # reduce.go:26
+    def ArgMax(self, n): return self._red_i("guda_sargmax", n)              # reduce.go:34
+    def ArgMin(self, n): return self._red_i("guda_sargmin", n)              # reduce.go:42
+    def SumSquares(self, n): return self._red_f("guda_ssumsq", n)           # reduce.go:51
+
+    def Mean(self, n):                                                       # reduce.go:59-64
+        return np.float32(0) if n == 0 else np.float32(self.Sum(n) / np.float32(n))
+
     def __repr__(self):
         return "DevicePtr(0x%x, size=%d, offset=%d)" % (self.ptr, self.size, self.offset)
 
@@ -315,6 +342,16 @@ def Dscal(n, alpha, x, incx, stream=None):
         raise BlasPanic("blas: n < 0")
     if (n - 1) * incx >= _len(x, 8): raise BlasPanic("blas: insufficient length of x")
     capi.check(_L().guda_dscal(n, alpha, x.ptr, incx, _sh(stream)), "Dscal")
+
+
+def Isamax(n, x, incx, stream=None):                # compute/level1float32.go:89-130
+    if incx < 1:
+        if incx == 0: raise BlasPanic("blas: zero x index increment")
+        return -1
+    if _len(x, 4) <= (n - 1) * incx: raise BlasPanic("blas: insufficient length of x")
+    r = C.c_longlong(0)
+    capi.check(_L().guda_isamax(n, x.ptr, incx, C.byref(r), _sh(stream)), "Isamax")
+    return int(r.value)
 
 
 # ---------------------------------------------------------------- Level 2

@@ -88,6 +88,13 @@ SIGNATURES = {
     "guda_add_bias_relu": (i, [vp, vp, i, i, vp]),
     "guda_sgemv": (i, [i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_sger": (i, [i, i, f, vp, i, vp, i, vp, i, vp]),
+    "guda_ssum": (i, [C.c_longlong, vp, fp, vp]),
+    "guda_ssumsq": (i, [C.c_longlong, vp, fp, vp]),
+    "guda_smax": (i, [C.c_longlong, vp, fp, vp]),
+    "guda_smin": (i, [C.c_longlong, vp, fp, vp]),
+    "guda_sargmax": (i, [C.c_longlong, vp, C.POINTER(C.c_longlong), vp]),
+    "guda_sargmin": (i, [C.c_longlong, vp, C.POINTER(C.c_longlong), vp]),
+    "guda_isamax": (i, [i, vp, i, C.POINTER(C.c_longlong), vp]),
     "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
     "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
     "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),

@@ -1,0 +1,438 @@
+// reduce.cu -- whole-vector reductions on the DOT streaming skeleton: Sum, SumSquares, Max, Min, ArgMax, ArgMin, Isamax.
+//
+// Replaces reduce.go:13-56 (DevicePtr.Sum/Max/Min/ArgMax/ArgMin/SumSquares -> compute/asm/f32/sum_amd64.s and
+// compute/asm/f32/reduce_avx2_amd64.s) and Isamax (compute/level1float32.go:89-130).
+//
+// Contract (what the oracle checks):
+//   ArgMax / ArgMin / Isamax : bit-exact.  The reference's scalar loops update only on an ordered strict compare, so the answer is
+//       "first index of the extreme among the non-NaN elements, or 0 when x[0] is NaN" -- a commutative (value, smallest index)
+//       reduction once every thread starts from (x[0], 0): a NaN x[0] then never loses, exactly like VCOMISS + JBE.
+//   Max / Min                : bit-exact, including NaN and signed-zero behaviour.  VMAXPS/VMINPS return the SECOND operand unless
+//       the first is strictly greater (smaller), so a NaN is forgotten by the next number in its AVX lane and +-0 ties go to the
+//       later element -- order-dependent, but only then.  One streaming pass computes the plain extreme plus a saw-a-NaN flag; when
+//       there was no NaN and the extreme is not zero the plain extreme IS the reference's result (a unique bit pattern).  Otherwise
+//       (rare) an exact kernel replays the 8-lane fold with an ordered, associative segment summary
+//       {EMPTY | NONAN v | HASNAN v} (v = fold of the elements after the segment's last NaN).
+//   Sum / SumSquares         : fp32 pairwise tree (more accurate than the reference's 16 / 8 sequential lanes), deterministic for a
+//       given n; compared under ReduceArchTolerance (tolerance_arch.go:99-106) like DOT.
+//
+// Memory plan: as DOT -- one persistent wave, 128-bit ld.global.nc, 4 independent vectors in flight per thread, shuffle tree,
+// one partial per CTA, the last CTA (acq_rel ticket) folds the partials in index order and writes 16 bytes straight into mapped
+// pinned host memory.  Algorithmic bytes: 4 per element.
+#include "common.cuh"
+#include <cmath>
+#include <mutex>
+
+namespace guda {
+
+enum RedOp { RED_SUM = 0, RED_SUMSQ, RED_MAX, RED_MIN, RED_ARGMAX, RED_ARGMIN, RED_IAMAX };
+
+struct __align__(16) RedResult {
+  float v;              // value (sum, extreme, or the extreme's value for arg ops)
+  unsigned flags;       // bit 0: a NaN was seen (Max / Min)
+  long long idx;        // index (arg ops)
+};
+
+constexpr int RED_THREADS = 256;
+constexpr int RED_UNROLL = 4;
+constexpr int RED_MAX_CTAS = 1024;
+constexpr int RED_SLOTS = 8;
+
+__device__ RedResult g_red_partials[RED_SLOTS][RED_MAX_CTAS];
+__device__ unsigned int g_red_counter[RED_SLOTS];
+
+__device__ __forceinline__ float4 red_ldg(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+
+template <int OP> struct RedState {
+  float v;
+  unsigned flags;
+  long long idx;
+};
+
+template <int OP>
+__device__ __forceinline__ void red_init(RedState<OP>& s, const float* x) {
+  s.flags = 0;
+  s.idx = 0;
+  if constexpr (OP == RED_SUM || OP == RED_SUMSQ) s.v = 0.0f;
+  else if constexpr (OP == RED_MAX) s.v = -INFINITY;
+  else if constexpr (OP == RED_MIN) s.v = INFINITY;
+  else if constexpr (OP == RED_IAMAX) s.v = fabsf(x[0]);
+  else s.v = x[0];
+}
+
+// fold one element (arg ops and max/min; the sums use their own lane accumulators)
+template <int OP>
+__device__ __forceinline__ void red_elem(RedState<OP>& s, float e, long long i) {
+  if constexpr (OP == RED_MAX) {
+    if (e != e) s.flags |= 1u;
+    else if (e > s.v) s.v = e;
+  } else if constexpr (OP == RED_MIN) {
+    if (e != e) s.flags |= 1u;
+    else if (e < s.v) s.v = e;
+  } else if constexpr (OP == RED_ARGMAX) {
+    if (e > s.v) { s.v = e; s.idx = i; }
+  } else if constexpr (OP == RED_ARGMIN) {
+    if (s.v > e) { s.v = e; s.idx = i; }
+  } else if constexpr (OP == RED_IAMAX) {
+    const float a = fabsf(e);
+    if (a > s.v) { s.v = a; s.idx = i; }
+  }
+}
+
+// merge two partial states; commutative for every op except the sums, whose callers fix the order
+template <int OP>
+__device__ __forceinline__ void red_merge(RedState<OP>& a, const RedState<OP>& b) {
+  if constexpr (OP == RED_SUM || OP == RED_SUMSQ) {
+    a.v = __fadd_rn(a.v, b.v);
+  } else if constexpr (OP == RED_MAX) {
+    a.flags |= b.flags;
+    if (b.v > a.v) a.v = b.v;
+  } else if constexpr (OP == RED_MIN) {
+    a.flags |= b.flags;
+    if (b.v < a.v) a.v = b.v;
+  } else if constexpr (OP == RED_ARGMAX || OP == RED_IAMAX) {
+    if (b.v > a.v || (b.v == a.v && b.idx < a.idx)) { a.v = b.v; a.idx = b.idx; }
+  } else {
+    if (b.v < a.v || (b.v == a.v && b.idx < a.idx)) { a.v = b.v; a.idx = b.idx; }
+  }
+}
+
+template <int OP>
+__device__ __forceinline__ RedState<OP> red_shfl_down(const RedState<OP>& s, int o) {
+  RedState<OP> r;
+  r.v = __shfl_down_sync(0xffffffffu, s.v, o);
+  r.flags = (OP == RED_MAX || OP == RED_MIN) ? __shfl_down_sync(0xffffffffu, s.flags, o) : 0u;
+  r.idx = (OP >= RED_ARGMAX) ? __shfl_down_sync(0xffffffffu, s.idx, o) : 0ll;
+  return r;
+}
+
+template <int OP>
+__device__ __forceinline__ void red_block(RedState<OP>& s, RedState<OP>* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) red_merge<OP>(s, red_shfl_down<OP>(s, o));
+  if ((threadIdx.x & 31) == 0) smem[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    RedState<OP> t;
+    if (threadIdx.x < RED_THREADS / 32) t = smem[threadIdx.x];
+    else {                                              // neutral element
+      t.flags = 0;
+      t.idx = 0x7fffffffffffffffll;
+      t.v = (OP == RED_SUM || OP == RED_SUMSQ) ? 0.0f : smem[0].v;
+      if (OP >= RED_ARGMAX) t.idx = smem[0].idx;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) red_merge<OP>(t, red_shfl_down<OP>(t, o));
+    s = t;
+  }
+}
+
+template <int OP>
+__global__ void __launch_bounds__(RED_THREADS, 4) reduce_kernel(size_t n, const float* __restrict__ x, long long incx, size_t head,
+                                                                RedResult* __restrict__ partials, unsigned int* __restrict__ counter,
+                                                                RedResult* __restrict__ out) {
+  RedState<OP> s;
+  red_init<OP>(s, x);
+  float acc[RED_UNROLL][4];
+#pragma unroll
+  for (int u = 0; u < RED_UNROLL; u++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[u][j] = 0.0f;
+
+  if (incx == 1) {
+    const size_t nvec = (n - head) / 4;
+    const float4* xv = reinterpret_cast<const float4*>(x + head);
+    const size_t stride = (size_t)gridDim.x * RED_THREADS * RED_UNROLL;
+    for (size_t base = (size_t)blockIdx.x * RED_THREADS * RED_UNROLL + threadIdx.x; base < nvec; base += stride) {
+      float4 r[RED_UNROLL];
+#pragma unroll
+      for (int u = 0; u < RED_UNROLL; u++) {
+        const size_t i = base + (size_t)u * RED_THREADS;
+        if (i < nvec) r[u] = red_ldg(xv + i);
+      }
+#pragma unroll
+      for (int u = 0; u < RED_UNROLL; u++) {
+        const size_t i = base + (size_t)u * RED_THREADS;
+        if (i < nvec) {
+          const float* e = reinterpret_cast<const float*>(&r[u]);
+          if constexpr (OP == RED_SUM) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[u][j] = __fadd_rn(acc[u][j], e[j]);
+          } else if constexpr (OP == RED_SUMSQ) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[u][j] = __fmaf_rn(e[j], e[j], acc[u][j]);
+          } else {
+            const long long i0 = (long long)(head + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; j++) red_elem<OP>(s, e[j], i0 + j);
+          }
+        }
+      }
+    }
+    if (blockIdx.x == 0) {                              // unaligned head and the < 4 element tail
+      const size_t tail0 = head + nvec * 4;
+      for (size_t k = threadIdx.x; k < head + (n - tail0); k += RED_THREADS) {
+        const size_t i = k < head ? k : tail0 + (k - head);
+        if constexpr (OP == RED_SUM) acc[0][0] = __fadd_rn(acc[0][0], x[i]);
+        else if constexpr (OP == RED_SUMSQ) acc[0][0] = __fmaf_rn(x[i], x[i], acc[0][0]);
+        else red_elem<OP>(s, x[i], (long long)i);
+      }
+    }
+  } else {
+    for (size_t i = (size_t)blockIdx.x * RED_THREADS + threadIdx.x; i < n; i += (size_t)gridDim.x * RED_THREADS) {
+      const float e = x[(long long)i * incx];
+      if constexpr (OP == RED_SUM) acc[0][0] = __fadd_rn(acc[0][0], e);
+      else if constexpr (OP == RED_SUMSQ) acc[0][0] = __fmaf_rn(e, e, acc[0][0]);
+      else red_elem<OP>(s, e, (long long)i);
+    }
+  }
+  if constexpr (OP == RED_SUM || OP == RED_SUMSQ) {     // fixed-order in-thread tree
+    float t = 0.0f;
+#pragma unroll
+    for (int u = 0; u < RED_UNROLL; u++) t = __fadd_rn(t, __fadd_rn(__fadd_rn(acc[u][0], acc[u][1]), __fadd_rn(acc[u][2], acc[u][3])));
+    s.v = t;
+  }
+
+  __shared__ RedState<OP> smem[RED_THREADS / 32];
+  __shared__ bool is_last;
+  red_block<OP>(s, smem);
+  if (threadIdx.x == 0) {
+    RedResult p;
+    p.v = s.v; p.flags = s.flags; p.idx = s.idx;
+    partials[blockIdx.x] = p;
+    unsigned int ticket;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(counter) : "memory");
+    is_last = (ticket == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    // deterministic final pass: thread t folds partials t, t+256, ... in index order, then the same block tree
+    RedState<OP> t;
+    red_init<OP>(t, x);
+    if constexpr (OP == RED_ARGMAX || OP == RED_ARGMIN || OP == RED_IAMAX) t.idx = 0;
+    for (unsigned int i = threadIdx.x; i < gridDim.x; i += RED_THREADS) {
+      const RedResult* pp = partials + i;
+      RedState<OP> b;
+      b.v = __ldcg(&pp->v); b.flags = __ldcg(&pp->flags); b.idx = __ldcg(&pp->idx);
+      red_merge<OP>(t, b);
+    }
+    __syncthreads();
+    red_block<OP>(t, smem);
+    if (threadIdx.x == 0) {
+      RedResult r;
+      r.v = t.v; r.flags = t.flags; r.idx = t.idx;
+      *out = r;
+      *counter = 0;
+      __threadfence_system();                           // out lives in mapped pinned host memory
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------- exact Max / Min replay
+// compute/asm/f32/reduce_avx2_amd64.s:9-113 lane for lane.  op(a, b) = a > b ? a : b (a < b for Min) is what VMAXPS computes; a
+// segment of one AVX lane's sequence is summarised as EMPTY, NONAN(v) or HASNAN(v) with v = fold of the elements after the
+// segment's last NaN (NaN when none follow), and summaries compose associatively in sequence order.  One CTA: thread t owns a
+// contiguous range of 8-element groups, ordered shuffle/shared-memory trees join them, thread 0 finishes the horizontal fold
+// and the scalar tail.
+enum { SEG_EMPTY = 0, SEG_NONAN = 1, SEG_HASNAN = 2 };
+struct Seg { int st; float v; };
+
+template <bool ISMAX> __device__ __forceinline__ float mm_op(float a, float b) { return ISMAX ? (a > b ? a : b) : (a < b ? a : b); }
+template <bool ISMAX> __device__ __forceinline__ void seg_append(Seg& s, float e) {
+  if (e != e) { s.st = SEG_HASNAN; s.v = e; }
+  else if (s.st == SEG_EMPTY) { s.st = SEG_NONAN; s.v = e; }
+  else s.v = mm_op<ISMAX>(s.v, e);                      // a NaN v (nothing after the last NaN yet) is replaced by e
+}
+template <bool ISMAX> __device__ __forceinline__ Seg seg_join(const Seg& l, const Seg& r) {
+  if (r.st == SEG_EMPTY) return l;
+  if (l.st == SEG_EMPTY || r.st == SEG_HASNAN) return r;
+  Seg o;
+  o.st = l.st;
+  o.v = mm_op<ISMAX>(l.v, r.v);
+  return o;
+}
+
+constexpr int MM_THREADS = 1024;
+
+template <bool ISMAX>
+__global__ void __launch_bounds__(MM_THREADS) minmax_exact_kernel(size_t n, const float* __restrict__ x, RedResult* __restrict__ out) {
+  __shared__ Seg sm[MM_THREADS / 32][8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (n < 8) {                                          // scalar_loop from the start, acc = x[0]
+    if (tid == 0) {
+      float r = x[0];
+      for (size_t i = 0; i < n; i++) r = mm_op<ISMAX>(r, x[i]);
+      RedResult o; o.v = r; o.flags = 0; o.idx = 0;
+      *out = o;
+      __threadfence_system();
+    }
+    return;
+  }
+  const size_t groups = n >> 3;
+  const size_t g0 = groups * (size_t)tid / MM_THREADS, g1 = groups * (size_t)(tid + 1) / MM_THREADS;
+  Seg s[8];
+#pragma unroll
+  for (int l = 0; l < 8; l++) { s[l].st = SEG_EMPTY; s[l].v = 0.0f; }
+  if (tid == 0) {
+    const float x0 = x[0];                              // VBROADCASTSS: every lane starts from x[0]
+#pragma unroll
+    for (int l = 0; l < 8; l++) seg_append<ISMAX>(s[l], x0);
+  }
+  for (size_t g = g0; g < g1; g++) {
+#pragma unroll
+    for (int l = 0; l < 8; l++) seg_append<ISMAX>(s[l], x[8 * g + l]);
+  }
+  // ordered tree inside the warp: after step o, lane i holds segments i .. i+2o-1 (only lane 0's total is used)
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+    for (int l = 0; l < 8; l++) {
+      Seg r;
+      r.st = __shfl_down_sync(0xffffffffu, s[l].st, o);
+      r.v = __shfl_down_sync(0xffffffffu, s[l].v, o);
+      if (lane + o < 32) s[l] = seg_join<ISMAX>(s[l], r);
+    }
+  }
+  if (lane == 0)
+#pragma unroll
+    for (int l = 0; l < 8; l++) sm[warp][l] = s[l];
+  __syncthreads();
+  if (warp == 0) {
+#pragma unroll
+    for (int l = 0; l < 8; l++) s[l] = sm[lane][l];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+      for (int l = 0; l < 8; l++) {
+        Seg r;
+        r.st = __shfl_down_sync(0xffffffffu, s[l].st, o);
+        r.v = __shfl_down_sync(0xffffffffu, s[l].v, o);
+        if (lane + o < 32) s[l] = seg_join<ISMAX>(s[l], r);
+      }
+    }
+    if (lane == 0) {
+      float q[4];
+#pragma unroll
+      for (int l = 0; l < 4; l++) q[l] = mm_op<ISMAX>(s[l].v, s[l + 4].v);      // VEXTRACTF128 + VMAXPS
+      q[0] = mm_op<ISMAX>(q[0], q[2]);                                           // VPSRLDQ $8 + VMAXPS
+      q[1] = mm_op<ISMAX>(q[1], q[3]);
+      float r = mm_op<ISMAX>(q[0], q[1]);                                        // VPSRLDQ $4 + VMAXSS
+      for (size_t i = groups * 8; i < n; i++) r = mm_op<ISMAX>(r, x[i]);
+      RedResult o; o.v = r; o.flags = 0; o.idx = 0;
+      *out = o;
+      __threadfence_system();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------- host side
+static std::mutex g_red_mu;
+static unsigned g_red_slot = 0;
+
+template <int OP>
+static int launch_reduce(size_t n, const float* x, long long incx, RedResult* host_out, cudaStream_t s, const char* what) {
+  Scratch* sc;
+  int rc = get_scratch(&sc);
+  if (rc) return rc;
+  size_t head = 0;
+  bool unit = incx == 1;
+  if (unit) {
+    if (((uintptr_t)x & 3) != 0) return set_error(GUDA_ERR_INVALID_ARG, "%s: misaligned pointer", what);
+    const uintptr_t mis = (uintptr_t)x & 15;
+    head = mis ? (16 - mis) / 4 : 0;
+    if (head > n) head = n;
+  }
+  size_t work = unit ? (n / 4 + (size_t)RED_THREADS * RED_UNROLL - 1) / ((size_t)RED_THREADS * RED_UNROLL) : (n + RED_THREADS - 1) / RED_THREADS;
+  unsigned grid = work > 0 ? (unsigned)(work > 65535 ? 65535 : work) : 1u;
+  unsigned wave = (unsigned)sm_count() * 4u;
+  if (wave > (unsigned)RED_MAX_CTAS) wave = RED_MAX_CTAS;
+  if (grid > wave) grid = wave;
+  RedResult* partials;
+  unsigned int* counters;
+  GUDA_CUDA(cudaGetSymbolAddress((void**)&partials, g_red_partials));
+  GUDA_CUDA(cudaGetSymbolAddress((void**)&counters, g_red_counter));
+  std::unique_lock<std::mutex> lk(g_red_mu);
+  const unsigned slot = (g_red_slot++) % RED_SLOTS;
+  // the second half of the library's 256-byte mapped pinned block (DOT owns the first 128 bytes)
+  RedResult* dev_alias = reinterpret_cast<RedResult*>(reinterpret_cast<char*>(sc->host_scalar_dev) + 128 + slot * 16);
+  volatile RedResult* host_alias = reinterpret_cast<volatile RedResult*>(reinterpret_cast<char*>(sc->host_scalar) + 128 + slot * 16);
+  reduce_kernel<OP><<<grid, RED_THREADS, 0, s>>>(n, x, incx, head, partials + (size_t)slot * RED_MAX_CTAS, counters + slot, dev_alias);
+  rc = check_launch(what);
+  if (rc) return rc;
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  host_out->v = host_alias->v; host_out->flags = host_alias->flags; host_out->idx = host_alias->idx;
+  if (OP == RED_MAX || OP == RED_MIN) {
+    if ((host_out->flags & 1u) || host_out->v == 0.0f) {          // NaN seen or a possible +-0 tie: replay the reference's order
+      if (OP == RED_MAX) minmax_exact_kernel<true><<<1, MM_THREADS, 0, s>>>(n, x, dev_alias);
+      else minmax_exact_kernel<false><<<1, MM_THREADS, 0, s>>>(n, x, dev_alias);
+      rc = check_launch(what);
+      if (rc) return rc;
+      GUDA_CUDA(cudaStreamSynchronize(s));
+      host_out->v = host_alias->v;
+    }
+  }
+  return GUDA_OK;
+}
+
+template <int OP>
+static int reduce_value(long long n, const float* x, float* host_result, float empty, guda_stream_t stream, const char* what) {
+  if (!host_result) return set_error(GUDA_ERR_INVALID_ARG, "%s: null result pointer", what);
+  *host_result = empty;
+  if (n < 0) return set_error(GUDA_ERR_INVALID_ARG, "%s: negative length", what);
+  if (n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x) return set_error(GUDA_ERR_INVALID_ARG, "%s: null pointer", what);
+  RedResult r;
+  rc = launch_reduce<OP>((size_t)n, x, 1, &r, native(stream), what);
+  if (rc) return rc;
+  *host_result = r.v;
+  return GUDA_OK;
+}
+
+template <int OP>
+static int reduce_index(long long n, const float* x, long long incx, long long* host_result, guda_stream_t stream, const char* what) {
+  if (!host_result) return set_error(GUDA_ERR_INVALID_ARG, "%s: null result pointer", what);
+  *host_result = -1;
+  if (n < 0) return set_error(GUDA_ERR_INVALID_ARG, "%s: negative length", what);
+  if (n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x) return set_error(GUDA_ERR_INVALID_ARG, "%s: null pointer", what);
+  RedResult r;
+  rc = launch_reduce<OP>((size_t)n, x, incx, &r, native(stream), what);
+  if (rc) return rc;
+  *host_result = r.idx;
+  return GUDA_OK;
+}
+
+}  // namespace guda
+
+using namespace guda;
+extern "C" {
+int guda_ssum(long long n, const float* x, float* host_result, guda_stream_t stream) { return reduce_value<RED_SUM>(n, x, host_result, 0.0f, stream, "Sum"); }
+int guda_ssumsq(long long n, const float* x, float* host_result, guda_stream_t stream) { return reduce_value<RED_SUMSQ>(n, x, host_result, 0.0f, stream, "SumSquares"); }
+int guda_smax(long long n, const float* x, float* host_result, guda_stream_t stream) { return reduce_value<RED_MAX>(n, x, host_result, -INFINITY, stream, "Max"); }
+int guda_smin(long long n, const float* x, float* host_result, guda_stream_t stream) { return reduce_value<RED_MIN>(n, x, host_result, INFINITY, stream, "Min"); }
+int guda_sargmax(long long n, const float* x, long long* host_result, guda_stream_t stream) { return reduce_index<RED_ARGMAX>(n, x, 1, host_result, stream, "ArgMax"); }
+int guda_sargmin(long long n, const float* x, long long* host_result, guda_stream_t stream) { return reduce_index<RED_ARGMIN>(n, x, 1, host_result, stream, "ArgMin"); }
+
+// compute/level1float32.go:89-130 (slice-length panic: host shim)
+int guda_isamax(int n, const float* x, int incx, long long* host_result, guda_stream_t stream) {
+  if (host_result) *host_result = -1;
+  if (incx < 1) {
+    if (incx == 0) GUDA_PANIC("blas: zero x index increment");
+    return GUDA_OK;
+  }
+  if (n < 2) {
+    if (n == 1) { if (host_result) *host_result = 0; return GUDA_OK; }
+    if (n == 0) return GUDA_OK;
+    GUDA_PANIC("blas: n < 0");
+  }
+  return reduce_index<RED_IAMAX>(n, x, incx, host_result, stream, "Isamax");
+}
+}

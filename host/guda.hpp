@@ -144,6 +144,20 @@ inline void GEMMFloat16(bool transA, bool transB, int m, int n, int k, float alp
   check(guda_gemm_f16(transA, transB, m, n, k, alpha, (const uint16_t*)a.ptr, lda, (const uint16_t*)b.ptr, ldb, beta, (uint16_t*)c.ptr, ldc, nullptr), "GEMMFloat16");
 }
 
+// reduce.go:13-56 (methods of DevicePtr in the reference; free functions here) and Isamax (compute/level1float32.go:89-130)
+inline void slice_check(const DevicePtr& d, long long n) { if (n < 0 || (size_t)n > d.size / 4) throw std::out_of_range("slice bounds out of range"); }
+inline float Sum(const DevicePtr& d, long long n) { slice_check(d, n); float r = 0; check(guda_ssum(n, f32(d), &r, nullptr), "Sum"); return r; }
+inline float SumSquares(const DevicePtr& d, long long n) { slice_check(d, n); float r = 0; check(guda_ssumsq(n, f32(d), &r, nullptr), "SumSquares"); return r; }
+inline float Max(const DevicePtr& d, long long n) { slice_check(d, n); float r = 0; check(guda_smax(n, f32(d), &r, nullptr), "Max"); return r; }
+inline float Min(const DevicePtr& d, long long n) { slice_check(d, n); float r = 0; check(guda_smin(n, f32(d), &r, nullptr), "Min"); return r; }
+inline long long ArgMax(const DevicePtr& d, long long n) { slice_check(d, n); long long r = -1; check(guda_sargmax(n, f32(d), &r, nullptr), "ArgMax"); return r; }
+inline long long ArgMin(const DevicePtr& d, long long n) { slice_check(d, n); long long r = -1; check(guda_sargmin(n, f32(d), &r, nullptr), "ArgMin"); return r; }
+inline long long Isamax(int n, const DevicePtr& x, int incX) {
+  if (incX < 1) { if (incX == 0) throw BlasPanic("blas: zero x index increment"); return -1; }
+  if ((long long)(x.size / 4) <= (long long)(n - 1) * incX) throw BlasPanic("blas: insufficient length of x");
+  long long r = -1; check(guda_isamax(n, f32(x), incX, &r, nullptr), "Isamax"); return r;
+}
+
 // compute/level2float32.go:244-308 Sgemv (row-major); slice-length panics here, the rest from the C ABI with the same strings
 inline void Sgemv(bool trans, int m, int n, float alpha, const DevicePtr& a, int lda, const DevicePtr& x, int incX, float beta,
                   const DevicePtr& y, int incY) {

@@ -121,6 +121,25 @@ int main() {
     EXPECT(pan, "short x must panic with the reference's string");
     Free(da); Free(dxn); Free(dxt); Free(dyn); Free(dyt);
   }
+  // ---- reductions (reduce.go:13-56): index / max / min outputs bit-exact, NaN and signed zero included
+  {
+    std::vector<float> v = uniform(100003, 81);
+    v[777] = 5.0f; v[99000] = 5.0f; v[31] = -7.0f;
+    DevicePtr d = Malloc(v.size() * 4); d.CopyFrom(v);
+    EXPECT(ArgMax(d, v.size()) == orc_sargmax(v.data(), v.size()) && ArgMax(d, v.size()) == 777, "ArgMax first of equal maxima");
+    EXPECT(ArgMin(d, v.size()) == 31, "ArgMin");
+    long long want = -1; orc_isamax((int)v.size(), v.data(), v.size(), 1, &want);
+    EXPECT(Isamax((int)v.size(), d, 1) == want && want == 31, "Isamax");
+    float mx = Max(d, v.size()), omx = orc_smax(v.data(), v.size());
+    EXPECT(std::memcmp(&mx, &omx, 4) == 0, "Max bit-exact");
+    v[5] = std::nanf(""); v[99999] = std::nanf(""); d.CopyFrom(v);
+    mx = Max(d, v.size()); omx = orc_smax(v.data(), v.size());
+    EXPECT(std::memcmp(&mx, &omx, 4) == 0, "Max with NaNs follows VMAXPS");
+    float mn = Min(d, v.size()), omn = orc_smin(v.data(), v.size());
+    EXPECT(std::memcmp(&mn, &omn, 4) == 0, "Min with NaNs follows VMINPS");
+    EXPECT(ArgMax(d, 0) == -1 && Max(d, 0) == -INFINITY && Min(d, 0) == INFINITY && Sum(d, 0) == 0.0f, "empty reductions");
+    Free(d);
+  }
   std::printf(failures ? "host_test: %d FAILED\n" : "host_test: all checks passed\n", failures);
   return failures ? 1 : 0;
 }

@@ -165,6 +165,19 @@ int guda_sgemv(int trans, int m, int n, float alpha, const float* a, int lda, co
                guda_stream_t stream);
 int guda_sger(int m, int n, float alpha, const float* x, int incx, const float* y, int incy, float* a, int lda, guda_stream_t stream);
 
+/* ---- Reductions: reduce.go:13-56 DevicePtr.Sum / SumSquares / Max / Min / ArgMax / ArgMin over x[0..n)
+ * (kernels compute/asm/f32/sum_amd64.s, reduce_avx2_amd64.s) and Isamax (compute/level1float32.go:89-130).  Results go to HOST
+ * memory and the calls block, like the reference's scalar returns.  n == 0: 0, 0, -Inf, +Inf, -1, -1 (reduce.go:18-44).
+ * ArgMax / ArgMin / Isamax / Max / Min are bit-identical to the reference, NaN and signed-zero behaviour included; Sum and
+ * SumSquares use a pairwise tree and are matched under ReduceArchTolerance (tolerance_arch.go:99-106) like DOT. */
+int guda_ssum(long long n, const float* x, float* host_result, guda_stream_t stream);
+int guda_ssumsq(long long n, const float* x, float* host_result, guda_stream_t stream);
+int guda_smax(long long n, const float* x, float* host_result, guda_stream_t stream);
+int guda_smin(long long n, const float* x, float* host_result, guda_stream_t stream);
+int guda_sargmax(long long n, const float* x, long long* host_result, guda_stream_t stream);
+int guda_sargmin(long long n, const float* x, long long* host_result, guda_stream_t stream);
+int guda_isamax(int n, const float* x, int incx, long long* host_result, guda_stream_t stream);
+
 /* ---- Conv2D: conv.go:9-31 ConvParams, :69 Conv2D = im2col -> Sgemm -> NCHW placement + bias.
  * input [B][IC][H][W], kernel [OC][IC][KH][KW], bias [OC] (used when use_bias != 0 and bias != NULL), output [B][OC][OH][OW].
  * Blocks until done (it owns a pooled workspace, like the reference's `defer Free(workspace)`). */

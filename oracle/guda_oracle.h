@@ -95,6 +95,15 @@ int orc_sgemv(int trans, int m, int n, float alpha, const float* a, size_t lena,
 int orc_sger(int m, int n, float alpha, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy,
              float* a, size_t lena, int lda);
 
+/* ---- Reductions (reduce.go:13-56 -> compute/asm/f32/{sum_amd64.s,reduce_avx2_amd64.s}; Isamax compute/level1float32.go:89-130) ---- */
+float orc_ssum(const float* x, size_t n);
+float orc_ssumsq(const float* x, size_t n);
+float orc_smax(const float* x, size_t n);
+float orc_smin(const float* x, size_t n);
+long long orc_sargmax(const float* x, size_t n);
+long long orc_sargmin(const float* x, size_t n);
+int orc_isamax(int n, const float* x, size_t lenx, int incx, long long* idx);
+
 /* ---- Conv2D via im2col -> Sgemm (conv.go:69-226) and the direct form (conv.go:231-300); NCHW, kernel [OC][IC][KH][KW] ---- */
 void orc_im2col(const float* input, int channels, int height, int width, int kh, int kw, int pad_h, int pad_w,
                 int stride_h, int stride_w, int dil_h, int dil_w, float* output, size_t ld_out);

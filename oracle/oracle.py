@@ -70,6 +70,11 @@ def lib():
         L.orc_sgemv.argtypes = [i, i, i, f, fp, sz, i, fp, sz, i, f, fp, sz, i]
         L.orc_f32_gemv.argtypes = [i, i, i, f, fp, i, fp, i, f, fp, sz, i]; L.orc_f32_gemv.restype = None
         L.orc_sger.argtypes = [i, i, f, fp, sz, i, fp, sz, i, fp, sz, i]
+        for name in ("orc_ssum", "orc_ssumsq", "orc_smax", "orc_smin"):
+            getattr(L, name).argtypes = [fp, sz]; getattr(L, name).restype = f
+        for name in ("orc_sargmax", "orc_sargmin"):
+            getattr(L, name).argtypes = [fp, sz]; getattr(L, name).restype = C.c_longlong
+        L.orc_isamax.argtypes = [i, fp, sz, i, C.POINTER(C.c_longlong)]
         L.orc_generate_f32.argtypes = [fp, sz, C.c_uint64]; L.orc_generate_f32.restype = None
         L.orc_generate_f32_masked.argtypes = [fp, sz, C.c_uint64, f, f]; L.orc_generate_f32_masked.restype = None
         L.orc_generate_f64_masked.argtypes = [dp, sz, C.c_uint64, d, d]; L.orc_generate_f64_masked.restype = None
@@ -246,6 +251,28 @@ def sger(m, n, alpha, x, incx, y, incy, a, lda):
     _chk(lib().orc_sger(m, n, C.c_float(alpha), _p(x, C.c_float), C.c_size_t(x.size), incx, _p(y, C.c_float), C.c_size_t(y.size), incy,
                         _p(a, C.c_float), C.c_size_t(a.size), lda))
     return a
+
+
+# ---------------------------------------------------------------- Reductions (reduce.go, compute/asm/f32/reduce*.s, sum_amd64.s)
+def _red(name, x, n=None):
+    x = _f32(x)
+    n = x.size if n is None else n
+    return getattr(lib(), name)(_p(x, C.c_float), C.c_size_t(n))
+
+
+def ssum(x, n=None): return np.float32(_red("orc_ssum", x, n))
+def ssumsq(x, n=None): return np.float32(_red("orc_ssumsq", x, n))
+def smax(x, n=None): return np.float32(_red("orc_smax", x, n))
+def smin(x, n=None): return np.float32(_red("orc_smin", x, n))
+def sargmax(x, n=None): return int(_red("orc_sargmax", x, n))
+def sargmin(x, n=None): return int(_red("orc_sargmin", x, n))
+
+
+def isamax(n, x, incx):
+    x = _f32(x)
+    r = C.c_longlong(0)
+    _chk(lib().orc_isamax(n, _p(x, C.c_float), C.c_size_t(x.size), incx, C.byref(r)))
+    return r.value
 
 
 # ---------------------------------------------------------------- Conv2D (conv.go)

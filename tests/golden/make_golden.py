@@ -156,6 +156,29 @@ def extract_struct_slice(path, varname):
     return Parser(tokenize(body)).composite()
 
 
+def extract_reduce_cases(path):
+    """reduce_test.go: testSum/testMax/testMin/testArgMax/testArgMin/testSumSquares each hold a table of
+    {"name", []float32{...} | makeSequence(k), expected} rows."""
+    src = open(path).read()
+    out = {}
+    for fn in ("testSum", "testMax", "testMin", "testArgMax", "testArgMin", "testSumSquares"):
+        body = src[src.index("func %s(" % fn):]
+        body = body[:body.index("\nfunc ", 10)]
+        rows = []
+        for name, inp, exp in re.findall(r'\{"(\w+)",\s*(\[\]float32\{[^}]*\}|makeSequence\(\d+\)),\s*([^}]+?)\},?\s*(?://[^\n]*)?\n', body):
+            if inp.startswith("makeSequence"):
+                vals = [float(i) for i in range(int(re.search(r"\d+", inp).group()))]
+            else:
+                vals = [float(v) for v in re.findall(r"-?\d+\.?\d*", inp[inp.index("{"):])]
+            exp = exp.strip()
+            if "math.Inf(-1)" in exp: e = "-inf"
+            elif "math.Inf(1)" in exp: e = "inf"
+            else: e = float(exp)
+            rows.append({"name": name, "input": vals, "expected": e})
+        out[fn] = rows
+    return out
+
+
 def extract_conv_cases(path):
     """conv_test.go: each TestConv2D* holds a ConvParams literal, input/kernel[/bias] float32 literals and `expected`."""
     src = open(path).read()
@@ -209,6 +232,10 @@ def main():
     json.dump({"source": "compute/asm/f32/gemv_test.go:35-506 (SgemvCases; harness :508-615, tol 1e-6 abs-or-rel); "
                          "compute/asm/f32/ge_test.go:14-144 (gerTests; harness :146-219, alpha 1 unit / 3.5 strided)",
                "gemv": gemv, "ger": ger}, open(os.path.join(OUT, "level2_cases.json"), "w"), indent=1)
+    red = extract_reduce_cases(os.path.join(REF, "reduce_test.go"))
+    assert [len(red[k]) for k in ("testSum", "testMax", "testMin", "testArgMax", "testArgMin", "testSumSquares")] == [5, 5, 5, 6, 6, 5], red
+    json.dump({"source": "reduce_test.go:28-240 (tables of testSum/testMax/testMin/testArgMax/testArgMin/testSumSquares; floatEquals tol 1e-5)",
+               "cases": red}, open(os.path.join(OUT, "reduce_cases.json"), "w"), indent=1)
     print("dgemm cases:", len(dg), "one-vector:", len(keep1), "two-vector:", len(keep2), "gelu points:", len(pts))
 
 

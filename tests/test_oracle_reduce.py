@@ -1,0 +1,94 @@
+"""The reductions oracle (oracle/reduce.c) against the reference's own tables (reduce_test.go:28-240, tolerance 1e-5 as
+floatEquals) and against the semantics of the AVX2 kernels it restates (VMAXPS operand rule, VCOMISS + JBE)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reduce_cases.json")))["cases"]
+FN = {"testSum": O.ssum, "testMax": O.smax, "testMin": O.smin, "testArgMax": O.sargmax, "testArgMin": O.sargmin, "testSumSquares": O.ssumsq}
+
+
+def _exp(e):
+    return {"-inf": -np.inf, "inf": np.inf}.get(e, e)
+
+
+@pytest.mark.parametrize("fn", sorted(GOLD))
+def test_reference_tables(fn):
+    for row in GOLD[fn]:
+        x = np.asarray(row["input"], np.float32)
+        got = FN[fn](x)
+        want = _exp(row["expected"])
+        if np.isinf(want):
+            assert got == want, (fn, row["name"])
+        else:
+            assert abs(float(got) - want) <= 1e-5, (fn, row["name"], got, want)
+
+
+def _fold(x, is_max):
+    """Pure-Python replay of MaxAVX2 / MinAVX2 (reduce_avx2_amd64.s:9-113)."""
+    op = (lambda a, b: a if a > b else b) if is_max else (lambda a, b: a if a < b else b)
+    n = len(x)
+    if n == 0:
+        return np.float32(-np.inf if is_max else np.inf)
+    r = x[0]
+    i = 0
+    if n >= 8:
+        acc = [x[0]] * 8
+        for g in range(n // 8):
+            for l in range(8):
+                acc[l] = op(acc[l], x[8 * g + l])
+        q = [op(acc[l], acc[l + 4]) for l in range(4)]
+        q = [op(q[0], q[2]), op(q[1], q[3])]
+        r = op(q[0], q[1])
+        i = 8 * (n // 8)
+    for j in range(i if n >= 8 else 0, n):
+        r = op(r, x[j])
+    return r
+
+
+@pytest.mark.parametrize("n", [1, 3, 7, 8, 9, 15, 16, 17, 64, 100, 1001])
+def test_minmax_matches_lane_replay_with_nans_and_signed_zeros(n):
+    rng = np.random.default_rng(n)
+    for trial in range(20):
+        x = rng.standard_normal(n).astype(np.float32)
+        if trial % 2:
+            x[rng.integers(0, n, max(1, n // 5))] = np.nan
+        if trial % 3 == 0:
+            x[:] = np.where(rng.random(n) < 0.5, np.float32(0.0), np.float32(-0.0))
+        for is_max, f in ((True, O.smax), (False, O.smin)):
+            got, want = f(x), _fold(list(x), is_max)
+            assert (np.isnan(got) and np.isnan(want)) or (got == want and np.signbit(got) == np.signbit(want)), (n, trial, is_max)
+
+
+def test_arg_semantics():
+    nan = np.nan
+    assert O.sargmax(np.array([nan, 5, 6], np.float32)) == 0            # NaN x[0] never loses (VCOMISS unordered -> JBE)
+    assert O.sargmax(np.array([1, nan, 6, nan, 6], np.float32)) == 2    # NaNs skipped, first of equal maxima
+    assert O.sargmin(np.array([1, nan, -6, nan, -6], np.float32)) == 2
+    assert O.sargmax(np.array([0.0, -0.0, 0.0], np.float32)) == 0       # +-0 compare equal
+    assert O.sargmax(np.zeros(0, np.float32)) == -1 and O.sargmin(np.zeros(0, np.float32)) == -1
+    assert O.isamax(5, np.array([1, -7, 7, nan, 3], np.float32), 1) == 1
+    assert O.isamax(3, np.array([1, 9, -7, 9, 8], np.float32), 2) == 2  # strided: elements 1, -7, 8 -> index 2
+    assert O.isamax(0, np.zeros(0, np.float32), 1) == -1 and O.isamax(3, np.ones(3, np.float32), -1) == -1
+    with pytest.raises(O.OraclePanic, match="blas: zero x index increment"):
+        O.isamax(3, np.ones(3, np.float32), 0)
+    with pytest.raises(O.OraclePanic, match="blas: insufficient length of x"):
+        O.isamax(3, np.ones(4, np.float32), 2)
+    with pytest.raises(O.OraclePanic, match="blas: n < 0"):
+        O.isamax(-1, np.ones(4, np.float32), 1)
+
+
+def test_sums_follow_the_lane_orders():
+    x = O.uniform_f32(1000, 5)
+    assert abs(float(O.ssum(x)) - float(np.sum(x.astype(np.float64)))) < 1e-3
+    assert abs(float(O.ssumsq(x)) - float(np.sum(x.astype(np.float64) ** 2))) < 1e-3
+    # SumSquares, n = 8: 8 FMA lanes, (l + l+4), hadd, hadd
+    y = np.arange(1, 9, dtype=np.float32) * np.float32(1.1)
+    sq = [np.float32(np.float64(v) * np.float64(v)) for v in y]           # fma(x, x, 0) = fl(x*x)
+    q = [np.float32(sq[l] + sq[l + 4]) for l in range(4)]
+    want = np.float32(np.float32(q[0] + q[1]) + np.float32(q[2] + q[3]))
+    assert O.ssumsq(y) == want

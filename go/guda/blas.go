@@ -167,3 +167,23 @@ func (s *Stream) GEMM(transA, transB bool, m, n, k int, alpha float32, a DeviceP
 
 // SetSgemmMode selects the SGEMM arithmetic: 0 = exact-FP32 SIMT (bit-exact, default), 1 = 3xTF32 tensor cores.
 func SetSgemmMode(mode int) error { return status(C.guda_set_sgemm_mode(C.int(mode)), "SetSgemmMode") }
+
+// GEMMHost is GEMM for operands that live in host memory (Go slices): the uploads are pipelined under the kernel by
+// K chunks and C streams back row panel by row panel, so the transfers cost one chunk in and one panel out instead of
+// the whole of A, B and C.  Same arguments, panics and bits as GEMM.  Slices from MallocHost (pinned) make the copies
+// asynchronous; ordinary Go slices work too (pin them for the duration of the call with runtime.Pinner).
+func GEMMHost(transA, transB bool, m, n, k int, alpha float32, a []float32, lda int, b []float32, ldb int,
+	beta float32, c []float32, ldc int) error {
+	if !checkGemm(transA, transB, m, n, k, lda, ldb, ldc, len(a), len(b), len(c)) {
+		return nil
+	}
+	var pa, pb *C.float
+	if len(a) > 0 {
+		pa = (*C.float)(&a[0])
+	}
+	if len(b) > 0 {
+		pb = (*C.float)(&b[0])
+	}
+	return status(C.guda_sgemm_host(cbool(transA), cbool(transB), C.int(m), C.int(n), C.int(k), C.float(alpha),
+		pa, C.int(lda), pb, C.int(ldb), C.float(beta), (*C.float)(&c[0]), C.int(ldc), nil), "GEMM")
+}

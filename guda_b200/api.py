@@ -354,6 +354,20 @@ def Isamax(n, x, incx, stream=None):                # compute/level1float32.go:8
     return int(r.value)
 
 
+def SgemmHost(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream=None):
+    """math.go:98 GEMM on HOST arrays (float32 numpy arrays, or integer addresses of pinned buffers): uploads pipelined under the
+    GEMM by K chunks, C streamed back by row panels; blocks until c holds the result.  Same panics as Sgemm."""
+    def addr(v):
+        return v.ctypes.data if isinstance(v, np.ndarray) else int(v)
+    if all(isinstance(v, np.ndarray) for v in (a, b, c)) and m > 0 and n > 0 and k >= 0 and min(lda, ldb, ldc) >= 1:
+        la, lb, lc = a.size, b.size, c.size
+        if (la < (k - 1) * lda + m) if transA else (la < (m - 1) * lda + k): raise BlasPanic("blas: insufficient length of a")
+        if (lb < (n - 1) * ldb + k) if transB else (lb < (k - 1) * ldb + n): raise BlasPanic("blas: insufficient length of b")
+        if lc < (m - 1) * ldc + n: raise BlasPanic("blas: insufficient length of c")
+    capi.check(_L().guda_sgemm_host(int(bool(transA)), int(bool(transB)), m, n, k, alpha, addr(a), lda, addr(b), ldb, beta, addr(c), ldc,
+                                    _sh(stream)), "GEMM")
+
+
 # ---------------------------------------------------------------- Level 2
 def Sgemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy, stream=None):    # compute/level2float32.go:244-308
     """Slice-length panics (which need len()) are raised here in the reference's order; the dimension / ld / increment panics

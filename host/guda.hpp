@@ -144,6 +144,13 @@ inline void GEMMFloat16(bool transA, bool transB, int m, int n, int k, float alp
   check(guda_gemm_f16(transA, transB, m, n, k, alpha, (const uint16_t*)a.ptr, lda, (const uint16_t*)b.ptr, ldb, beta, (uint16_t*)c.ptr, ldc, nullptr), "GEMMFloat16");
 }
 
+// GEMM on host-resident operands: copies pipelined under the kernel (guda_sgemm_host); same arguments, panics and bits as GEMM
+inline void GEMMHost(bool transA, bool transB, int m, int n, int k, float alpha, const float* a, size_t lenA, int lda, const float* b, size_t lenB,
+                     int ldb, float beta, float* c, size_t lenC, int ldc) {
+  if (m >= 0 && n >= 0 && k >= 0 && lda >= 1 && ldb >= 1 && ldc >= 1) check_lengths(transA, transB, m, n, k, lda, ldb, ldc, lenA, lenB, lenC);
+  check(guda_sgemm_host(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr), "GEMM");
+}
+
 // reduce.go:13-56 (methods of DevicePtr in the reference; free functions here) and Isamax (compute/level1float32.go:89-130)
 inline void slice_check(const DevicePtr& d, long long n) { if (n < 0 || (size_t)n > d.size / 4) throw std::out_of_range("slice bounds out of range"); }
 inline float Sum(const DevicePtr& d, long long n) { slice_check(d, n); float r = 0; check(guda_ssum(n, f32(d), &r, nullptr), "Sum"); return r; }

@@ -121,6 +121,14 @@ int main() {
     EXPECT(pan, "short x must panic with the reference's string");
     Free(da); Free(dxn); Free(dxt); Free(dyn); Free(dyt);
   }
+  // ---- GEMMHost: host operands, pipelined copies; bit-identical to the oracle
+  {
+    const int m = 150, n = 70, k = 90;
+    std::vector<float> a = uniform(m * k, 91), b = uniform(k * n, 92), c = uniform(m * n, 93), want = c;
+    GEMMHost(false, false, m, n, k, 1.5f, a.data(), a.size(), k, b.data(), b.size(), n, 0.5f, c.data(), c.size(), n);
+    orc_sgemm(0, 0, m, n, k, 1.5f, a.data(), a.size(), k, b.data(), b.size(), n, 0.5f, want.data(), want.size(), n, 0, 1);
+    EXPECT(c == want, "GEMMHost bit-exact");
+  }
   // ---- reductions (reduce.go:13-56): index / max / min outputs bit-exact, NaN and signed zero included
   {
     std::vector<float> v = uniform(100003, 81);

@@ -155,6 +155,14 @@ int guda_gemm_bf16_bias_gelu(int m, int n, int k, float alpha, const uint16_t* a
 int guda_add_bias_gelu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
 int guda_add_bias_relu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream);
 
+/* ---- SGEMM on HOST-resident operands: math.go:98 GEMM end to end for callers whose matrices are host memory (the reference's
+ * DevicePtr was a host slice, memory.go:246-300).  Same arguments and panics as guda_sgemm, but a, b, c are HOST pointers (pinned
+ * memory from guda_malloc_host makes the copies asynchronous).  Uploads are pipelined under the GEMM by K chunks (a C element is
+ * one sequential FMA chain, so resuming it chunk by chunk keeps every bit) and C returns row panel by row panel while the next
+ * panel computes.  Blocks until C is on the host.  Bit-identical to guda_sgemm on device-resident copies of the same operands. */
+int guda_sgemm_host(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* host_a, int lda, const float* host_b, int ldb,
+                    float beta, float* host_c, int ldc, guda_stream_t stream);
+
 /* ---- Level 2: compute/level2float32.go:244-308 Sgemv, :24-65 Sger (row-major; lda = row stride);
  * kernels compute/asm/f32/gemv.go:12-91 (GemvN / GemvT) and compute/asm/f32/ge_amd64.s (Ger).  trans: 0 = NoTrans,
  * non-zero = Trans / ConjTrans.  Dimension, ld and zero-increment panics come back as GUDA_ERR_INVALID_ARG with the

@@ -106,3 +106,23 @@ func Isamax(n int, x DevicePtr, incX int) int {
 	}
 	return int(r)
 }
+
+// Softmax mirrors reduce.go:180-187 (in place over x[:n]): MaxAVX2, fastExp(x - max), sum, ScalUnitary(1/sum).
+func Softmax(x DevicePtr, n int) error {
+	if n == 0 {
+		return nil
+	}
+	x.sliceCheck(n)
+	return status(C.guda_softmax((*C.float)(x.ptr), C.longlong(n), nil), "Softmax")
+}
+
+// LayerNorm mirrors fused.go:270-310 (in place over x[:n]); gamma and beta are applied only when both are non-nil
+// device pointers, like the reference.
+func LayerNorm(x DevicePtr, gamma, beta DevicePtr, n int, eps float32) error {
+	x.sliceCheck(n)
+	var g, b *C.float
+	if gamma.ptr != nil && beta.ptr != nil {
+		g, b = (*C.float)(gamma.ptr), (*C.float)(beta.ptr)
+	}
+	return status(C.guda_layer_norm((*C.float)(x.ptr), g, b, C.longlong(n), C.float(eps), nil), "LayerNorm")
+}

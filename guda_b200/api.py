@@ -344,6 +344,18 @@ def Dscal(n, alpha, x, incx, stream=None):
     capi.check(_L().guda_dscal(n, alpha, x.ptr, incx, _sh(stream)), "Dscal")
 
 
+def Softmax(x, n, stream=None):                      # reduce.go:180-187
+    x._slice_check(n)
+    capi.check(_L().guda_softmax(x.ptr, n, _sh(stream)), "Softmax")
+
+
+def LayerNorm(x, gamma, beta, n, eps, stream=None):  # fused.go:270-310
+    x._slice_check(n)
+    gp = gamma.ptr if (gamma is not None and gamma.ptr) else None
+    bp = beta.ptr if (beta is not None and beta.ptr) else None
+    capi.check(_L().guda_layer_norm(x.ptr, gp, bp, n, eps, _sh(stream)), "LayerNorm")
+
+
 def Isamax(n, x, incx, stream=None):                # compute/level1float32.go:89-130
     if incx < 1:
         if incx == 0: raise BlasPanic("blas: zero x index increment")

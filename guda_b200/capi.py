@@ -96,6 +96,8 @@ SIGNATURES = {
     "guda_sargmax": (i, [C.c_longlong, vp, C.POINTER(C.c_longlong), vp]),
     "guda_sargmin": (i, [C.c_longlong, vp, C.POINTER(C.c_longlong), vp]),
     "guda_isamax": (i, [i, vp, i, C.POINTER(C.c_longlong), vp]),
+    "guda_softmax": (i, [vp, C.c_longlong, vp]),
+    "guda_layer_norm": (i, [vp, vp, vp, C.c_longlong, f, vp]),
     "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
     "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
     "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),

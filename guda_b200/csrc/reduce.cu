@@ -410,10 +410,90 @@ static int reduce_index(long long n, const float* x, long long incx, long long* 
   return GUDA_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------- Softmax / LayerNorm
+// compute/asm/f32/reduce.go:152-186 fastExp, operation by operation in unfused fp32 (Go does not contract on amd64)
+__device__ __forceinline__ float fast_exp_f32(float x) {
+  if (x < -87.3f) return 0.0f;
+  const float ln2 = 0.6931472f, inv_ln2 = 1.4426951f;
+  const float sc = __fmul_rn(x, inv_ln2);
+  const int k = (int)(x < 0.0f ? __fsub_rn(sc, 0.5f) : __fadd_rn(sc, 0.5f));      // Go int32(): truncation toward zero
+  const float r = __fsub_rn(x, __fmul_rn((float)k, ln2));
+  float p = __fadd_rn(0.041666668f, __fmul_rn(r, 0.008333334f));
+  p = __fadd_rn(0.16666667f, __fmul_rn(r, p));
+  p = __fadd_rn(0.5f, __fmul_rn(r, p));
+  p = __fadd_rn(1.0f, __fmul_rn(r, p));
+  p = __fadd_rn(1.0f, __fmul_rn(r, p));
+  return __fmul_rn(p, __int_as_float((k + 127) << 23));
+}
+
+__global__ void __launch_bounds__(256) softmax_exp_kernel(size_t n, float* __restrict__ x, float mx) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    x[i] = fast_exp_f32(__fsub_rn(x[i], mx));
+}
+
+__global__ void __launch_bounds__(256) layer_norm_apply_kernel(size_t n, float* __restrict__ x, const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta, float mean, float inv_std) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float nm = __fmul_rn(__fsub_rn(x[i], mean), inv_std);
+    x[i] = (gamma && beta) ? __fadd_rn(__fmul_rn(nm, gamma[i]), beta[i]) : nm;
+  }
+}
+
+static unsigned ew_grid(size_t n) {
+  size_t g = (n + 255) / 256;
+  const size_t cap = (size_t)sm_count() * 16;
+  return (unsigned)(g > cap ? cap : (g ? g : 1));
+}
+
 }  // namespace guda
 
 using namespace guda;
 extern "C" {
+// reduce.go:180-187 Softmax (in place over x[0..n)): Max exactly as MaxAVX2, e_i = fastExp(x_i - max) bit for bit, then the sum
+// (pairwise here, one sequential chain in the reference: ReduceArchTolerance) and x_i = e_i * fl(1/sum).  Blocking.
+int guda_softmax(float* x, long long n, guda_stream_t stream) {
+  if (n < 0) return set_error(GUDA_ERR_INVALID_ARG, "Softmax: negative length");
+  if (n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x) return set_error(GUDA_ERR_INVALID_ARG, "Softmax: null pointer");
+  cudaStream_t s = native(stream);
+  RedResult r;
+  if ((rc = launch_reduce<RED_MAX>((size_t)n, x, 1, &r, s, "Softmax"))) return rc;
+  softmax_exp_kernel<<<ew_grid((size_t)n), 256, 0, s>>>((size_t)n, x, r.v);
+  if ((rc = check_launch("Softmax"))) return rc;
+  if ((rc = launch_reduce<RED_SUM>((size_t)n, x, 1, &r, s, "Softmax"))) return rc;
+  const float inv = 1.0f / r.v;
+  if (n > 0x7fffffffll) return set_error(GUDA_ERR_INVALID_ARG, "Softmax: n exceeds the Level-1 index range");
+  if ((rc = guda_sscal((int)n, inv, x, 1, stream))) return rc;               // ScalUnitary(invSum, x)
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  return GUDA_OK;
+}
+
+// fused.go:270-310 LayerNorm (in place; gamma and beta are applied only when BOTH are given, like the reference).  The two sums
+// are pairwise (sequential in the reference: tolerance), everything after them follows the reference operation by operation.
+int guda_layer_norm(float* x, const float* gamma, const float* beta, long long n, float eps, guda_stream_t stream) {
+  if (n < 0) return set_error(GUDA_ERR_INVALID_ARG, "LayerNorm: negative length");
+  if (n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x) return set_error(GUDA_ERR_INVALID_ARG, "LayerNorm: null pointer");
+  cudaStream_t s = native(stream);
+  RedResult sum, sumsq;
+  if ((rc = launch_reduce<RED_SUM>((size_t)n, x, 1, &sum, s, "LayerNorm"))) return rc;
+  if ((rc = launch_reduce<RED_SUMSQ>((size_t)n, x, 1, &sumsq, s, "LayerNorm"))) return rc;
+  const float fn = (float)n;
+  const float mean = sum.v / fn;
+  volatile float ex2 = sumsq.v / fn, m2 = mean * mean;      // volatile: keep the host compiler from fusing ex2 - mean*mean
+  const float variance = ex2 - m2;
+  volatile float ve = variance + eps;
+  const float inv_std = 1.0f / (float)std::sqrt((double)ve);
+  layer_norm_apply_kernel<<<ew_grid((size_t)n), 256, 0, s>>>((size_t)n, x, gamma, beta, mean, inv_std);
+  if ((rc = check_launch("LayerNorm"))) return rc;
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  return GUDA_OK;
+}
+
 int guda_ssum(long long n, const float* x, float* host_result, guda_stream_t stream) { return reduce_value<RED_SUM>(n, x, host_result, 0.0f, stream, "Sum"); }
 int guda_ssumsq(long long n, const float* x, float* host_result, guda_stream_t stream) { return reduce_value<RED_SUMSQ>(n, x, host_result, 0.0f, stream, "SumSquares"); }
 int guda_smax(long long n, const float* x, float* host_result, guda_stream_t stream) { return reduce_value<RED_MAX>(n, x, host_result, -INFINITY, stream, "Max"); }

@@ -159,6 +159,12 @@ inline float Max(const DevicePtr& d, long long n) { slice_check(d, n); float r =
 inline float Min(const DevicePtr& d, long long n) { slice_check(d, n); float r = 0; check(guda_smin(n, f32(d), &r, nullptr), "Min"); return r; }
 inline long long ArgMax(const DevicePtr& d, long long n) { slice_check(d, n); long long r = -1; check(guda_sargmax(n, f32(d), &r, nullptr), "ArgMax"); return r; }
 inline long long ArgMin(const DevicePtr& d, long long n) { slice_check(d, n); long long r = -1; check(guda_sargmin(n, f32(d), &r, nullptr), "ArgMin"); return r; }
+inline void Softmax(const DevicePtr& x, long long n) { slice_check(x, n); check(guda_softmax(f32(x), n, nullptr), "Softmax"); }   // reduce.go:180
+inline void LayerNorm(const DevicePtr& x, const DevicePtr& gamma, const DevicePtr& beta, long long n, float eps) {            // fused.go:270
+  slice_check(x, n);
+  const bool affine = gamma.ptr && beta.ptr;
+  check(guda_layer_norm(f32(x), affine ? f32(gamma) : nullptr, affine ? f32(beta) : nullptr, n, eps, nullptr), "LayerNorm");
+}
 inline long long Isamax(int n, const DevicePtr& x, int incX) {
   if (incX < 1) { if (incX == 0) throw BlasPanic("blas: zero x index increment"); return -1; }
   if ((long long)(x.size / 4) <= (long long)(n - 1) * incX) throw BlasPanic("blas: insufficient length of x");

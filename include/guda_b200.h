@@ -185,6 +185,11 @@ int guda_smin(long long n, const float* x, float* host_result, guda_stream_t str
 int guda_sargmax(long long n, const float* x, long long* host_result, guda_stream_t stream);
 int guda_sargmin(long long n, const float* x, long long* host_result, guda_stream_t stream);
 int guda_isamax(int n, const float* x, int incx, long long* host_result, guda_stream_t stream);
+/* reduce.go:180-187 Softmax (in place; compute/asm/f32/reduce.go:130-186: MaxAVX2, fastExp, sum, ScalUnitary) and fused.go:270-310
+ * LayerNorm (in place; gamma / beta applied only when both are non-NULL).  The exp, normalise and scale steps follow the reference
+ * operation by operation; the sums are pairwise (ReduceArchTolerance).  Both block. */
+int guda_softmax(float* x, long long n, guda_stream_t stream);
+int guda_layer_norm(float* x, const float* gamma, const float* beta, long long n, float eps, guda_stream_t stream);
 
 /* ---- Conv2D: conv.go:9-31 ConvParams, :69 Conv2D = im2col -> Sgemm -> NCHW placement + bias.
  * input [B][IC][H][W], kernel [OC][IC][KH][KW], bias [OC] (used when use_bias != 0 and bias != NULL), output [B][OC][OH][OW].

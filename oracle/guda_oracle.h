@@ -103,6 +103,9 @@ float orc_smin(const float* x, size_t n);
 long long orc_sargmax(const float* x, size_t n);
 long long orc_sargmin(const float* x, size_t n);
 int orc_isamax(int n, const float* x, size_t lenx, int incx, long long* idx);
+float orc_fast_exp(float x);                         /* compute/asm/f32/reduce.go:152-186 */
+void orc_softmax(float* x, size_t n);                /* reduce.go:180 -> compute/asm/f32/reduce.go:130-149 */
+void orc_layer_norm(float* x, const float* gamma, const float* beta, size_t n, float eps);   /* fused.go:270-310 */
 
 /* ---- Conv2D via im2col -> Sgemm (conv.go:69-226) and the direct form (conv.go:231-300); NCHW, kernel [OC][IC][KH][KW] ---- */
 void orc_im2col(const float* input, int channels, int height, int width, int kh, int kw, int pad_h, int pad_w,

@@ -74,6 +74,9 @@ def lib():
             getattr(L, name).argtypes = [fp, sz]; getattr(L, name).restype = f
         for name in ("orc_sargmax", "orc_sargmin"):
             getattr(L, name).argtypes = [fp, sz]; getattr(L, name).restype = C.c_longlong
+        L.orc_fast_exp.argtypes = [f]; L.orc_fast_exp.restype = f
+        L.orc_softmax.argtypes = [fp, sz]; L.orc_softmax.restype = None
+        L.orc_layer_norm.argtypes = [fp, fp, fp, sz, f]; L.orc_layer_norm.restype = None
         L.orc_isamax.argtypes = [i, fp, sz, i, C.POINTER(C.c_longlong)]
         L.orc_generate_f32.argtypes = [fp, sz, C.c_uint64]; L.orc_generate_f32.restype = None
         L.orc_generate_f32_masked.argtypes = [fp, sz, C.c_uint64, f, f]; L.orc_generate_f32_masked.restype = None
@@ -266,6 +269,24 @@ def smax(x, n=None): return np.float32(_red("orc_smax", x, n))
 def smin(x, n=None): return np.float32(_red("orc_smin", x, n))
 def sargmax(x, n=None): return int(_red("orc_sargmax", x, n))
 def sargmin(x, n=None): return int(_red("orc_sargmin", x, n))
+
+
+def fast_exp(x): return np.float32(lib().orc_fast_exp(C.c_float(x)))
+
+
+def softmax(x):
+    """In place on x (float32 array)."""
+    assert x.dtype == np.float32 and x.flags.c_contiguous
+    lib().orc_softmax(_p(x, C.c_float), C.c_size_t(x.size))
+    return x
+
+
+def layer_norm(x, gamma, beta, eps):
+    assert x.dtype == np.float32 and x.flags.c_contiguous
+    gp = _p(_f32(gamma), C.c_float) if gamma is not None else None
+    bp = _p(_f32(beta), C.c_float) if beta is not None else None
+    lib().orc_layer_norm(_p(x, C.c_float), gp, bp, C.c_size_t(x.size), C.c_float(eps))
+    return x
 
 
 def isamax(n, x, incx):

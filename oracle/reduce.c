@@ -119,3 +119,50 @@ float orc_ssum(const float* x, size_t n) {
   if (tail & 1) r = r + x[i];
   return r;
 }
+
+/* compute/asm/f32/reduce.go:152-186 fastExp: float32 arithmetic, unfused (Go does not contract on amd64) */
+float orc_fast_exp(float x) {
+  if (x < -87.3f) return 0.0f;
+  const float ln2 = 0.6931472f, inv_ln2 = 1.4426951f;
+  float s = x * inv_ln2;
+  int32_t k = (int32_t)(x < 0 ? s - 0.5f : s + 0.5f);
+  float kl = (float)k * ln2;
+  float r = x - kl;
+  const float c2 = 0.5f, c3 = 0.16666667f, c4 = 0.041666668f, c5 = 0.008333334f;
+  float p = r * c5;  p = c4 + p;
+  p = r * p;  p = c3 + p;
+  p = r * p;  p = c2 + p;
+  p = r * p;  p = 1.0f + p;
+  p = r * p;  p = 1.0f + p;
+  union { uint32_t u; float f; } sc;
+  sc.u = (uint32_t)((k + 127) << 23);
+  return p * sc.f;
+}
+
+/* reduce.go:180-187 -> compute/asm/f32/reduce.go:130-149 Softmax: Max (AVX2), fastExp(x - max), sequential sum, ScalUnitary(1/sum) */
+void orc_softmax(float* x, size_t n) {
+  if (n == 0) return;
+  float mx = orc_smax(x, n);
+  float sum = 0.0f;
+  for (size_t i = 0; i < n; i++) { x[i] = orc_fast_exp(x[i] - mx); sum = sum + x[i]; }
+  float inv = 1.0f / sum;
+  for (size_t i = 0; i < n; i++) x[i] = x[i] * inv;
+}
+
+/* fused.go:270-310 LayerNorm: one pass sum / sum of squares (sequential, unfused), variance = E[x^2] - mean^2,
+ * invStd = 1 / float32(sqrt(float64(variance + eps))), then (x - mean) * invStd [* gamma + beta when both are given] */
+void orc_layer_norm(float* x, const float* gamma, const float* beta, size_t n, float eps) {
+  float sum = 0.0f, sumsq = 0.0f;
+  for (size_t i = 0; i < n; i++) { float v = x[i]; sum = sum + v; float q = v * v; sumsq = sumsq + q; }
+  float mean = sum / (float)n;
+  float ex2 = sumsq / (float)n, m2 = mean * mean;
+  float variance = ex2 - m2;
+  float ve = variance + eps;
+  float inv = 1.0f / (float)sqrt((double)ve);
+  for (size_t i = 0; i < n; i++) {
+    float d = x[i] - mean;
+    float nm = d * inv;
+    if (gamma && beta) { float g = nm * gamma[i]; x[i] = g + beta[i]; }
+    else x[i] = nm;
+  }
+}

@@ -149,3 +149,49 @@ def test_large_2_pow_26(g, O):
     assert d.Max(n) == x.max() and d.Min(n) == x.min()
     assert abs(float(d.Sum(n)) - float(np.sum(x.astype(np.float64)))) <= 1e-4 * float(np.sum(np.abs(x.astype(np.float64)))) * 1e-2
     g.Free(d)
+
+
+@pytest.mark.parametrize("n", [1, 4, 5, 1000, 4099, 1 << 20, 3_000_001])
+def test_softmax_against_oracle(g, O, n):
+    """exp step bit-exact given the (bit-exact) max; the normaliser differs only by summation order -> a few ULP."""
+    x = (O.uniform_f32(n, 300 + n % 7) * np.float32(8.0)).astype(np.float32)
+    want = O.softmax(x.copy())
+    d = g.to_device(x)
+    g.Softmax(d, n)
+    got = d.Float32()
+    assert np.all((got >= 0) & (got <= 1)) and abs(float(np.sum(got.astype(np.float64))) - 1.0) <= 1e-5     # reduce_test.go:318-329
+    # got_i = e_i * fl(1/S_gpu), want_i = e_i * fl(1/S_ref) with identical e_i: the ratio is ONE constant for every i (to the two
+    # roundings of the scale step), and it is near 1 up to the reference's own sequential-sum error (~n/2 ulp)
+    nz = want > 1e-30
+    ratio = got[nz].astype(np.float64) / want[nz].astype(np.float64)
+    assert ratio.max() - ratio.min() <= 3e-7 * ratio.mean()
+    assert abs(ratio.mean() - 1.0) <= 4e-6 + 1e-9 * n
+    assert int(np.argmax(got)) == int(np.argmax(want))
+    g.Free(d)
+
+
+def test_softmax_reference_cases(g):
+    for inp in ([1, 1, 1, 1], [1, 2, 3, 4], [10, 20, 30, 40]):
+        d = g.to_device(np.asarray(inp, np.float32))
+        g.Softmax(d, 4)
+        assert abs(float(d.Sum(4)) - 1.0) <= 1e-5
+        g.Free(d)
+
+
+@pytest.mark.parametrize("n", [1, 2, 256, 1000, 4099, 1 << 20])
+@pytest.mark.parametrize("affine", [True, False])
+def test_layer_norm_against_oracle(g, O, n, affine):
+    x = O.uniform_f32(n, 400 + n % 5); gamma = O.uniform_f32(n, 401); beta = O.uniform_f32(n, 402)
+    want = O.layer_norm(x.copy(), gamma if affine else None, beta if affine else None, 1e-5)
+    dx, dg, db = g.to_device(x), g.to_device(gamma), g.to_device(beta)
+    g.LayerNorm(dx, dg if affine else None, db if affine else None, n, 1e-5)
+    got = dx.Float32()
+    x64 = x.astype(np.float64)
+    model = (x64 - x64.mean()) / np.sqrt(x64.var() + 1e-5)
+    if affine:
+        model = model * gamma + beta
+    assert np.allclose(got, model, rtol=1e-4, atol=1e-4)                # reference_test.go:338 (tol * 10), float64 model as arbiter
+    ref_err = float(np.max(np.abs(want - model)))                       # the reference's own sequential-sum error (grows with n)
+    assert float(np.max(np.abs(got - want))) <= 1e-4 + 2.0 * ref_err
+    assert np.array_equal(dg.Float32(), gamma) and np.array_equal(db.Float32(), beta)
+    g.Free(dx); g.Free(dg); g.Free(db)

@@ -92,3 +92,24 @@ def test_sums_follow_the_lane_orders():
     q = [np.float32(sq[l] + sq[l + 4]) for l in range(4)]
     want = np.float32(np.float32(q[0] + q[1]) + np.float32(q[2] + q[3]))
     assert O.ssumsq(y) == want
+
+
+def test_softmax_reference_properties_and_fast_exp():
+    """reduce_test.go:297-333 (sum == 1 within 1e-5, values in [0, 1]) and fastExp against exp within its design error."""
+    for inp in ([1, 1, 1, 1], [1, 2, 3, 4], [10, 20, 30, 40]):
+        x = O.softmax(np.asarray(inp, np.float32))
+        assert abs(float(O.ssum(x)) - 1.0) <= 1e-5 and np.all((x >= 0) & (x <= 1))
+        want = np.exp(np.asarray(inp, np.float64) - max(inp)); want /= want.sum()
+        assert np.allclose(x, want, rtol=2e-5, atol=1e-7)
+    for v in (0.0, -0.1, -1.0, -5.5, -20.0, -87.0, -100.0):
+        assert abs(float(O.fast_exp(v)) - np.exp(v)) <= 2e-6 * np.exp(v) + 1e-38
+
+
+def test_layer_norm_matches_float64_model():
+    x = O.uniform_f32(256, 21); gamma = O.uniform_f32(256, 22); beta = O.uniform_f32(256, 23)
+    got = O.layer_norm(x.copy(), gamma, beta, 1e-5)
+    x64 = x.astype(np.float64)
+    want = (x64 - x64.mean()) / np.sqrt(x64.var() + 1e-5) * gamma + beta
+    assert np.allclose(got, want, rtol=1e-4, atol=1e-4)                 # reference_test.go:338: tol * 10
+    plain = O.layer_norm(x.copy(), None, beta, 1e-5)                    # gamma or beta missing: no affine step (fused.go:299)
+    assert np.allclose(plain, (x64 - x64.mean()) / np.sqrt(x64.var() + 1e-5), rtol=1e-4, atol=1e-4)

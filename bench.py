@@ -509,10 +509,8 @@ def main():
                     # the host-operand entry point: uploads pipelined under the GEMM by K chunks, C streamed back by row panels
                     g.capi.check(L.guda_sgemm_host(0, 0, n, n, n, 1.0, ha, n, hb, n, 0.0, hc, n, None), "SgemmHost")
                     return
-                L.guda_memcpy_async(a_panel.ptr, ha, m_loc * n * 4, 1, None)
-                L.guda_memcpy_async(b_panel.ptr, hb, n * n_loc * 4, 1, None)
-                step()
-                L.guda_memcpy_async(hc, c_block.ptr, m_loc * n_loc * 4, 2, None)
+                g.capi.check(L.guda_sgemm_sharded_host(comm, pr, pc, n, n, n, 1.0, ha, n, hb, n_loc, hc, n_loc, a_panel.ptr, b_panel.ptr,
+                                                       c_block.ptr, c_full.ptr, n, None), "SgemmShardedHost")
             e2e_step()
             barrier()
             e_ms = max_over_ranks(dev.time_ms(e2e_step, max(1, min(args.steps, 2))))
@@ -521,7 +519,7 @@ def main():
                    "h2d_bytes_per_step": (m_loc * n + n * n_loc) * 4 * world, "d2h_bytes_per_step": m_loc * n_loc * 4 * world,
                    "host_memory": "pinned",
                    "call": "guda_sgemm_host (K-chunk pipelined H2D, row-panel D2H)" if world == 1 else
-                           "guda_memcpy_async H2D + guda_sgemm_sharded + guda_memcpy_async D2H"}
+                           "guda_sgemm_sharded_host (K-chunk pipelined H2D under the GEMM, fused gather on the last chunk, D2H of the C block)"}
             for hp in (ha, hb, hc):
                 L.guda_free_host(hp)
         else:

@@ -109,6 +109,7 @@ SIGNATURES = {
     "guda_comm_init_rank": (i, [C.POINTER(vp), i, i, C.POINTER(C.c_uint8)]),
     "guda_comm_destroy": (i, [vp]),
     "guda_sgemm_sharded": (i, [vp, i, i, i, i, i, f, vp, i, vp, i, vp, i, vp, i, vp]),
+    "guda_sgemm_sharded_host": (i, [vp, i, i, i, i, i, f, vp, i, vp, i, vp, i, vp, vp, vp, vp, i, vp]),
     "guda_comm_set_gather_mode": (i, [vp, i]),
     "guda_comm_get_gather_mode": (i, [vp, ip]),
     "guda_sdot_sharded": (i, [vp, i, vp, vp, fp, vp]),

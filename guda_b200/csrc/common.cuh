@@ -51,4 +51,7 @@ struct Scratch {
 };
 int get_scratch(Scratch** out);
 
+// two library-lifetime non-blocking streams for copies pipelined under compute (host_gemm.cu)
+int aux_copy_streams(cudaStream_t* in, cudaStream_t* out);
+
 }  // namespace guda

@@ -27,6 +27,15 @@ static int hg_streams(HgStreams** o) {
   return GUDA_OK;
 }
 
+int aux_copy_streams(cudaStream_t* in, cudaStream_t* out) {
+  HgStreams* st;
+  int rc = hg_streams(&st);
+  if (rc) return rc;
+  *in = st->in;
+  *out = st->out;
+  return GUDA_OK;
+}
+
 struct HgBuffers {
   void *a = nullptr, *b = nullptr, *c = nullptr;
   std::vector<cudaEvent_t> ev;

@@ -205,8 +205,10 @@ int guda_comm_destroy(guda_comm_t comm) {
   return GUDA_OK;
 }
 
-int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha, const float* a_panel, int lda,
-                       const float* b_panel, int ldb, float* c_block, int ldc_block, float* c_full, int ldc_full, guda_stream_t stream) {
+// beta applies to this rank's c_block (the K-chunked host form resumes the FMA chain with beta = 1); c_full receives the result
+static int sgemm_sharded_impl(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha, const float* a_panel, int lda,
+                              const float* b_panel, int ldb, float beta, float* c_block, int ldc_block, float* c_full, int ldc_full,
+                              guda_stream_t stream) {
   if (!comm) return set_error(GUDA_ERR_INVALID_ARG, "null communicator");
   Comm* c = reinterpret_cast<Comm*>(comm);
   if (pr < 1 || pc < 1 || pr * pc != c->nranks) return set_error(GUDA_ERR_INVALID_ARG, "process grid %dx%d does not match %d ranks", pr, pc, c->nranks);
@@ -227,7 +229,7 @@ int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_tota
     if ((rc = resolve_peers(c, c_full, s, peers, &ok))) return rc;
     if (ok) {
       const int r = c->rank / pc, q = c->rank % pc;
-      rc = guda_sgemm_scatter(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, peers, c->nranks,
+      rc = guda_sgemm_scatter(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, beta, c_block, ldc_block, peers, c->nranks,
                               ldc_full, r * m_loc, q * n_loc, stream);
       if (rc) return rc;
       // exit barrier: the one-float all-reduce completes on this stream only after every rank's kernel has finished
@@ -238,7 +240,7 @@ int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_tota
     c->p2p_failed = true;                  // agreed by all ranks (resolve_peers reduces the flag): use NCCL from now on
   }
   // ---- NCCL route: local block, then all-gather ----
-  rc = guda_sgemm(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, stream);
+  rc = guda_sgemm(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, beta, c_block, ldc_block, stream);
   if (rc) return rc;
   if (!c_full) return GUDA_OK;             // caller only wants its block
   const size_t per_block = (size_t)m_loc * n_loc;
@@ -258,6 +260,73 @@ int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_tota
   GUDA_NCCL(g_nccl.AllGather(c_block, c->staging, per_block, ncclFloat, c->comm, s));
   unpack_blocks_kernel<<<sm_count() * 8, 256, 0, s>>>(c->staging, c_full, ldc_full, pr, pc, m_loc, n_loc);
   return check_launch("unpack_blocks");
+}
+
+int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha, const float* a_panel, int lda,
+                       const float* b_panel, int ldb, float* c_block, int ldc_block, float* c_full, int ldc_full, guda_stream_t stream) {
+  return sgemm_sharded_impl(comm, pr, pc, m_total, n_total, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, c_full, ldc_full, stream);
+}
+
+// The same step from HOST panels (each rank's A row panel and B column panel in pinned host memory) to a HOST C block: the uploads
+// are pipelined under the GEMM by 8192-deep K chunks (chunk j's FMA chains resume from the stored block with beta = 1: same
+// bits), the last chunk is the fused GEMM + all-gather launch, then the block returns to the host.  Blocks.
+int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha, const float* host_a_panel, int lda,
+                            const float* host_b_panel, int ldb, float* host_c_block, int ldc_host, float* a_panel_dev, float* b_panel_dev,
+                            float* c_block_dev, float* c_full, int ldc_full, guda_stream_t stream) {
+  if (!comm) return set_error(GUDA_ERR_INVALID_ARG, "null communicator");
+  Comm* c = reinterpret_cast<Comm*>(comm);
+  if (pr < 1 || pc < 1 || pr * pc != c->nranks) return set_error(GUDA_ERR_INVALID_ARG, "process grid %dx%d does not match %d ranks", pr, pc, c->nranks);
+  if (m_total < 0) GUDA_PANIC("blas: m < 0");
+  if (n_total < 0) GUDA_PANIC("blas: n < 0");
+  if (k < 1) return set_error(GUDA_ERR_INVALID_ARG, "sgemm_sharded_host: k must be positive");
+  if (m_total % pr || n_total % pc) return set_error(GUDA_ERR_INVALID_ARG, "m (n) must divide evenly over the process grid");
+  const int m_loc = m_total / pr, n_loc = n_total / pc;
+  if (lda < k) GUDA_PANIC("blas: bad leading dimension of A");
+  if (ldb < n_loc) GUDA_PANIC("blas: bad leading dimension of B");
+  if (ldc_host < n_loc) GUDA_PANIC("blas: bad leading dimension of C");
+  if (!host_a_panel || !host_b_panel || !host_c_block || !a_panel_dev || !b_panel_dev || !c_block_dev)
+    return set_error(GUDA_ERR_INVALID_ARG, "sgemm_sharded_host: null pointer");
+  int rc = bind_device();
+  if (rc) return rc;
+  cudaStream_t s = native(stream), s_in, s_out;
+  if ((rc = aux_copy_streams(&s_in, &s_out))) return rc;
+  std::vector<cudaEvent_t> evs;
+  auto new_event = [&](cudaEvent_t* e) -> int {
+    GUDA_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    evs.push_back(*e);
+    return GUDA_OK;
+  };
+  cudaEvent_t e0;
+  if ((rc = new_event(&e0))) return rc;
+  GUDA_CUDA(cudaEventRecord(e0, s));
+  GUDA_CUDA(cudaStreamWaitEvent(s_in, e0, 0));
+  constexpr int KC = 8192;
+  const int nk = (k + KC - 1) / KC;
+  for (int j = 0; j < nk && !rc; j++) {
+    const int k0 = j * KC, kc = k - k0 < KC ? k - k0 : KC;
+    GUDA_CUDA(cudaMemcpy2DAsync(a_panel_dev + k0, (size_t)k * 4, host_a_panel + k0, (size_t)lda * 4, (size_t)kc * 4, m_loc, cudaMemcpyHostToDevice, s_in));
+    GUDA_CUDA(cudaMemcpy2DAsync(b_panel_dev + (size_t)k0 * n_loc, (size_t)n_loc * 4, host_b_panel + (size_t)k0 * ldb, (size_t)ldb * 4,
+                                (size_t)n_loc * 4, kc, cudaMemcpyHostToDevice, s_in));
+    cudaEvent_t e_in;
+    if ((rc = new_event(&e_in))) break;
+    GUDA_CUDA(cudaEventRecord(e_in, s_in));
+    GUDA_CUDA(cudaStreamWaitEvent(s, e_in, 0));
+    const float bj = j == 0 ? 0.0f : 1.0f;
+    if (j + 1 < nk)
+      rc = guda_sgemm(0, 0, m_loc, n_loc, kc, alpha, a_panel_dev + k0, k, b_panel_dev + (size_t)k0 * n_loc, n_loc, bj, c_block_dev, n_loc, stream);
+    else
+      rc = sgemm_sharded_impl(comm, pr, pc, m_total, n_total, kc, alpha, a_panel_dev + k0, k, b_panel_dev + (size_t)k0 * n_loc, n_loc, bj,
+                              c_block_dev, n_loc, c_full, ldc_full, stream);
+  }
+  if (!rc) {
+    cudaError_t ce = cudaMemcpy2DAsync(host_c_block, (size_t)ldc_host * 4, c_block_dev, (size_t)n_loc * 4, (size_t)n_loc * 4, m_loc,
+                                       cudaMemcpyDeviceToHost, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) rc = set_error(map_cuda_error(ce), "sgemm_sharded_host: %s", cudaGetErrorString(ce));
+  }
+  (void)s_out;
+  for (cudaEvent_t e : evs) cudaEventDestroy(e);
+  return rc;
 }
 
 int guda_comm_set_gather_mode(guda_comm_t comm, int mode) {

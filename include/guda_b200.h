@@ -234,6 +234,12 @@ int guda_comm_destroy(guda_comm_t comm);
 int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha,
                        const float* a_panel, int lda, const float* b_panel, int ldb, float* c_block, int ldc_block,
                        float* c_full, int ldc_full, guda_stream_t stream);
+/* The same step from pinned HOST panels to a HOST C block; a_panel_dev (m/pr x k), b_panel_dev (k x n/pc) and c_block_dev
+ * (m/pr x n/pc) are caller-provided device staging.  Uploads are pipelined under the GEMM by 8192-deep K chunks (same bits: each
+ * chunk resumes the stored FMA chains with beta = 1); the last chunk is the fused GEMM + all-gather launch.  Blocks. */
+int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha, const float* host_a_panel, int lda,
+                            const float* host_b_panel, int ldb, float* host_c_block, int ldc_host, float* a_panel_dev, float* b_panel_dev,
+                            float* c_block_dev, float* c_full, int ldc_full, guda_stream_t stream);
 /* per-GPU partial dot products combined by ncclAllReduce(sum) */
 /* how guda_sgemm_sharded gathers C: P2P (default) = ONE kernel, the GEMM epilogue stores each finished tile straight into every
  * rank's c_full through NVLink-mapped peer pointers (CUDA IPC), no staging copy, no unpack pass; NCCL = local GEMM, then

@@ -83,6 +83,37 @@ def main():
             g.Free(p)
         return res
 
+    def run_host(n, k, mode):
+        """guda_sgemm_sharded_host: pinned host panels -> host C block + gathered c_full; k spans several 8192-deep chunks."""
+        g.capi.check(L.guda_comm_set_gather_mode(comm, mode), "SetGatherMode")
+        r0, m_loc, c0, n_loc = block_extents(rank, pr, pc, n, n)
+        a_panel, b_panel = g.Malloc(m_loc * k * 4), g.Malloc(k * n_loc * 4)
+        c_block, c_full = g.Malloc(m_loc * n_loc * 4), g.Malloc(n * n * 4)
+        g.FillUniform(a_panel, m_loc, k, k, seed=21, row0=r0, col0=0, full_cols=k)
+        g.FillUniform(b_panel, k, n_loc, n_loc, seed=22, row0=0, col0=c0, full_cols=n)
+        ha, hb, hc = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        for h, nb in ((ha, m_loc * k * 4), (hb, k * n_loc * 4), (hc, m_loc * n_loc * 4)):
+            g.capi.check(L.guda_malloc_host(C.byref(h), nb), "MallocHost")
+        L.guda_memcpy(ha, a_panel.ptr, m_loc * k * 4, 2, None); L.guda_memcpy(hb, b_panel.ptr, k * n_loc * 4, 2, None)
+        g.Memset(a_panel, 0xFF, m_loc * k * 4); g.Memset(b_panel, 0xFF, k * n_loc * 4); g.Memset(c_full, 0xFF, n * n * 4)
+        g.capi.check(L.guda_sgemm_sharded_host(comm, pr, pc, n, n, k, 1.0, ha, k, hb, n_loc, hc, n_loc, a_panel.ptr, b_panel.ptr,
+                                               c_block.ptr, c_full.ptr, n, None), "SgemmShardedHost")
+        a, b, c = g.Malloc(n * k * 4), g.Malloc(k * n * 4), g.Malloc(n * n * 4)
+        g.FillUniform(a, n, k, k, seed=21); g.FillUniform(b, k, n, n, seed=22)
+        g.GEMM(False, False, n, n, k, 1.0, a, k, b, n, 0.0, c, n)
+        g.Synchronize()
+        want = c.Float32().reshape(n, n)
+        host_block = np.ctypeslib.as_array(C.cast(hc, C.POINTER(C.c_float)), shape=(m_loc, n_loc))
+        res = {"gathered_bit_identical": bool(np.array_equal(c_full.Float32().reshape(n, n), want)),
+               "host_block_bit_identical": bool(np.array_equal(host_block, want[r0:r0 + m_loc, c0:c0 + n_loc]))}
+        for p in (a, b, c, a_panel, b_panel, c_block, c_full):
+            g.Free(p)
+        for h in (ha, hb, hc):
+            L.guda_free_host(h)
+        return res
+
+    out["check_host_p2p"] = run_host(1024, 2 * 8192 + 300, 0)
+    out["check_host_nccl"] = run_host(1024, 2 * 8192 + 300, 1)
     out["check_p2p"] = run(args.check_size, 0, 1, True)
     out["check_nccl"] = run(args.check_size, 1, 1, True)
     out["time_p2p"] = run(args.size, 0, args.iters, False)
@@ -97,6 +128,8 @@ def main():
     g.capi.check(L.guda_sdot_sharded(comm, nvec // world, x.ptr + lo * 4, y.ptr + lo * 4, C.byref(r), None), "SdotSharded")
     out["sdot"] = {"one_gpu": float(whole), "sharded": float(r.value), "within_reduce_tolerance": bool(abs(r.value - whole) <= max(1e-5, 1e-4 * abs(whole)))}
     ok = torch.tensor([1.0 if (out["check_p2p"]["bit_identical_to_one_gpu"] and out["check_nccl"]["bit_identical_to_one_gpu"]
+                               and all(out[k][f] for k in ("check_host_p2p", "check_host_nccl")
+                                       for f in ("gathered_bit_identical", "host_block_bit_identical"))
                                and out["sdot"]["within_reduce_tolerance"]) else 0.0], device="cuda")
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     out["all_ranks_ok"] = bool(ok.item() > 0.5)

@@ -302,6 +302,7 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
   GUDA_CUDA(cudaStreamWaitEvent(s_in, e0, 0));
   constexpr int KC = 8192;
   const int nk = (k + KC - 1) / KC;
+  bool downloaded = false;
   for (int j = 0; j < nk && !rc; j++) {
     const int k0 = j * KC, kc = k - k0 < KC ? k - k0 : KC;
     GUDA_CUDA(cudaMemcpy2DAsync(a_panel_dev + k0, (size_t)k * 4, host_a_panel + k0, (size_t)lda * 4, (size_t)kc * 4, m_loc, cudaMemcpyHostToDevice, s_in));
@@ -314,17 +315,55 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
     const float bj = j == 0 ? 0.0f : 1.0f;
     if (j + 1 < nk)
       rc = guda_sgemm(0, 0, m_loc, n_loc, kc, alpha, a_panel_dev + k0, k, b_panel_dev + (size_t)k0 * n_loc, n_loc, bj, c_block_dev, n_loc, stream);
-    else
-      rc = sgemm_sharded_impl(comm, pr, pc, m_total, n_total, kc, alpha, a_panel_dev + k0, k, b_panel_dev + (size_t)k0 * n_loc, n_loc, bj,
-                              c_block_dev, n_loc, c_full, ldc_full, stream);
+    else {
+      // last chunk.  Fused route: the GEMM + all-gather launch is cut into row panels so that each finished panel of this rank's
+      // block streams back to the host while the next one computes; otherwise the generic step, then one download.
+      bool fused = false;
+      float* peers[GUDA_MAX_SCATTER_RANKS];
+      if (c_full && ldc_full >= n_total && c->gather_mode == GUDA_GATHER_P2P && !c->p2p_failed && sgemm_mode() == GUDA_SGEMM_EXACT) {
+        if ((rc = resolve_peers(c, c_full, s, peers, &fused))) break;
+        if (!fused) c->p2p_failed = true;
+      }
+      if (!fused) {
+        rc = sgemm_sharded_impl(comm, pr, pc, m_total, n_total, kc, alpha, a_panel_dev + k0, k, b_panel_dev + (size_t)k0 * n_loc, n_loc, bj,
+                                c_block_dev, n_loc, c_full, ldc_full, stream);
+        break;
+      }
+      GUDA_CUDA(cudaStreamWaitEvent(s_out, e0, 0));
+      const int r = c->rank / pc, q = c->rank % pc;
+      const int panels = m_loc >= 2048 ? 8 : 1;
+      const int pm = ((m_loc + panels - 1) / panels + 127) / 128 * 128;
+      for (int p0 = 0; p0 < m_loc && !rc; p0 += pm) {
+        const int ph = m_loc - p0 < pm ? m_loc - p0 : pm;
+        rc = guda_sgemm_scatter(0, 0, ph, n_loc, kc, alpha, a_panel_dev + (size_t)p0 * k + k0, k, b_panel_dev + (size_t)k0 * n_loc, n_loc, bj,
+                                c_block_dev + (size_t)p0 * n_loc, n_loc, peers, c->nranks, ldc_full, r * m_loc + p0, q * n_loc, stream);
+        if (rc) break;
+        cudaEvent_t e_panel;
+        if ((rc = new_event(&e_panel))) break;
+        GUDA_CUDA(cudaEventRecord(e_panel, s));
+        GUDA_CUDA(cudaStreamWaitEvent(s_out, e_panel, 0));
+        GUDA_CUDA(cudaMemcpy2DAsync(host_c_block + (size_t)p0 * ldc_host, (size_t)ldc_host * 4, c_block_dev + (size_t)p0 * n_loc, (size_t)n_loc * 4,
+                                    (size_t)n_loc * 4, ph, cudaMemcpyDeviceToHost, s_out));
+      }
+      if (rc) break;
+      // exit barrier (every rank's kernels have finished storing into this rank's c_full), then wait for the downloads
+      GUDA_NCCL(g_nccl.AllReduce(c->dev_scalar, c->dev_scalar, 1, ncclFloat, ncclSum, c->comm, s));
+      cudaEvent_t e_out;
+      if ((rc = new_event(&e_out))) break;
+      GUDA_CUDA(cudaEventRecord(e_out, s_out));
+      GUDA_CUDA(cudaStreamWaitEvent(s, e_out, 0));
+      downloaded = true;
+    }
   }
-  if (!rc) {
+  if (!rc && downloaded) {
+    cudaError_t ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) rc = set_error(map_cuda_error(ce), "sgemm_sharded_host: %s", cudaGetErrorString(ce));
+  } else if (!rc) {
     cudaError_t ce = cudaMemcpy2DAsync(host_c_block, (size_t)ldc_host * 4, c_block_dev, (size_t)n_loc * 4, (size_t)n_loc * 4, m_loc,
                                        cudaMemcpyDeviceToHost, s);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
     if (ce != cudaSuccess) rc = set_error(map_cuda_error(ce), "sgemm_sharded_host: %s", cudaGetErrorString(ce));
   }
-  (void)s_out;
   for (cudaEvent_t e : evs) cudaEventDestroy(e);
   return rc;
 }

@@ -1,6 +1,7 @@
 // common.cuh -- shared plumbing for libguda_b200: status/last-error, stream handles, launch checks.
 #pragma once
 #include <cuda_runtime.h>
+#include <vector>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -53,5 +54,7 @@ int get_scratch(Scratch** out);
 
 // two library-lifetime non-blocking streams for copies pipelined under compute (host_gemm.cu)
 int aux_copy_streams(cudaStream_t* in, cudaStream_t* out);
+// K boundaries of the host-operand pipeline (short first chunk, then 8192-deep)
+void host_k_chunks(int k, std::vector<int>& bounds);
 
 }  // namespace guda

@@ -27,6 +27,17 @@ static int hg_streams(HgStreams** o) {
   return GUDA_OK;
 }
 
+// K-chunk schedule: a short first chunk (its upload is the only one nothing can hide), then up to the next multiple of HG_KC, then
+// HG_KC-deep chunks.  Any split keeps the bits: every chunk resumes the same FMA chains.
+void host_k_chunks(int k, std::vector<int>& bounds) {
+  bounds.clear();
+  bounds.push_back(0);
+  if (k > 2 * HG_KC) { bounds.push_back(HG_KC / 8); bounds.push_back(HG_KC); }
+  else if (k > HG_KC) bounds.push_back(HG_KC / 8);
+  for (int b = bounds.back() + HG_KC; b < k; b += HG_KC) bounds.push_back(b);
+  bounds.push_back(k);
+}
+
 int aux_copy_streams(cudaStream_t* in, cudaStream_t* out) {
   HgStreams* st;
   int rc = hg_streams(&st);
@@ -98,10 +109,12 @@ extern "C" int guda_sgemm_host(int ta, int tb, int m, int n, int k, float alpha,
 
   // K chunks (NN only: there a chunk is a column block of A and a row block of B); other forms upload whole operands
   const bool chunked = !ta && !tb && k > HG_KC;
-  const int nk = chunked ? (k + HG_KC - 1) / HG_KC : 1;
+  std::vector<int> kb;
+  if (chunked) host_k_chunks(k, kb);
+  const int nk = chunked ? (int)kb.size() - 1 : 1;
   for (int j = 0; j < nk; j++) {
-    const int k0 = chunked ? j * HG_KC : 0;
-    const int kc = chunked ? (k - k0 < HG_KC ? k - k0 : HG_KC) : k;
+    const int k0 = chunked ? kb[j] : 0;
+    const int kc = chunked ? kb[j + 1] - kb[j] : k;
     if (k > 0) {
       if (chunked) {
         GUDA_CUDA(cudaMemcpy2DAsync(da + k0, (size_t)k * 4, host_a + k0, (size_t)lda * 4, (size_t)kc * 4, m, cudaMemcpyHostToDevice, st->in));

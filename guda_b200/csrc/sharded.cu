@@ -300,11 +300,12 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
   if ((rc = new_event(&e0))) return rc;
   GUDA_CUDA(cudaEventRecord(e0, s));
   GUDA_CUDA(cudaStreamWaitEvent(s_in, e0, 0));
-  constexpr int KC = 8192;
-  const int nk = (k + KC - 1) / KC;
+  std::vector<int> kb;
+  host_k_chunks(k, kb);
+  const int nk = (int)kb.size() - 1;
   bool downloaded = false;
   for (int j = 0; j < nk && !rc; j++) {
-    const int k0 = j * KC, kc = k - k0 < KC ? k - k0 : KC;
+    const int k0 = kb[j], kc = kb[j + 1] - kb[j];
     GUDA_CUDA(cudaMemcpy2DAsync(a_panel_dev + k0, (size_t)k * 4, host_a_panel + k0, (size_t)lda * 4, (size_t)kc * 4, m_loc, cudaMemcpyHostToDevice, s_in));
     GUDA_CUDA(cudaMemcpy2DAsync(b_panel_dev + (size_t)k0 * n_loc, (size_t)n_loc * 4, host_b_panel + (size_t)k0 * ldb, (size_t)ldb * 4,
                                 (size_t)n_loc * 4, kc, cudaMemcpyHostToDevice, s_in));

@@ -187,3 +187,67 @@ func GEMMHost(transA, transB bool, m, n, k int, alpha float32, a []float32, lda 
 	return status(C.guda_sgemm_host(cbool(transA), cbool(transB), C.int(m), C.int(n), C.int(k), C.float(alpha),
 		pa, C.int(lda), pb, C.int(ldb), C.float(beta), (*C.float)(&c[0]), C.int(ldc), nil), "GEMM")
 }
+
+// Dsdot mirrors compute/level1float32_dsdot.go:18-54: dot product of two float32 vectors accumulated in float64
+// (the products are exact).  Blocks until the scalar is on the host.
+func Dsdot(n int, x DevicePtr, incX int, y DevicePtr, incY int) float64 {
+	if !checkDsdot(n, x.size/4, incX, y.size/4, incY) {
+		return 0
+	}
+	var r C.double
+	if err := status(C.guda_dsdot(C.int(n), (*C.float)(x.ptr), C.int(incX), (*C.float)(y.ptr), C.int(incY), &r, nil), "Dsdot"); err != nil {
+		panic(err)
+	}
+	return float64(r)
+}
+
+// Sdsdot mirrors compute/level1float32_sdsdot.go:18-54: alpha + float32(Dsdot); 0 when n == 0.
+func Sdsdot(n int, alpha float32, x DevicePtr, incX int, y DevicePtr, incY int) float32 {
+	if !checkDsdot(n, x.size/4, incX, y.size/4, incY) {
+		return 0
+	}
+	var r C.float
+	if err := status(C.guda_sdsdot(C.int(n), C.float(alpha), (*C.float)(x.ptr), C.int(incX), (*C.float)(y.ptr), C.int(incY), &r, nil), "Sdsdot"); err != nil {
+		panic(err)
+	}
+	return float32(r)
+}
+
+// checkDsdot makes the reference's checks in its order (level1float32_dsdot.go:19-52); false = nothing to compute.
+func checkDsdot(n, lenX, incX, lenY, incY int) bool {
+	if incX == 0 {
+		panic("blas: zero x index increment")
+	}
+	if incY == 0 {
+		panic("blas: zero y index increment")
+	}
+	if n <= 0 {
+		if n == 0 {
+			return false
+		}
+		panic("blas: n < 0")
+	}
+	if incX == 1 && incY == 1 {
+		if lenX < n {
+			panic(shortX)
+		}
+		if lenY < n {
+			panic(shortY)
+		}
+		return true
+	}
+	ix, iy := 0, 0
+	if incX < 0 {
+		ix = (-n + 1) * incX
+	}
+	if incY < 0 {
+		iy = (-n + 1) * incY
+	}
+	if ix >= lenX || ix+(n-1)*incX >= lenX {
+		panic(shortX)
+	}
+	if iy >= lenY || iy+(n-1)*incY >= lenY {
+		panic(shortY)
+	}
+	return true
+}

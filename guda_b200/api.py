@@ -322,6 +322,39 @@ def Ddot(n, x, incx, y, incy, stream=None):
     return r.value
 
 
+def _check_dsdot(n, x, incx, y, incy):
+    # compute/level1float32_dsdot.go:19-52 (order and strings)
+    if incx == 0: raise BlasPanic("blas: zero x index increment")
+    if incy == 0: raise BlasPanic("blas: zero y index increment")
+    if n <= 0:
+        if n == 0: return False
+        raise BlasPanic("blas: n < 0")
+    lx, ly = _len(x, 4), _len(y, 4)
+    if incx == 1 and incy == 1:
+        if lx < n: raise BlasPanic("blas: insufficient length of x")
+        if ly < n: raise BlasPanic("blas: insufficient length of y")
+        return True
+    ix = (-n + 1) * incx if incx < 0 else 0
+    iy = (-n + 1) * incy if incy < 0 else 0
+    if ix >= lx or ix + (n - 1) * incx >= lx: raise BlasPanic("blas: insufficient length of x")
+    if iy >= ly or iy + (n - 1) * incy >= ly: raise BlasPanic("blas: insufficient length of y")
+    return True
+
+
+def Dsdot(n, x, incx, y, incy, stream=None):       # compute/level1float32_dsdot.go:18
+    if not _check_dsdot(n, x, incx, y, incy): return 0.0
+    r = C.c_double(0)
+    capi.check(_L().guda_dsdot(n, x.ptr, incx, y.ptr, incy, C.byref(r), _sh(stream)), "Dsdot")
+    return r.value
+
+
+def Sdsdot(n, alpha, x, incx, y, incy, stream=None):   # compute/level1float32_sdsdot.go:18
+    if not _check_dsdot(n, x, incx, y, incy): return np.float32(0)
+    r = C.c_float(0)
+    capi.check(_L().guda_sdsdot(n, alpha, x.ptr, incx, y.ptr, incy, C.byref(r), _sh(stream)), "Sdsdot")
+    return np.float32(r.value)
+
+
 def Sscal(n, alpha, x, incx, stream=None):
     if incx < 1:
         if incx == 0: raise BlasPanic("blas: zero x index increment")

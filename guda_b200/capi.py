@@ -89,6 +89,8 @@ SIGNATURES = {
     "guda_add_bias_relu": (i, [vp, vp, i, i, vp]),
     "guda_sgemv": (i, [i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_sger": (i, [i, i, f, vp, i, vp, i, vp, i, vp]),
+    "guda_dsdot": (i, [i, vp, i, vp, i, dp, vp]),
+    "guda_sdsdot": (i, [i, f, vp, i, vp, i, fp, vp]),
     "guda_ssum": (i, [C.c_longlong, vp, fp, vp]),
     "guda_ssumsq": (i, [C.c_longlong, vp, fp, vp]),
     "guda_smax": (i, [C.c_longlong, vp, fp, vp]),

@@ -410,6 +410,112 @@ static int reduce_index(long long n, const float* x, long long incx, long long* 
   return GUDA_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------- Dsdot / Sdsdot
+// fp32 inputs, fp64 accumulation (compute/level1float32_dsdot.go, level1float32_sdsdot.go; kernels ddotunitary_amd64.s /
+// ddotinc_amd64.s).  The products of two floats are exact in double, so only the summation order differs from the reference
+// (pairwise here, two or four sequential lanes there): agreement to ~1e-15 relative.
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = __dadd_rn(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__global__ void __launch_bounds__(RED_THREADS, 4) dsdot_kernel(size_t n, const float* __restrict__ x, long long incx, const float* __restrict__ y,
+                                                               long long incy, int vec, RedResult* __restrict__ partials,
+                                                               unsigned int* __restrict__ counter, RedResult* __restrict__ out) {
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  if (vec) {                                            // unit strides, both 16-byte aligned
+    const size_t nvec = n / 4;
+    const float4* xv = reinterpret_cast<const float4*>(x);
+    const float4* yv = reinterpret_cast<const float4*>(y);
+    for (size_t i = (size_t)blockIdx.x * RED_THREADS + threadIdx.x; i < nvec; i += (size_t)gridDim.x * RED_THREADS) {
+      const float4 a = red_ldg(xv + i), b = red_ldg(yv + i);
+      acc[0] = __fma_rn((double)a.x, (double)b.x, acc[0]);   // exact product: the FMA rounds once, like MULPD (exact) + ADDPD
+      acc[1] = __fma_rn((double)a.y, (double)b.y, acc[1]);
+      acc[2] = __fma_rn((double)a.z, (double)b.z, acc[2]);
+      acc[3] = __fma_rn((double)a.w, (double)b.w, acc[3]);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+      const size_t i = nvec * 4 + threadIdx.x;
+      acc[0] = __fma_rn((double)x[i], (double)y[i], acc[0]);
+    }
+  } else {
+    for (size_t i = (size_t)blockIdx.x * RED_THREADS + threadIdx.x; i < n; i += (size_t)gridDim.x * RED_THREADS)
+      acc[0] = __fma_rn((double)x[(long long)i * incx], (double)y[(long long)i * incy], acc[0]);
+  }
+  double v = __dadd_rn(__dadd_rn(acc[0], acc[1]), __dadd_rn(acc[2], acc[3]));
+  v = warp_sum_f64(v);
+  __shared__ double wsum[RED_THREADS / 32];
+  __shared__ bool is_last;
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    double w = threadIdx.x < RED_THREADS / 32 ? wsum[threadIdx.x] : 0.0;
+    w = warp_sum_f64(w);
+    if (threadIdx.x == 0) {
+      *reinterpret_cast<double*>(&partials[blockIdx.x]) = w;
+      unsigned int ticket;
+      asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(counter) : "memory");
+      is_last = (ticket == gridDim.x - 1);
+    }
+  }
+  __syncthreads();
+  if (is_last) {
+    double t = 0.0;
+    for (unsigned int i = threadIdx.x; i < gridDim.x; i += RED_THREADS) t = __dadd_rn(t, __ldcg(reinterpret_cast<const double*>(&partials[i])));
+    t = warp_sum_f64(t);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      double w = threadIdx.x < RED_THREADS / 32 ? wsum[threadIdx.x] : 0.0;
+      w = warp_sum_f64(w);
+      if (threadIdx.x == 0) {
+        *reinterpret_cast<double*>(out) = w;
+        *counter = 0;
+        __threadfence_system();
+      }
+    }
+  }
+}
+
+static int dsdot_impl(int n, const float* x, int incx, const float* y, int incy, double* result, guda_stream_t stream, const char* what) {
+  *result = 0.0;
+  if (incx == 0) GUDA_PANIC("blas: zero x index increment");
+  if (incy == 0) GUDA_PANIC("blas: zero y index increment");
+  if (n <= 0) {
+    if (n == 0) return GUDA_OK;
+    GUDA_PANIC("blas: n < 0");
+  }
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x || !y) return set_error(GUDA_ERR_INVALID_ARG, "%s: null pointer", what);
+  cudaStream_t s = native(stream);
+  Scratch* sc;
+  if ((rc = get_scratch(&sc))) return rc;
+  const float* xs = incx < 0 ? x + (long long)(-n + 1) * incx : x;
+  const float* ys = incy < 0 ? y + (long long)(-n + 1) * incy : y;
+  const int vec = incx == 1 && incy == 1 && (((uintptr_t)x | (uintptr_t)y) & 15) == 0;
+  size_t work = vec ? ((size_t)n / 4 + RED_THREADS - 1) / RED_THREADS : ((size_t)n + RED_THREADS - 1) / RED_THREADS;
+  unsigned grid = work > 0 ? (unsigned)(work > 65535 ? 65535 : work) : 1u;
+  unsigned wave = (unsigned)sm_count() * 4u;
+  if (wave > (unsigned)RED_MAX_CTAS) wave = RED_MAX_CTAS;
+  if (grid > wave) grid = wave;
+  RedResult* partials;
+  unsigned int* counters;
+  GUDA_CUDA(cudaGetSymbolAddress((void**)&partials, g_red_partials));
+  GUDA_CUDA(cudaGetSymbolAddress((void**)&counters, g_red_counter));
+  std::unique_lock<std::mutex> lk(g_red_mu);
+  const unsigned slot = (g_red_slot++) % RED_SLOTS;
+  RedResult* dev_alias = reinterpret_cast<RedResult*>(reinterpret_cast<char*>(sc->host_scalar_dev) + 128 + slot * 16);
+  volatile double* host_alias = reinterpret_cast<volatile double*>(reinterpret_cast<char*>(sc->host_scalar) + 128 + slot * 16);
+  dsdot_kernel<<<grid, RED_THREADS, 0, s>>>((size_t)n, xs, incx, ys, incy, vec, partials + (size_t)slot * RED_MAX_CTAS, counters + slot, dev_alias);
+  if ((rc = check_launch(what))) return rc;
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  *result = *host_alias;
+  return GUDA_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------- Softmax / LayerNorm
 // compute/asm/f32/reduce.go:152-186 fastExp, operation by operation in unfused fp32 (Go does not contract on amd64)
 __device__ __forceinline__ float fast_exp_f32(float x) {
@@ -491,6 +597,21 @@ int guda_layer_norm(float* x, const float* gamma, const float* beta, long long n
   layer_norm_apply_kernel<<<ew_grid((size_t)n), 256, 0, s>>>((size_t)n, x, gamma, beta, mean, inv_std);
   if ((rc = check_launch("LayerNorm"))) return rc;
   GUDA_CUDA(cudaStreamSynchronize(s));
+  return GUDA_OK;
+}
+
+// compute/level1float32_dsdot.go:18-54 / level1float32_sdsdot.go:18-54 (slice-length panics: host shim).  Blocking.
+int guda_dsdot(int n, const float* x, int incx, const float* y, int incy, double* host_result, guda_stream_t stream) {
+  if (!host_result) return set_error(GUDA_ERR_INVALID_ARG, "Dsdot: null result pointer");
+  return dsdot_impl(n, x, incx, y, incy, host_result, stream, "Dsdot");
+}
+int guda_sdsdot(int n, float alpha, const float* x, int incx, const float* y, int incy, float* host_result, guda_stream_t stream) {
+  if (!host_result) return set_error(GUDA_ERR_INVALID_ARG, "Sdsdot: null result pointer");
+  double d = 0.0;
+  *host_result = 0.0f;
+  int rc = dsdot_impl(n, x, incx, y, incy, &d, stream, "Sdsdot");
+  if (rc || n <= 0) return rc;                       // n == 0 returns 0, not alpha (level1float32_sdsdot.go:25-28)
+  *host_result = alpha + (float)d;
   return GUDA_OK;
 }
 

@@ -144,6 +144,22 @@ inline void GEMMFloat16(bool transA, bool transB, int m, int n, int k, float alp
   check(guda_gemm_f16(transA, transB, m, n, k, alpha, (const uint16_t*)a.ptr, lda, (const uint16_t*)b.ptr, ldb, beta, (uint16_t*)c.ptr, ldc, nullptr), "GEMMFloat16");
 }
 
+// compute/level1float32_dsdot.go:18 / level1float32_sdsdot.go:18 (unit-stride length checks here; the rest in the C ABI)
+inline double Dsdot(int n, const DevicePtr& x, int incX, const DevicePtr& y, int incY) {
+  if (n > 0 && incX == 1 && incY == 1) {
+    if (x.size / 4 < (size_t)n) throw BlasPanic("blas: insufficient length of x");
+    if (y.size / 4 < (size_t)n) throw BlasPanic("blas: insufficient length of y");
+  }
+  double r = 0; check(guda_dsdot(n, f32(x), incX, f32(y), incY, &r, nullptr), "Dsdot"); return r;
+}
+inline float Sdsdot(int n, float alpha, const DevicePtr& x, int incX, const DevicePtr& y, int incY) {
+  if (n > 0 && incX == 1 && incY == 1) {
+    if (x.size / 4 < (size_t)n) throw BlasPanic("blas: insufficient length of x");
+    if (y.size / 4 < (size_t)n) throw BlasPanic("blas: insufficient length of y");
+  }
+  float r = 0; check(guda_sdsdot(n, alpha, f32(x), incX, f32(y), incY, &r, nullptr), "Sdsdot"); return r;
+}
+
 // GEMM on host-resident operands: copies pipelined under the kernel (guda_sgemm_host); same arguments, panics and bits as GEMM
 inline void GEMMHost(bool transA, bool transB, int m, int n, int k, float alpha, const float* a, size_t lenA, int lda, const float* b, size_t lenB,
                      int ldb, float beta, float* c, size_t lenC, int ldc) {

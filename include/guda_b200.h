@@ -178,6 +178,10 @@ int guda_sger(int m, int n, float alpha, const float* x, int incx, const float* 
  * memory and the calls block, like the reference's scalar returns.  n == 0: 0, 0, -Inf, +Inf, -1, -1 (reduce.go:18-44).
  * ArgMax / ArgMin / Isamax / Max / Min are bit-identical to the reference, NaN and signed-zero behaviour included; Sum and
  * SumSquares use a pairwise tree and are matched under ReduceArchTolerance (tolerance_arch.go:99-106) like DOT. */
+/* Dsdot / Sdsdot: compute/level1float32_dsdot.go:18-54, level1float32_sdsdot.go:18-54 -- fp32 vectors, fp64
+ * accumulation (exact products); Sdsdot = alpha + float32(Dsdot), 0 for n == 0.  Host result, blocking. */
+int guda_dsdot(int n, const float* x, int incx, const float* y, int incy, double* host_result, guda_stream_t stream);
+int guda_sdsdot(int n, float alpha, const float* x, int incx, const float* y, int incy, float* host_result, guda_stream_t stream);
 int guda_ssum(long long n, const float* x, float* host_result, guda_stream_t stream);
 int guda_ssumsq(long long n, const float* x, float* host_result, guda_stream_t stream);
 int guda_smax(long long n, const float* x, float* host_result, guda_stream_t stream);

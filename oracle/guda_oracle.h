@@ -44,6 +44,8 @@ float orc_sdot_inc(const float* x, const float* y, size_t n, ptrdiff_t incx, ptr
 int   orc_saxpy(int n, float alpha, const float* x, size_t lenx, int incx, float* y, size_t leny, int incy);
 int   orc_sdot(int n, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy, float* result);
 int   orc_sscal(int n, float alpha, float* x, size_t lenx, int incx);
+int   orc_dsdot(int n, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy, double* result);   /* level1float32_dsdot.go */
+int   orc_sdsdot(int n, float alpha, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy, float* result);
 
 /* ---- Level 1, fp64 (compute/level1float64.go, compute/asm/f64) ---- */
 void   orc_daxpy_unitary_fma(double alpha, const double* x, double* y, size_t n);

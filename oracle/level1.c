@@ -307,3 +307,69 @@ int orc_dscal(int n, double alpha, double* x, size_t lenx, int incx) {
   for (long long i = 0; i < n; i++) x[i * incx] = x[i * incx] * alpha;
   return ORC_OK;
 }
+
+/* ------------------------------------------------------------------ Dsdot / Sdsdot (fp32 inputs, fp64 accumulation)
+ * compute/level1float32_dsdot.go:18-54, level1float32_sdsdot.go:18-54; kernels compute/asm/f32/ddotunitary_amd64.s (peel until y
+ * is 16-byte aligned, then two 2-lane accumulators over groups of 8, pair tail, single tail, HADDPD) and ddotinc_amd64.s (two
+ * scalar accumulators over groups of 4, then a sequential tail).  Products of two floats are exact in double. */
+static double ddot_unitary(const float* x, const float* y, size_t n) {
+  double s0 = 0, s1 = 0, p0 = 0, p1 = 0;
+  if (n == 0) return 0.0;
+  size_t i = 0, len = n;
+  while (((uintptr_t)(y + i) & 15) != 0) {
+    s0 = s0 + (double)x[i] * (double)y[i];
+    i++; len--;
+    if (len == 0) return s0 + s1;
+  }
+  size_t tail = len & 7;
+  for (size_t it = 0; it < (len >> 3); it++, i += 8) {
+    s0 = s0 + (double)x[i] * (double)y[i];         s1 = s1 + (double)x[i + 1] * (double)y[i + 1];
+    p0 = p0 + (double)x[i + 2] * (double)y[i + 2]; p1 = p1 + (double)x[i + 3] * (double)y[i + 3];
+    s0 = s0 + (double)x[i + 4] * (double)y[i + 4]; s1 = s1 + (double)x[i + 5] * (double)y[i + 5];
+    p0 = p0 + (double)x[i + 6] * (double)y[i + 6]; p1 = p1 + (double)x[i + 7] * (double)y[i + 7];
+  }
+  if (len >> 3) { s0 = s0 + p0; s1 = s1 + p1; }
+  for (size_t it = 0; it < (tail >> 1); it++, i += 2) { s0 = s0 + (double)x[i] * (double)y[i]; s1 = s1 + (double)x[i + 1] * (double)y[i + 1]; }
+  if (tail & 1) s0 = s0 + (double)x[i] * (double)y[i];
+  return s0 + s1;
+}
+static double ddot_inc(const float* x, const float* y, size_t n, ptrdiff_t incx, ptrdiff_t incy, size_t ix, size_t iy) {
+  double sum = 0, psum = 0;
+  const float* px = x + ix; const float* py = y + iy;
+  size_t len = n >> 2, tail = n & 3;
+  for (size_t it = 0; it < len; it++) {
+    sum = sum + (double)px[0] * (double)py[0];               psum = psum + (double)px[incx] * (double)py[incy];
+    sum = sum + (double)px[2 * incx] * (double)py[2 * incy]; psum = psum + (double)px[3 * incx] * (double)py[3 * incy];
+    px += 4 * incx; py += 4 * incy;
+  }
+  if (len) sum = sum + psum;
+  for (; tail; tail--, px += incx, py += incy) sum = sum + (double)px[0] * (double)py[0];
+  return sum;
+}
+int orc_dsdot(int n, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy, double* result) {
+  *result = 0.0;
+  if (incx == 0) return ORC_ZERO_INCX;
+  if (incy == 0) return ORC_ZERO_INCY;
+  if (n <= 0) return n == 0 ? ORC_OK : ORC_N_LT0;
+  if (incx == 1 && incy == 1) {
+    if (lenx < (size_t)n) return ORC_SHORT_X;
+    if (leny < (size_t)n) return ORC_SHORT_Y;
+    *result = ddot_unitary(x, y, (size_t)n);
+    return ORC_OK;
+  }
+  long long ix = 0, iy = 0;
+  if (incx < 0) ix = (long long)(-n + 1) * incx;
+  if (incy < 0) iy = (long long)(-n + 1) * incy;
+  if (ix >= (long long)lenx || ix + (long long)(n - 1) * incx >= (long long)lenx) return ORC_SHORT_X;
+  if (iy >= (long long)leny || iy + (long long)(n - 1) * incy >= (long long)leny) return ORC_SHORT_Y;
+  *result = ddot_inc(x, y, (size_t)n, incx, incy, (size_t)ix, (size_t)iy);
+  return ORC_OK;
+}
+int orc_sdsdot(int n, float alpha, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy, float* result) {
+  double d;
+  int rc = orc_dsdot(n, x, lenx, incx, y, leny, incy, &d);
+  *result = 0.0f;
+  if (rc || n <= 0) return rc;                      /* n == 0 returns 0, not alpha (level1float32_sdsdot.go:25-28) */
+  *result = alpha + (float)d;
+  return ORC_OK;
+}

@@ -46,6 +46,8 @@ def lib():
         L.orc_saxpy.argtypes = [i, f, fp, sz, i, fp, sz, i]
         L.orc_sdot.argtypes = [i, fp, sz, i, fp, sz, i, fp]
         L.orc_sscal.argtypes = [i, f, fp, sz, i]
+        L.orc_dsdot.argtypes = [i, fp, sz, i, fp, sz, i, dp]
+        L.orc_sdsdot.argtypes = [i, f, fp, sz, i, fp, sz, i, fp]
         L.orc_daxpy.argtypes = [i, d, dp, sz, i, dp, sz, i]
         L.orc_ddot.argtypes = [i, dp, sz, i, dp, sz, i, dp]
         L.orc_dscal.argtypes = [i, d, dp, sz, i]
@@ -226,6 +228,20 @@ def fused_gemm_bias_gelu(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, b
                                         beta, _p(c, C.c_float), ldc, _p(bias, C.c_float),
                                         0 if route == "scalar" else 1, threads))
     return c
+
+
+def dsdot(n, x, incx, y, incy):
+    x, y = _f32(x), _f32(y)
+    r = C.c_double(0)
+    _chk(lib().orc_dsdot(n, _p(x, C.c_float), x.size, incx, _p(y, C.c_float), y.size, incy, C.byref(r)))
+    return r.value
+
+
+def sdsdot(n, alpha, x, incx, y, incy):
+    x, y = _f32(x), _f32(y)
+    r = C.c_float(0)
+    _chk(lib().orc_sdsdot(n, C.c_float(alpha), _p(x, C.c_float), x.size, incx, _p(y, C.c_float), y.size, incy, C.byref(r)))
+    return np.float32(r.value)
 
 
 # ---------------------------------------------------------------- Level 2

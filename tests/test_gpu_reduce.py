@@ -195,3 +195,29 @@ def test_layer_norm_against_oracle(g, O, n, affine):
     assert float(np.max(np.abs(got - want))) <= 1e-4 + 2.0 * ref_err
     assert np.array_equal(dg.Float32(), gamma) and np.array_equal(db.Float32(), beta)
     g.Free(dx); g.Free(dg); g.Free(db)
+
+
+@pytest.mark.parametrize("n,incx,incy", [(1, 1, 1), (7, 1, 1), (1001, 1, 1), (1 << 20, 1, 1), (3_000_001, 1, 1), (300, 3, -2), (5000, -1, 2), (4099, 2, 2)])
+def test_dsdot_sdsdot(g, O, n, incx, incy):
+    """fp32 inputs, fp64 accumulation: products are exact, so GPU and reference differ only by the order of the double adds."""
+    from guda_b200.api import BlasPanic
+    x = O.uniform_f32((n - 1) * abs(incx) + 1, 500 + n % 11); y = O.uniform_f32((n - 1) * abs(incy) + 1, 501)
+    dx, dy = g.to_device(x), g.to_device(y)
+    want = O.dsdot(n, x, incx, y, incy)
+    got = g.Dsdot(n, dx, incx, dy, incy)
+    # the reference adds ~n/4 doubles per lane sequentially (error up to ~n/4 ulp of the running sum); the GPU tree is tighter.
+    # Bound both against a float64 pairwise sum of the exact products.
+    xs, ys = x[::abs(incx)][:n].astype(np.float64), y[::abs(incy)][:n].astype(np.float64)
+    if (incx < 0) != (incy < 0):
+        ys = ys[::-1]
+    exact, mag = float(np.sum(xs * ys)), float(np.sum(np.abs(xs * ys)))
+    assert abs(got - exact) <= 1e-14 * mag + 1e-15
+    assert abs(got - want) <= 1e-14 * mag + abs(want - exact) + 1e-15
+    s = g.Sdsdot(n, 2.5, dx, incx, dy, incy)
+    assert abs(float(s) - float(O.sdsdot(n, 2.5, x, incx, y, incy))) <= 2.4e-7 * max(1.0, abs(float(s)))       # one fp32 ulp
+    assert g.Dsdot(0, dx, incx, dy, incy) == 0.0 and g.Sdsdot(0, 2.5, dx, incx, dy, incy) == 0.0
+    with pytest.raises(BlasPanic, match="blas: n < 0"):
+        g.Dsdot(-1, dx, incx, dy, incy)
+    with pytest.raises(BlasPanic, match="blas: insufficient length of x"):
+        g.Dsdot(n + 1, dx, incx, dy, incy)
+    g.Free(dx); g.Free(dy)

@@ -113,3 +113,23 @@ def test_layer_norm_matches_float64_model():
     assert np.allclose(got, want, rtol=1e-4, atol=1e-4)                 # reference_test.go:338: tol * 10
     plain = O.layer_norm(x.copy(), None, beta, 1e-5)                    # gamma or beta missing: no affine step (fused.go:299)
     assert np.allclose(plain, (x64 - x64.mean()) / np.sqrt(x64.var() + 1e-5), rtol=1e-4, atol=1e-4)
+
+
+def test_dsdot_sdsdot_oracle():
+    """compute/level1float32_dsdot.go / _sdsdot.go: exact products, double accumulation; panics in the reference's order."""
+    for n, incx, incy in [(1, 1, 1), (7, 1, 1), (8, 1, 1), (1001, 1, 1), (300, 3, -2), (100, -1, 2)]:
+        x = O.uniform_f32(n * abs(incx) + 1, 5); y = O.uniform_f32(n * abs(incy) + 1, 6)
+        xs = x[:(n - 1) * abs(incx) + 1:abs(incx)][:n].astype(np.float64); ys = y[:(n - 1) * abs(incy) + 1:abs(incy)][:n].astype(np.float64)
+        if incx < 0: xs = xs[::-1]
+        if incy < 0: ys = ys[::-1]
+        want = float(np.dot(xs, ys))
+        got = O.dsdot(n, x, incx, y, incy)
+        assert abs(got - want) <= 1e-13 * max(1.0, float(np.sum(np.abs(xs * ys))))
+        assert O.sdsdot(n, 2.5, x, incx, y, incy) == np.float32(np.float32(2.5) + np.float32(got))
+    one = np.ones(4, np.float32)
+    assert O.dsdot(0, one, 1, one, 1) == 0.0 and O.sdsdot(0, 2.5, one, 1, one, 1) == 0.0
+    for args, msg in [((3, one, 0, one, 1), "blas: zero x index increment"), ((3, one, 1, one, 0), "blas: zero y index increment"),
+                      ((-1, one, 1, one, 1), "blas: n < 0"), ((5, one, 1, one, 1), "blas: insufficient length of x"),
+                      ((3, one, 1, one, 2), "blas: insufficient length of y")]:
+        with pytest.raises(O.OraclePanic, match=msg):
+            O.dsdot(*args)

@@ -429,6 +429,25 @@ def Sgemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy, stream=None):    #
         capi.check(_L().guda_memset(y.ptr + 4 * n, 0, 4 * (_len(y, 4) - n), _sh(stream)), "Sgemv")
 
 
+def Dgemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy, stream=None):    # compute/level2float64.go:232-300
+    if m >= 0 and n >= 0 and lda >= max(1, n) and incx != 0 and incy != 0 and m > 0 and n > 0:
+        lenx, leny = (m, n) if trans else (n, m)
+        lx, ly = _len(x, 8), _len(y, 8)
+        if (incx > 0 and (lenx - 1) * incx >= lx) or (incx < 0 and (1 - lenx) * incx >= lx): raise BlasPanic("blas: insufficient length of x")
+        if (incy > 0 and (leny - 1) * incy >= ly) or (incy < 0 and (1 - leny) * incy >= ly): raise BlasPanic("blas: insufficient length of y")
+        if _len(a, 8) < lda * (m - 1) + n: raise BlasPanic("blas: insufficient length of a")
+    capi.check(_L().guda_dgemv(int(bool(trans)), m, n, alpha, a.ptr, lda, x.ptr, incx, beta, y.ptr, incy, _sh(stream)), "Dgemv")
+
+
+def Dger(m, n, alpha, x, incx, y, incy, a, lda, stream=None):                  # compute/level2float64.go:24-65
+    if m >= 0 and n >= 0 and lda >= max(1, n) and incx != 0 and incy != 0 and m > 0 and n > 0:
+        lx, ly = _len(x, 8), _len(y, 8)
+        if (incx > 0 and lx <= (m - 1) * incx) or (incx < 0 and lx <= (1 - m) * incx): raise BlasPanic("blas: insufficient length of x")
+        if (incy > 0 and ly <= (n - 1) * incy) or (incy < 0 and ly <= (1 - n) * incy): raise BlasPanic("blas: insufficient length of y")
+        if _len(a, 8) < lda * (m - 1) + n: raise BlasPanic("blas: insufficient length of a")
+    capi.check(_L().guda_dger(m, n, alpha, x.ptr, incx, y.ptr, incy, a.ptr, lda, _sh(stream)), "Dger")
+
+
 def Sger(m, n, alpha, x, incx, y, incy, a, lda, stream=None):                  # compute/level2float32.go:24-65
     if m >= 0 and n >= 0 and lda >= max(1, n) and incx != 0 and incy != 0 and m > 0 and n > 0:
         lx, ly = _len(x, 4), _len(y, 4)

@@ -88,6 +88,8 @@ SIGNATURES = {
     "guda_add_bias_gelu": (i, [vp, vp, i, i, vp]),
     "guda_add_bias_relu": (i, [vp, vp, i, i, vp]),
     "guda_sgemv": (i, [i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
+    "guda_dgemv": (i, [i, i, i, d, vp, i, vp, i, d, vp, i, vp]),
+    "guda_dger": (i, [i, i, d, vp, i, vp, i, vp, i, vp]),
     "guda_sger": (i, [i, i, f, vp, i, vp, i, vp, i, vp]),
     "guda_dsdot": (i, [i, vp, i, vp, i, dp, vp]),
     "guda_sdsdot": (i, [i, f, vp, i, vp, i, fp, vp]),

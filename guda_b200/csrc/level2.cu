@@ -359,6 +359,224 @@ __global__ void __launch_bounds__(256) sger_scalar_kernel(int m, int n, float al
   }
 }
 
+// ---------------------------------------------------------------------------------------------------- fp64: Dgemv / Dger
+// compute/asm/f64/gemvN_avx2_amd64.s: per row four FMA lanes (lane l owns the elements j = l mod 4 of the 4-blocked body), folded
+// (l0+l2)+(l1+l3), unfused remainder, y_i = fl(alpha*s) + (beta == 0 ? 0 : fl(y_i*beta)).  Four threads per row, eight rows per
+// warp: each lane replays its AVX lane's chain, the folds are shuffles by 2 and 1.
+__global__ void __launch_bounds__(256) dgemv_n_unit_kernel(int m, int n, double alpha, const double* __restrict__ a, long long lda,
+                                                           const double* __restrict__ x, double beta, double* __restrict__ y, long long incy,
+                                                           long long ky) {
+  const long long row = (long long)blockIdx.x * 64 + (threadIdx.x >> 2);
+  const int l = threadIdx.x & 3;
+  const double* ap = a + (row < m ? row : m - 1) * lda;
+  double acc = 0.0;
+  const int n4 = n >> 2;
+  int it = 0;
+  for (; it + 16 <= n4; it += 16) {
+    double av[16], xv[16];
+#pragma unroll
+    for (int u = 0; u < 16; u++) { av[u] = ap[4 * (it + u) + l]; xv[u] = x[4 * (it + u) + l]; }
+#pragma unroll
+    for (int u = 0; u < 16; u++) acc = __fma_rn(av[u], xv[u], acc);
+  }
+  for (; it < n4; it++) acc = __fma_rn(ap[4 * it + l], x[4 * it + l], acc);
+  const double v = __dadd_rn(acc, __shfl_down_sync(0xffffffffu, acc, 2));      // l = 0: l0 + l2, l = 1: l1 + l3
+  double s = __dadd_rn(v, __shfl_down_sync(0xffffffffu, v, 1));                // l = 0: (l0 + l2) + (l1 + l3)
+  if (l == 0 && row < m) {
+    for (int j = n4 << 2; j < n; j++) s = __dadd_rn(s, __dmul_rn(ap[j], x[j]));
+    double* yp = y + ky + row * incy;
+    const double ys = beta == 0.0 ? 0.0 : __dmul_rn(*yp, beta);
+    *yp = __dadd_rn(__dmul_rn(alpha, s), ys);
+  }
+}
+
+// incX != 1: one unfused scalar chain per row, then the same fold with empty upper lanes ((s + 0) + (0 + 0))
+__global__ void __launch_bounds__(128) dgemv_n_inc_kernel(int m, int n, double alpha, const double* __restrict__ a, long long lda,
+                                                          const double* __restrict__ x, long long incx, long long kx, double beta,
+                                                          double* __restrict__ y, long long incy, long long ky) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const double* row = a + i * lda;
+  const double* px = x + kx;
+  double s = 0.0;
+  for (int j = 0; j < n; j++, px += incx) s = __dadd_rn(s, __dmul_rn(row[j], px[0]));
+  s = __dadd_rn(__dadd_rn(s, 0.0), 0.0);
+  double* yp = y + ky + i * incy;
+  const double ys = beta == 0.0 ? 0.0 : __dmul_rn(*yp, beta);
+  *yp = __dadd_rn(__dmul_rn(alpha, s), ys);
+}
+
+// compute/asm/f64/gemvT_amd64.s: per column the sequential unfused chain y_j += fl(fl(alpha*x_i) * a_ij) in row order.  One thread
+// per column (coalesced across columns), 32 rows of loads in flight.
+__global__ void __launch_bounds__(64) dgemv_t_kernel(int m, int n, double alpha, const double* __restrict__ a, long long lda,
+                                                      const double* __restrict__ x, long long incx, long long kx, double beta,
+                                                      double* __restrict__ y, long long incy, long long ky) {
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  double* yp = y + ky + j * incy;
+  double yv = beta == 0.0 ? 0.0 : (beta == 1.0 ? *yp : __dmul_rn(*yp, beta));
+  const double* ap = a + j;
+  const double* px = x + kx;
+  int i = 0;
+  for (; i + 32 <= m; i += 32) {
+    double av[32];
+#pragma unroll
+    for (int u = 0; u < 32; u++) av[u] = ap[(long long)(i + u) * lda];
+#pragma unroll
+    for (int u = 0; u < 32; u++) yv = __dadd_rn(yv, __dmul_rn(__dmul_rn(alpha, px[(long long)(i + u) * incx]), av[u]));
+  }
+  for (; i < m; i++) yv = __dadd_rn(yv, __dmul_rn(__dmul_rn(alpha, px[(long long)i * incx]), ap[(long long)i * lda]));
+  *yp = yv;
+}
+
+
+// The fp64 GemvT on the same two-warp ring as sgemv_t_kernel (one column per lane, 256-byte strips, 8 stages of 32 rows): the
+// producer stages 16-byte chunks (two doubles) and the tile's 32 x values, the consumer holds tile k+1 in registers while it runs
+// tile k's 32 dependent adds.  Needs 16-byte aligned rows (a % 16 == 0, lda even); dgemv_t_kernel above is the fallback.
+constexpr int DT_STAGES = 8;
+constexpr int DT_STAGE_DOUBLES = GT_ROWS * 32 + GT_ROWS;
+
+__device__ __forceinline__ void cp_async_8(void* smem, const void* gmem, int src_bytes) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(s), "l"(gmem), "r"(src_bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(64) dgemv_t_ring_kernel(int m, int n, double alpha, const double* __restrict__ a, long long lda,
+                                                          const double* __restrict__ x, long long incx, long long kx, double beta,
+                                                          double* __restrict__ y, long long incy, long long ky) {
+  extern __shared__ __align__(16) double dt_smem[];                // [DT_STAGES][DT_STAGE_DOUBLES], then full[], empty[]
+  uint64_t* full = reinterpret_cast<uint64_t*>(dt_smem + (size_t)DT_STAGES * DT_STAGE_DOUBLES);
+  uint64_t* empty = full + DT_STAGES;
+  const int lane = threadIdx.x & 31;
+  const int j0 = blockIdx.x * 32;
+  const int ntiles = (m + GT_ROWS - 1) / GT_ROWS;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < DT_STAGES; s++) {
+      mbar_init(&full[s], 32);
+      mbar_init(&empty[s], 1);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  if (threadIdx.x >= 32) {
+    // ---------------- producer warp: 16 lanes cover one 256-byte tile row, one instruction two rows, 16 instructions a tile
+    const bool cols_full = j0 + 32 <= n;
+    const int vr = lane >> 4, vc = (lane & 15) * 2;
+    const double* vsrc = a + (long long)vr * lda + j0 + vc;
+    const double* xsrc = x + kx + (long long)lane * incx;
+    const unsigned smem_base = smem_u32(dt_smem);
+    const long long qstep = 2 * lda;
+#pragma unroll 1
+    for (int tile = 0; tile < ntiles; tile++) {
+      const int st = tile % DT_STAGES, use = tile / DT_STAGES;
+      if (use > 0) mbar_wait(&empty[st], (use - 1) & 1);
+      double* dst = dt_smem + (size_t)st * DT_STAGE_DOUBLES;
+      const int i0 = tile * GT_ROWS;
+      {
+        const bool ok = i0 + lane < m;
+        cp_async_8(dst + GT_ROWS * 32 + lane, ok ? xsrc : x, ok ? 8 : 0);
+        xsrc += GT_ROWS * incx;
+      }
+      if (cols_full && i0 + GT_ROWS <= m) {
+        unsigned d = smem_base + (unsigned)((st * DT_STAGE_DOUBLES + vr * 32 + vc) * 8);
+        const double* p = vsrc;
+#pragma unroll
+        for (int q = 0; q < 16; q++) {
+          cp_async_16_full(d, p);
+          d += 2 * 32 * 8;
+          p += qstep;
+        }
+      } else {
+#pragma unroll 4
+        for (int q = 0; q < 16; q++) {
+          const int r = q * 2 + vr;
+          const int rem = n - (j0 + vc);
+          const bool ok = (i0 + r < m) && rem > 0;
+          cp_async_16(dst + r * 32 + vc, ok ? vsrc + (long long)q * qstep : a, ok ? (rem >= 2 ? 16 : 8) : 0);
+        }
+      }
+      vsrc += (long long)GT_ROWS * lda;
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[st])) : "memory");
+    }
+    cp_async_wait_all();
+    return;
+  }
+
+  // ---------------- consumer warp
+  const int j = j0 + lane;
+  double* yp = y + ky + (long long)j * incy;
+  double yv = 0.0;
+  if (j < n && beta != 0.0) yv = beta == 1.0 ? *yp : __dmul_rn(*yp, beta);
+  auto load = [&](int tile, double (&v)[GT_ROWS]) {
+    const int st = tile % DT_STAGES;
+    mbar_wait(&full[st], (tile / DT_STAGES) & 1);
+    const double* stage = dt_smem + (size_t)st * DT_STAGE_DOUBLES;
+#pragma unroll
+    for (int r = 0; r < GT_ROWS; r++) v[r] = stage[r * 32 + lane];
+  };
+  auto release = [&](int tile) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[tile % DT_STAGES]);
+  };
+  auto step = [&](double xr, double v) { yv = __dadd_rn(yv, __dmul_rn(__dmul_rn(alpha, xr), v)); };
+  // the x values stay in the stage (the tile's 64 registers per buffer are all a double-precision chain can afford) and are read
+  // as broadcast 128-bit loads while the chain runs; the stage is released after the chain either way
+  auto chain = [&](int tile, const double (&v)[GT_ROWS]) {
+    const double2* xs = reinterpret_cast<const double2*>(dt_smem + (size_t)(tile % DT_STAGES) * DT_STAGE_DOUBLES + GT_ROWS * 32);
+#pragma unroll
+    for (int r2 = 0; r2 < GT_ROWS / 2; r2++) {
+      const double2 x2 = xs[r2];
+      step(x2.x, v[2 * r2]); step(x2.y, v[2 * r2 + 1]);
+    }
+  };
+  const int nfull = m / GT_ROWS;
+  double va[GT_ROWS], vb[GT_ROWS];
+  int tile = 0;
+  if (nfull > 0) load(0, va);
+#pragma unroll 1
+  for (; tile + 2 <= nfull; tile += 2) {
+    load(tile + 1, vb);
+    chain(tile, va);
+    release(tile);
+    if (tile + 2 < nfull) load(tile + 2, va);
+    chain(tile + 1, vb);
+    release(tile + 1);
+  }
+  if (tile < nfull) {
+    chain(tile, va);
+    release(tile);
+    tile++;
+  }
+  if (tile < ntiles) {
+    const int st = tile % DT_STAGES;
+    mbar_wait(&full[st], (tile / DT_STAGES) & 1);
+    const double* stage = dt_smem + (size_t)st * DT_STAGE_DOUBLES;
+    const int rows = m - tile * GT_ROWS;
+    for (int r = 0; r < rows; r++) step(stage[GT_ROWS * 32 + r], stage[r * 32 + lane]);
+  }
+  if (j < n) *yp = yv;
+}
+
+// compute/asm/f64/ger_amd64.s: a_ij = fl(fl(alpha*x_i) * y_j) + a_ij (MULPD + ADDPD in every block shape)
+__global__ void __launch_bounds__(256) dger_kernel(int m, int n, double alpha, const double* __restrict__ x, long long incx, long long kx,
+                                                   const double* __restrict__ y, long long incy, long long ky, double* __restrict__ a,
+                                                   long long lda) {
+  const int j = blockIdx.y * 32 + (threadIdx.x & 31);
+  const int i0 = blockIdx.x * 32 + (threadIdx.x >> 5);
+  if (j >= n) return;
+  const double yv = y[ky + (long long)j * incy];
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const int i = i0 + 8 * q;
+    if (i < m) {
+      const double t = __dmul_rn(alpha, x[kx + (long long)i * incx]);
+      double* p = a + (long long)i * lda + j;
+      *p = __dadd_rn(__dmul_rn(t, yv), *p);
+    }
+  }
+}
+
 // Columns per lane for GemvT.  The chains are sequential in m, so the kernel's time is ~ m * (cycles per row of the consumer warp)
 // until n supplies more strips than the GPU has schedulers (592); past that, two columns per lane (fewer instructions per byte)
 // is what reaches the HBM roofline.  Measured on B200: C = 1 wins for n <= 8192, C = 2 from n = 16384 up.
@@ -414,6 +632,57 @@ int guda_sgemv(int trans, int m, int n, float alpha, const float* a, int lda, co
   else GT_LAUNCH(1, 8);
 #undef GT_LAUNCH
   return check_launch("Sgemv");
+}
+
+int guda_dgemv(int trans, int m, int n, double alpha, const double* a, int lda, const double* x, int incx, double beta, double* y, int incy,
+               guda_stream_t stream) {
+  if (m < 0) GUDA_PANIC("blas: m < 0");
+  if (n < 0) GUDA_PANIC("blas: n < 0");
+  if (lda < (n > 1 ? n : 1)) GUDA_PANIC("blas: bad leading dimension of A");
+  if (incx == 0) GUDA_PANIC("blas: zero x index increment");
+  if (incy == 0) GUDA_PANIC("blas: zero y index increment");
+  if (m == 0 || n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!a || !x || !y) return set_error(GUDA_ERR_INVALID_ARG, "Dgemv: null pointer");
+  if (alpha == 0.0 && beta == 1.0) return GUDA_OK;
+  const int lenx = trans ? m : n, leny = trans ? n : m;
+  if (alpha == 0.0) return guda_dscal(leny, beta, y, incy > 0 ? incy : -incy, stream);      // compute/level2float64.go:279-287
+  cudaStream_t s = native(stream);
+  const long long kx = incx < 0 ? -(long long)(lenx - 1) * incx : 0, ky = incy < 0 ? -(long long)(leny - 1) * incy : 0;
+  if (!trans) {
+    if (incx == 1) dgemv_n_unit_kernel<<<(unsigned)(((long long)m + 63) / 64), 256, 0, s>>>(m, n, alpha, a, lda, x, beta, y, incy, ky);
+    else dgemv_n_inc_kernel<<<(unsigned)((m + 127) / 128), 128, 0, s>>>(m, n, alpha, a, lda, x, incx, kx, beta, y, incy, ky);
+  } else if ((((uintptr_t)a & 15) == 0) && (lda % 2 == 0) && !getenv("GUDA_DGEMVT_SIMPLE")) {
+    const size_t smem = (size_t)DT_STAGES * (DT_STAGE_DOUBLES * sizeof(double) + 16);
+    static bool attr_done = false;
+    if (!attr_done) {
+      GUDA_CUDA(cudaFuncSetAttribute(dgemv_t_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_done = true;
+    }
+    dgemv_t_ring_kernel<<<(unsigned)((n + 31) / 32), 64, smem, s>>>(m, n, alpha, a, lda, x, incx, kx, beta, y, incy, ky);
+  } else {
+    dgemv_t_kernel<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(m, n, alpha, a, lda, x, incx, kx, beta, y, incy, ky);
+  }
+  return check_launch("Dgemv");
+}
+
+int guda_dger(int m, int n, double alpha, const double* x, int incx, const double* y, int incy, double* a, int lda, guda_stream_t stream) {
+  if (m < 0) GUDA_PANIC("blas: m < 0");
+  if (n < 0) GUDA_PANIC("blas: n < 0");
+  if (lda < (n > 1 ? n : 1)) GUDA_PANIC("blas: bad leading dimension of A");
+  if (incx == 0) GUDA_PANIC("blas: zero x index increment");
+  if (incy == 0) GUDA_PANIC("blas: zero y index increment");
+  if (m == 0 || n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!a || !x || !y) return set_error(GUDA_ERR_INVALID_ARG, "Dger: null pointer");
+  if (alpha == 0.0) return GUDA_OK;
+  const long long kx = incx < 0 ? -(long long)(m - 1) * incx : 0, ky = incy < 0 ? -(long long)(n - 1) * incy : 0;
+  dim3 grid((unsigned)((m + 31) / 32), (unsigned)((n + 31) / 32));
+  if (grid.y > 65535u) return set_error(GUDA_ERR_INVALID_ARG, "Dger: n too large for one launch");
+  dger_kernel<<<grid, 256, 0, native(stream)>>>(m, n, alpha, x, incx, kx, y, incy, ky, a, lda);
+  return check_launch("Dger");
 }
 
 int guda_sger(int m, int n, float alpha, const float* x, int incx, const float* y, int incy, float* a, int lda, guda_stream_t stream) {

@@ -172,6 +172,11 @@ int guda_sgemm_host(int trans_a, int trans_b, int m, int n, int k, float alpha, 
 int guda_sgemv(int trans, int m, int n, float alpha, const float* a, int lda, const float* x, int incx, float beta, float* y, int incy,
                guda_stream_t stream);
 int guda_sger(int m, int n, float alpha, const float* x, int incx, const float* y, int incy, float* a, int lda, guda_stream_t stream);
+/* fp64 twins: compute/level2float64.go:232-300 Dgemv, :24-65 Dger; kernels compute/asm/f64/gemvN_avx2_amd64.s, gemvT_amd64.s,
+ * ger_amd64.s.  Bit-identical to the reference's AVX2+FMA route (4 FMA lanes per row for NoTrans, unfused chains otherwise). */
+int guda_dgemv(int trans, int m, int n, double alpha, const double* a, int lda, const double* x, int incx, double beta, double* y, int incy,
+               guda_stream_t stream);
+int guda_dger(int m, int n, double alpha, const double* x, int incx, const double* y, int incy, double* a, int lda, guda_stream_t stream);
 
 /* ---- Reductions: reduce.go:13-56 DevicePtr.Sum / SumSquares / Max / Min / ArgMax / ArgMin over x[0..n)
  * (kernels compute/asm/f32/sum_amd64.s, reduce_avx2_amd64.s) and Isamax (compute/level1float32.go:89-130).  Results go to HOST

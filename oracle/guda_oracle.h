@@ -94,6 +94,11 @@ void orc_f32_gemv(int trans, int m, int n, float alpha, const float* a, int lda,
                   float beta, float* y, size_t leny, int incy);   /* package f32's GemvN/GemvT: no checks, no alpha == 0 shortcut */
 int orc_sgemv(int trans, int m, int n, float alpha, const float* a, size_t lena, int lda, const float* x, size_t lenx, int incx,
               float beta, float* y, size_t leny, int incy);
+void orc_f64_gemv(int trans, int m, int n, double alpha, const double* a, int lda, const double* x, int incx, double beta, double* y, int incy);
+int orc_dgemv(int trans, int m, int n, double alpha, const double* a, size_t lena, int lda, const double* x, size_t lenx, int incx,
+              double beta, double* y, size_t leny, int incy);                       /* compute/level2float64.go:232-300 */
+int orc_dger(int m, int n, double alpha, const double* x, size_t lenx, int incx, const double* y, size_t leny, int incy,
+             double* a, size_t lena, int lda);                                      /* compute/level2float64.go:24-65 */
 int orc_sger(int m, int n, float alpha, const float* x, size_t lenx, int incx, const float* y, size_t leny, int incy,
              float* a, size_t lena, int lda);
 

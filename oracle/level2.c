@@ -83,3 +83,85 @@ int orc_sger(int m, int n, float alpha, const float* x, size_t lenx, int incx, c
   }
   return ORC_OK;
 }
+
+/* ------------------------------------------------------------------ fp64: Dgemv / Dger
+ * compute/level2float64.go:232-300 (Dgemv), :24-65 (Dger); kernels compute/asm/f64/gemvN_avx2_amd64.s (GemvNAVX2: per row 4 FMA
+ * lanes over n/4 groups when incX == 1, (l0+l2)+(l1+l3), unfused remainder; incX != 1: one unfused scalar chain, then the same
+ * fold with zero upper lanes; y_i = fl(alpha*s) + (beta == 0 ? 0 : fl(y_i*beta))), compute/asm/f64/gemvT_amd64.s (beta == 1: keep,
+ * beta == 0: clear n, else scale; then per column the sequential unfused chain y_j += fl(fl(alpha*x_i) * a_ij) in row order) and
+ * compute/asm/f64/ger_amd64.s (a_ij = fl(fl(alpha*x_i)*y_j) + a_ij).  Negative increments follow the BLAS definition. */
+#include <math.h>
+void orc_f64_gemv(int trans, int m, int n, double alpha, const double* a, int lda, const double* x, int incx,
+                  double beta, double* y, int incy) {
+  int lenx = trans ? m : n, leny = trans ? n : m;
+  long long kx = incx < 0 ? -(long long)(lenx - 1) * incx : 0, ky = incy < 0 ? -(long long)(leny - 1) * incy : 0;
+  if (!trans) {
+    for (int i = 0; i < m; i++) { double* yp = y + ky + (long long)i * incy; *yp = beta == 0 ? 0.0 : *yp * beta; }
+    for (int i = 0; i < m; i++) {
+      const double* row = a + (size_t)lda * i;
+      double l[4] = {0, 0, 0, 0};
+      int j = 0;
+      double s;
+      if (incx == 1) {
+        for (; j + 4 <= n; j += 4)
+          for (int q = 0; q < 4; q++) l[q] = fma(row[j + q], x[j + q], l[q]);
+        s = (l[0] + l[2]) + (l[1] + l[3]);
+        for (; j < n; j++) { double p = row[j] * x[j]; s = s + p; }
+      } else {
+        const double* px = x + kx;
+        for (; j < n; j++, px += incx) { double p = row[j] * px[0]; l[0] = l[0] + p; }
+        s = (l[0] + 0.0) + (0.0 + 0.0);
+      }
+      double as = alpha * s;
+      double* yp = y + ky + (long long)i * incy;
+      *yp = as + *yp;
+    }
+    return;
+  }
+  if (beta == 0) { for (int j = 0; j < n; j++) y[ky + (long long)j * incy] = 0.0; }
+  else if (beta != 1) { for (int j = 0; j < n; j++) { double* yp = y + ky + (long long)j * incy; *yp = *yp * beta; } }
+  for (int i = 0; i < m; i++) {
+    const double* row = a + (size_t)lda * i;
+    double t = alpha * x[kx + (long long)i * incx];
+    for (int j = 0; j < n; j++) { double p = t * row[j]; double* yp = y + ky + (long long)j * incy; *yp = *yp + p; }
+  }
+}
+
+int orc_dgemv(int trans, int m, int n, double alpha, const double* a, size_t lena, int lda, const double* x, size_t lenx_, int incx,
+              double beta, double* y, size_t leny_, int incy) {
+  if (m < 0) return ORC_M_LT0;
+  if (n < 0) return ORC_N_LT0;
+  if (lda < imax2(1, n)) return ORC_BAD_LDA;
+  if (incx == 0) return ORC_ZERO_INCX;
+  if (incy == 0) return ORC_ZERO_INCY;
+  int lenx = trans ? m : n, leny = trans ? n : m;
+  if (m == 0 || n == 0) return ORC_OK;
+  if ((incx > 0 && (long long)(lenx - 1) * incx >= (long long)lenx_) || (incx < 0 && (long long)(1 - lenx) * incx >= (long long)lenx_)) return ORC_SHORT_X;
+  if ((incy > 0 && (long long)(leny - 1) * incy >= (long long)leny_) || (incy < 0 && (long long)(1 - leny) * incy >= (long long)leny_)) return ORC_SHORT_Y;
+  if ((long long)lena < (long long)lda * (m - 1) + n) return ORC_SHORT_A;
+  if (alpha == 0 && beta == 1) return ORC_OK;
+  if (alpha == 0) return orc_dscal(leny, beta, y, leny_, incy > 0 ? incy : -incy);
+  orc_f64_gemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy);
+  return ORC_OK;
+}
+
+int orc_dger(int m, int n, double alpha, const double* x, size_t lenx, int incx, const double* y, size_t leny, int incy,
+             double* a, size_t lena, int lda) {
+  if (m < 0) return ORC_M_LT0;
+  if (n < 0) return ORC_N_LT0;
+  if (lda < imax2(1, n)) return ORC_BAD_LDA;
+  if (incx == 0) return ORC_ZERO_INCX;
+  if (incy == 0) return ORC_ZERO_INCY;
+  if (m == 0 || n == 0) return ORC_OK;
+  if ((incx > 0 && (long long)lenx <= (long long)(m - 1) * incx) || (incx < 0 && (long long)lenx <= (long long)(1 - m) * incx)) return ORC_SHORT_X;
+  if ((incy > 0 && (long long)leny <= (long long)(n - 1) * incy) || (incy < 0 && (long long)leny <= (long long)(1 - n) * incy)) return ORC_SHORT_Y;
+  if ((long long)lena < (long long)lda * (m - 1) + n) return ORC_SHORT_A;
+  if (alpha == 0) return ORC_OK;
+  long long kx = incx < 0 ? -(long long)(m - 1) * incx : 0, ky = incy < 0 ? -(long long)(n - 1) * incy : 0;
+  for (int i = 0; i < m; i++) {
+    double t = alpha * x[kx + (long long)i * incx];
+    double* row = a + (size_t)lda * i;
+    for (int j = 0; j < n; j++) { double p = t * y[ky + (long long)j * incy]; row[j] = p + row[j]; }
+  }
+  return ORC_OK;
+}

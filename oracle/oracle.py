@@ -71,6 +71,8 @@ def lib():
         L.orc_gemm_f16.argtypes = [i, i, i, i, i, f, u16p, i, u16p, i, f, u16p, i, i]
         L.orc_sgemv.argtypes = [i, i, i, f, fp, sz, i, fp, sz, i, f, fp, sz, i]
         L.orc_f32_gemv.argtypes = [i, i, i, f, fp, i, fp, i, f, fp, sz, i]; L.orc_f32_gemv.restype = None
+        L.orc_dgemv.argtypes = [i, i, i, d, dp, sz, i, dp, sz, i, d, dp, sz, i]
+        L.orc_dger.argtypes = [i, i, d, dp, sz, i, dp, sz, i, dp, sz, i]
         L.orc_sger.argtypes = [i, i, f, fp, sz, i, fp, sz, i, fp, sz, i]
         for name in ("orc_ssum", "orc_ssumsq", "orc_smax", "orc_smin"):
             getattr(L, name).argtypes = [fp, sz]; getattr(L, name).restype = f
@@ -252,6 +254,28 @@ def sgemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy):
     _chk(lib().orc_sgemv(int(trans), m, n, C.c_float(alpha), _p(a, C.c_float), C.c_size_t(a.size), lda, _p(x, C.c_float), C.c_size_t(x.size), incx,
                          C.c_float(beta), _p(y, C.c_float), C.c_size_t(y.size), incy))
     return y
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def dgemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy):
+    """In place on y (float64 array)."""
+    assert y.dtype == np.float64 and y.flags.c_contiguous
+    a, x = _f64(a), _f64(x)
+    _chk(lib().orc_dgemv(int(trans), m, n, C.c_double(alpha), _p(a, C.c_double), C.c_size_t(a.size), lda, _p(x, C.c_double), C.c_size_t(x.size), incx,
+                         C.c_double(beta), _p(y, C.c_double), C.c_size_t(y.size), incy))
+    return y
+
+
+def dger(m, n, alpha, x, incx, y, incy, a, lda):
+    """In place on a (float64 array)."""
+    assert a.dtype == np.float64 and a.flags.c_contiguous
+    x, y = _f64(x), _f64(y)
+    _chk(lib().orc_dger(m, n, C.c_double(alpha), _p(x, C.c_double), C.c_size_t(x.size), incx, _p(y, C.c_double), C.c_size_t(y.size), incy,
+                        _p(a, C.c_double), C.c_size_t(a.size), lda))
+    return a
 
 
 def f32_gemv(trans, m, n, alpha, a, lda, x, incx, beta, y, incy):

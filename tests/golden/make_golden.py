@@ -156,6 +156,13 @@ def extract_struct_slice(path, varname):
     return Parser(tokenize(body)).composite()
 
 
+def Fraction_eval(expr):
+    """Exact rational evaluation of a Go constant expression made of decimal literals, + - * and parentheses."""
+    from fractions import Fraction
+    expr = re.sub(r"(\d+\.?\d*)", lambda m: "Fraction('%s')" % m.group(1), expr)
+    return eval(expr, {"Fraction": Fraction})
+
+
 def extract_reduce_cases(path):
     """reduce_test.go: testSum/testMax/testMin/testArgMax/testArgMin/testSumSquares each hold a table of
     {"name", []float32{...} | makeSequence(k), expected} rows."""
@@ -232,6 +239,14 @@ def main():
     json.dump({"source": "compute/asm/f32/gemv_test.go:35-506 (SgemvCases; harness :508-615, tol 1e-6 abs-or-rel); "
                          "compute/asm/f32/ge_test.go:14-144 (gerTests; harness :146-219, alpha 1 unit / 3.5 strided)",
                "gemv": gemv, "ger": ger}, open(os.path.join(OUT, "level2_cases.json"), "w"), indent=1)
+    dgv = extract_var(os.path.join(REF, "blas/testblas/dgemv.go"), "DgemvCases")
+    for c in dgv:
+        c["tA"] = c["tA"]["_expr"] if isinstance(c["tA"], dict) else c["tA"]
+        for sub in c["Subcases"]:            # a few answers are written as constant expressions ("40.8 * 8 - 6 * 7"): Go folds them exactly
+            sub["ans"] = [float(Fraction_eval(v["_expr"])) if isinstance(v, dict) else v for v in sub["ans"]]
+    assert len(dgv) == 15, len(dgv)
+    json.dump({"source": "blas/testblas/dgemv.go:34-629 (DgemvCases; harness :631-683, dSliceTolEqual 1e-14 normalised)", "cases": dgv},
+              open(os.path.join(OUT, "dgemv_cases.json"), "w"), indent=1)
     red = extract_reduce_cases(os.path.join(REF, "reduce_test.go"))
     assert [len(red[k]) for k in ("testSum", "testMax", "testMin", "testArgMax", "testArgMin", "testSumSquares")] == [5, 5, 5, 6, 6, 5], red
     json.dump({"source": "reduce_test.go:28-240 (tables of testSum/testMax/testMin/testArgMax/testArgMin/testSumSquares; floatEquals tol 1e-5)",

@@ -233,3 +233,68 @@ def test_sgemv_large_properties(g, O):
     assert np.array_equal(yT[cols], O.sgemv(True, m, len(cols), 1.0, subT, len(cols), xt, 1, 0.0, np.zeros(len(cols), np.float32), 1))
     ref64 = a.reshape(m, n).astype(np.float64).T @ xt.astype(np.float64)
     assert np.allclose(yT, ref64, rtol=1e-3, atol=1e-2)
+
+
+# ---------------------------------------------------------------- fp64 (Dgemv / Dger): bit-exact against the oracle
+DGEMV = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "dgemv_cases.json")))["cases"]
+
+
+def gpu_dgemv(g, trans, m, n, alpha, a, lda, x, incx, beta, y, incy):
+    da, dx, dy = g.to_device(a), g.to_device(x), g.to_device(y)
+    g.Dgemv(trans, m, n, alpha, da, lda, dx, incx, beta, dy, incy)
+    g.Synchronize()
+    out = dy.Float64()
+    assert np.array_equal(da.Float64(), a) and np.array_equal(dx.Float64(), x)
+    g.Free(da); g.Free(dx); g.Free(dy)
+    return out
+
+
+@pytest.mark.parametrize("case", DGEMV, ids=[c["Name"] for c in DGEMV])
+def test_dgemv_testblas_cases(g, O, case):
+    trans = "NoTrans" not in case["tA"]
+    a = np.array(case["A"], np.float64).ravel()
+    for sub in case["Subcases"]:
+        incx = -case["incX"] if sub.get("mulXNeg1") else case["incX"]
+        incy = -case["incY"] if sub.get("mulYNeg1") else case["incY"]
+        x = np.array(case["x"], np.float64); y = np.array(case["y"], np.float64)
+        got = gpu_dgemv(g, trans, case["m"], case["n"], sub["alpha"], a, case["n"], x, incx, sub["beta"], y, incy)
+        assert np.array_equal(got, O.dgemv(trans, case["m"], case["n"], sub["alpha"], a, case["n"], x, incx, sub["beta"], y.copy(), incy))
+        ans = np.array(sub["ans"], np.float64)
+        assert np.all(np.abs(got - ans) <= 1e-14 * np.maximum(1.0, np.maximum(np.abs(got), np.abs(ans))))
+
+
+@pytest.mark.parametrize("trans", [False, True])
+@pytest.mark.parametrize("m,n", [(1, 1), (3, 5), (9, 4), (33, 67), (64, 64), (130, 1001), (1000, 37), (257, 4099)])
+@pytest.mark.parametrize("incx,incy", [(1, 1), (2, 1), (1, -3), (-1, 2)])
+def test_dgemv_bit_exact(g, O, trans, m, n, incx, incy):
+    lda = n + (m % 3)
+    lx, ly = (m, n) if trans else (n, m)
+    a = O.uniform_f64(m * lda, 41); x = O.uniform_f64((lx - 1) * abs(incx) + 1, 42); y = O.uniform_f64((ly - 1) * abs(incy) + 1, 43)
+    for alpha, beta in [(1.0, 0.0), (0.75, -1.5), (2.0, 1.0)]:
+        want = O.dgemv(trans, m, n, alpha, a, lda, x, incx, beta, y.copy(), incy)
+        got = gpu_dgemv(g, trans, m, n, alpha, a, lda, x, incx, beta, y, incy)
+        assert np.array_equal(got, want), (alpha, beta, int(np.sum(got != want)))
+
+
+@pytest.mark.parametrize("m,n,lda", [(1, 1, 1), (5, 3, 3), (33, 64, 64), (70, 100, 101), (300, 36, 40), (513, 1028, 1028)])
+@pytest.mark.parametrize("incx,incy", [(1, 1), (2, -1), (-3, 2)])
+def test_dger_bit_exact(g, O, m, n, lda, incx, incy):
+    a = O.uniform_f64(m * lda, 44); x = O.uniform_f64((m - 1) * abs(incx) + 1, 45); y = O.uniform_f64((n - 1) * abs(incy) + 1, 46)
+    da, dx, dy = g.to_device(a), g.to_device(x), g.to_device(y)
+    g.Dger(m, n, -0.3, dx, incx, dy, incy, da, lda)
+    g.Synchronize()
+    assert np.array_equal(da.Float64(), O.dger(m, n, -0.3, x, incx, y, incy, a.copy(), lda))
+    g.Free(da); g.Free(dx); g.Free(dy)
+
+
+def test_dgemv_quick_returns_and_panics(g, O):
+    from guda_b200.api import BlasPanic
+    a, x, y = g.to_device(np.ones(6)), g.to_device(np.ones(3)), g.to_device(np.full(2, 7.0))
+    with pytest.raises(BlasPanic, match="blas: bad leading dimension of A"):
+        g.Dgemv(False, 2, 3, 1.0, a, 2, x, 1, 0.0, y, 1)
+    with pytest.raises(BlasPanic, match="blas: insufficient length of x"):
+        g.Dgemv(False, 2, 3, 1.0, a, 3, y, 1, 0.0, y, 1)
+    g.Dgemv(False, 2, 3, 0.0, a, 3, x, 1, 0.5, y, 1); g.Synchronize()
+    assert np.array_equal(y.Float64(), np.full(2, 3.5))                    # alpha == 0: Dscal(beta)
+    g.Dgemv(False, 2, 3, 1.0, a, 3, x, 1, 0.0, y, 1); g.Synchronize()
+    assert np.array_equal(y.Float64(), np.full(2, 3.0))

@@ -152,3 +152,48 @@ def test_sger_quick_returns_and_panics():
     xs = np.array([1.0000001], np.float32); ys = np.array([1.0000001], np.float32); aa = np.array([-1.0], np.float32)
     got = O.sger(1, 1, 1.0, xs, 1, ys, 1, aa.copy(), 1)[0]
     assert got == np.float32(np.float32(xs[0] * ys[0]) + aa[0])
+
+
+# ---------------------------------------------------------------- fp64
+DGEMV = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "dgemv_cases.json")))["cases"]
+
+
+@pytest.mark.parametrize("case", DGEMV, ids=[c["Name"] for c in DGEMV])
+def test_dgemv_testblas_cases(case):
+    """blas/testblas/dgemv.go: DgemvCases with the harness's increment flips (dgemvcomp :643-683), dSliceTolEqual (1e-14 normalised)."""
+    trans = "NoTrans" not in case["tA"]
+    a = np.array(case["A"], np.float64).ravel()
+    for sub in case["Subcases"]:
+        incx = -case["incX"] if sub.get("mulXNeg1") else case["incX"]
+        incy = -case["incY"] if sub.get("mulYNeg1") else case["incY"]
+        x = np.array(case["x"], np.float64); y = np.array(case["y"], np.float64)
+        O.dgemv(trans, case["m"], case["n"], sub["alpha"], a, case["n"], x, incx, sub["beta"], y, incy)
+        ans = np.array(sub["ans"], np.float64)
+        assert np.all(np.abs(y - ans) <= 1e-14 * np.maximum(1.0, np.maximum(np.abs(y), np.abs(ans)))), (case["Name"], sub)
+        assert np.array_equal(x, np.array(case["x"], np.float64))
+
+
+def test_dger_is_the_unfused_elementwise_form():
+    """compute/asm/f64/ger_amd64.s: fl(fl(alpha*x_i)*y_j) + a_ij -- numpy float64 arithmetic is the exact model."""
+    rng = np.random.default_rng(3)
+    for m, n, incx, incy in [(1, 1, 1, 1), (5, 3, 1, 1), (7, 9, 2, 3), (6, 4, -1, 1), (4, 6, 1, -2)]:
+        x = rng.standard_normal((m - 1) * abs(incx) + 1); y = rng.standard_normal((n - 1) * abs(incy) + 1); a = rng.standard_normal(m * (n + 1))
+        xs, ys = x[::abs(incx)][:m], y[::abs(incy)][:n]
+        if incx < 0: xs = xs[::-1]
+        if incy < 0: ys = ys[::-1]
+        want = a.copy().reshape(m, n + 1)
+        want[:, :n] = ((1.7 * xs)[:, None] * ys[None, :]) + want[:, :n]
+        got = O.dger(m, n, 1.7, x, incx, y, incy, a.copy(), n + 1)
+        assert np.array_equal(got, want.ravel())
+    with pytest.raises(O.OraclePanic, match="blas: insufficient length of a"):
+        O.dger(2, 3, 1.0, np.ones(2), 1, np.ones(3), 1, np.ones(5), 3)
+
+
+def test_dgemv_t_is_the_sequential_unfused_chain():
+    rng = np.random.default_rng(4)
+    m, n = 37, 21
+    a = rng.standard_normal(m * n); x = rng.standard_normal(m); y = rng.standard_normal(n)
+    want = y * 0.5
+    for i in range(m):
+        want = want + (1.3 * x[i]) * a[i * n:(i + 1) * n]                 # numpy: one rounding per operation, row order
+    assert np.array_equal(O.dgemv(True, m, n, 1.3, a, n, x, 1, 0.5, y.copy(), 1), want)

@@ -390,6 +390,80 @@ __global__ void __launch_bounds__(256) dgemv_n_unit_kernel(int m, int n, double 
   }
 }
 
+// The same chains fed through shared memory: m rows supply only 4m chains, far too few 8-byte loads in flight to cover HBM latency
+// from registers (8192^2: 2.96 TB/s).  One warp per CTA owns 8 rows; all 32 lanes stream 8 x 64-column tiles (and the tile's 64 x
+// values) with 16-byte cp.async into a DN_STAGES-deep ring, 512 contiguous bytes of one row per instruction, and lane (r, l) then
+// runs its chain out of the stage.  Rows are padded by 32 bytes so the 8 rows' 32-byte groups land in distinct banks (two
+// wavefronts per 256-byte warp read, the minimum).  Needs 16-byte aligned rows and x (else dgemv_n_unit_kernel above).
+constexpr int DN_STAGES = 6, DN_COLS = 64, DN_ROW = DN_COLS + 4, DN_STAGE_DOUBLES = 8 * DN_ROW + DN_COLS;
+
+__global__ void __launch_bounds__(32) dgemv_n_ring_kernel(int m, int n, double alpha, const double* __restrict__ a, long long lda,
+                                                          const double* __restrict__ x, double beta, double* __restrict__ y, long long incy,
+                                                          long long ky) {
+  __shared__ __align__(16) double ring[DN_STAGES * DN_STAGE_DOUBLES];
+  const int lane = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * 8;
+  const int n4 = n >> 2, nbody = n4 << 2;
+  const int ntiles = (nbody + DN_COLS - 1) / DN_COLS;
+  // producer view: lane covers the 16-byte chunk `lane` of a row's 512-byte tile segment, one instruction per row
+  const double* src[8];
+#pragma unroll
+  for (int r = 0; r < 8; r++) src[r] = a + (row0 + r < m ? row0 + r : (long long)m - 1) * lda + 2 * lane;
+  const unsigned ring_base = smem_u32(ring);
+  auto issue = [&](int tile) {
+    if (tile < ntiles) {
+      const int st = tile % DN_STAGES;
+      const int c0 = tile * DN_COLS;
+      const unsigned d = ring_base + (unsigned)((st * DN_STAGE_DOUBLES + 2 * lane) * 8);
+      if (c0 + DN_COLS <= nbody) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) cp_async_16_full(d + r * DN_ROW * 8, src[r] + c0);
+        if (lane < DN_COLS / 2) cp_async_16_full(d + 8 * DN_ROW * 8, x + c0 + 2 * lane);
+      } else if (c0 + 2 * lane < nbody) {                               // nbody is a multiple of 4: chunks are whole or absent
+#pragma unroll
+        for (int r = 0; r < 8; r++) cp_async_16_full(d + r * DN_ROW * 8, src[r] + c0);
+        cp_async_16_full(d + 8 * DN_ROW * 8, x + c0 + 2 * lane);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+#pragma unroll
+  for (int t = 0; t < DN_STAGES - 1; t++) issue(t);
+
+  const int r = lane >> 2, l = lane & 3;
+  double acc = 0.0;
+#pragma unroll 1
+  for (int tile = 0; tile < ntiles; tile++) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(DN_STAGES - 2) : "memory");
+    __syncwarp();                                                       // tile landed for every lane; all lanes are past tile - 1,
+    issue(tile + DN_STAGES - 1);                                        // whose stage this refills
+    const double* stage = ring + (size_t)(tile % DN_STAGES) * DN_STAGE_DOUBLES;
+    const double* ar = stage + r * DN_ROW + l;
+    const double* xr = stage + 8 * DN_ROW + l;
+    const int nb = min(DN_COLS / 4, n4 - tile * (DN_COLS / 4));
+    if (nb == DN_COLS / 4) {
+      double av[DN_COLS / 4], xv[DN_COLS / 4];
+#pragma unroll
+      for (int u = 0; u < DN_COLS / 4; u++) { av[u] = ar[4 * u]; xv[u] = xr[4 * u]; }
+#pragma unroll
+      for (int u = 0; u < DN_COLS / 4; u++) acc = __fma_rn(av[u], xv[u], acc);
+    } else {
+      for (int u = 0; u < nb; u++) acc = __fma_rn(ar[4 * u], xr[4 * u], acc);
+    }
+  }
+  cp_async_wait_all();
+  const double v = __dadd_rn(acc, __shfl_down_sync(0xffffffffu, acc, 2));
+  double s = __dadd_rn(v, __shfl_down_sync(0xffffffffu, v, 1));
+  const long long row = row0 + r;
+  if (l == 0 && row < m) {
+    const double* ap = a + row * lda;
+    for (int j = nbody; j < n; j++) s = __dadd_rn(s, __dmul_rn(ap[j], x[j]));
+    double* yp = y + ky + row * incy;
+    const double ys = beta == 0.0 ? 0.0 : __dmul_rn(*yp, beta);
+    *yp = __dadd_rn(__dmul_rn(alpha, s), ys);
+  }
+}
+
 // incX != 1: one unfused scalar chain per row, then the same fold with empty upper lanes ((s + 0) + (0 + 0))
 __global__ void __launch_bounds__(128) dgemv_n_inc_kernel(int m, int n, double alpha, const double* __restrict__ a, long long lda,
                                                           const double* __restrict__ x, long long incx, long long kx, double beta,
@@ -651,7 +725,9 @@ int guda_dgemv(int trans, int m, int n, double alpha, const double* a, int lda, 
   cudaStream_t s = native(stream);
   const long long kx = incx < 0 ? -(long long)(lenx - 1) * incx : 0, ky = incy < 0 ? -(long long)(leny - 1) * incy : 0;
   if (!trans) {
-    if (incx == 1) dgemv_n_unit_kernel<<<(unsigned)(((long long)m + 63) / 64), 256, 0, s>>>(m, n, alpha, a, lda, x, beta, y, incy, ky);
+    if (incx == 1 && (((uintptr_t)a | (uintptr_t)x) & 15) == 0 && lda % 2 == 0 && n >= 4 * DN_COLS && !getenv("GUDA_DGEMVN_SIMPLE"))
+      dgemv_n_ring_kernel<<<(unsigned)(((long long)m + 7) / 8), 32, 0, s>>>(m, n, alpha, a, lda, x, beta, y, incy, ky);
+    else if (incx == 1) dgemv_n_unit_kernel<<<(unsigned)(((long long)m + 63) / 64), 256, 0, s>>>(m, n, alpha, a, lda, x, beta, y, incy, ky);
     else dgemv_n_inc_kernel<<<(unsigned)((m + 127) / 128), 128, 0, s>>>(m, n, alpha, a, lda, x, incx, kx, beta, y, incy, ky);
   } else if ((((uintptr_t)a & 15) == 0) && (lda % 2 == 0) && !getenv("GUDA_DGEMVT_SIMPLE")) {
     const size_t smem = (size_t)DT_STAGES * (DT_STAGE_DOUBLES * sizeof(double) + 16);

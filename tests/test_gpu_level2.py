@@ -264,7 +264,8 @@ def test_dgemv_testblas_cases(g, O, case):
 
 
 @pytest.mark.parametrize("trans", [False, True])
-@pytest.mark.parametrize("m,n", [(1, 1), (3, 5), (9, 4), (33, 67), (64, 64), (130, 1001), (1000, 37), (257, 4099)])
+@pytest.mark.parametrize("m,n", [(1, 1), (3, 5), (9, 4), (33, 67), (64, 64), (130, 1001), (1000, 37), (257, 4099),
+                                 (8, 256), (264, 320), (519, 4098)])      # the last three: 16-byte aligned rows, the cp.async ring route of GemvN
 @pytest.mark.parametrize("incx,incy", [(1, 1), (2, 1), (1, -3), (-1, 2)])
 def test_dgemv_bit_exact(g, O, trans, m, n, incx, incy):
     lda = n + (m % 3)

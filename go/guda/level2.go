@@ -60,3 +60,45 @@ func Sger(m, n int, alpha float32, x DevicePtr, incX int, y DevicePtr, incY int,
 	return status(C.guda_sger(C.int(m), C.int(n), C.float(alpha), (*C.float)(x.ptr), C.int(incX), (*C.float)(y.ptr), C.int(incY),
 		(*C.float)(a.ptr), C.int(lda), nil), "Sger")
 }
+
+// Dgemv mirrors compute/level2float64.go:232-300 (fp64 twin of Sgemv; kernels compute/asm/f64/gemvN_avx2_amd64.s and
+// gemvT_amd64.s).  Bit-identical to the reference's AVX2+FMA route for every increment sign.  Unlike the fp32 GemvT, the
+// fp64 one clears or scales exactly n elements of y (compute/asm/f64/gemvT_amd64.s), so there is no whole-slice clear to reproduce.
+func Dgemv(trans bool, m, n int, alpha float64, a DevicePtr, lda int, x DevicePtr, incX int, beta float64, y DevicePtr, incY int) error {
+	if m >= 0 && n >= 0 && lda >= imax(1, n) && incX != 0 && incY != 0 && m > 0 && n > 0 {
+		lenX, lenY := n, m
+		if trans {
+			lenX, lenY = m, n
+		}
+		lx, ly := x.size/8, y.size/8
+		if (incX > 0 && (lenX-1)*incX >= lx) || (incX < 0 && (1-lenX)*incX >= lx) {
+			panic(shortX)
+		}
+		if (incY > 0 && (lenY-1)*incY >= ly) || (incY < 0 && (1-lenY)*incY >= ly) {
+			panic(shortY)
+		}
+		if a.size/8 < lda*(m-1)+n {
+			panic(shortA)
+		}
+	}
+	return status(C.guda_dgemv(cbool(trans), C.int(m), C.int(n), C.double(alpha), (*C.double)(a.ptr), C.int(lda),
+		(*C.double)(x.ptr), C.int(incX), C.double(beta), (*C.double)(y.ptr), C.int(incY), nil), "Dgemv")
+}
+
+// Dger mirrors compute/level2float64.go:24-65: A += alpha * x * yᵀ on float64 (compute/asm/f64/ger_amd64.s).
+func Dger(m, n int, alpha float64, x DevicePtr, incX int, y DevicePtr, incY int, a DevicePtr, lda int) error {
+	if m >= 0 && n >= 0 && lda >= imax(1, n) && incX != 0 && incY != 0 && m > 0 && n > 0 {
+		lx, ly := x.size/8, y.size/8
+		if (incX > 0 && lx <= (m-1)*incX) || (incX < 0 && lx <= (1-m)*incX) {
+			panic(shortX)
+		}
+		if (incY > 0 && ly <= (n-1)*incY) || (incY < 0 && ly <= (1-n)*incY) {
+			panic(shortY)
+		}
+		if a.size/8 < lda*(m-1)+n {
+			panic(shortA)
+		}
+	}
+	return status(C.guda_dger(C.int(m), C.int(n), C.double(alpha), (*C.double)(x.ptr), C.int(incX), (*C.double)(y.ptr), C.int(incY),
+		(*C.double)(a.ptr), C.int(lda), nil), "Dger")
+}

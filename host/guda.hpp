@@ -212,6 +212,28 @@ inline void Sger(int m, int n, float alpha, const DevicePtr& x, int incX, const 
   check(guda_sger(m, n, alpha, f32(x), incX, f32(y), incY, f32(a), lda, nullptr), "Sger");
 }
 
+// compute/level2float64.go:232-300 Dgemv (fp64 twin; gemvN_avx2_amd64.s / gemvT_amd64.s clear or scale exactly len(y) elements)
+inline void Dgemv(bool trans, int m, int n, double alpha, const DevicePtr& a, int lda, const DevicePtr& x, int incX, double beta,
+                  const DevicePtr& y, int incY) {
+  if (m > 0 && n > 0 && lda >= (n > 1 ? n : 1) && incX != 0 && incY != 0) {
+    const long long lenX = trans ? m : n, lenY = trans ? n : m, lx = (long long)(x.size / 8), ly = (long long)(y.size / 8);
+    if ((incX > 0 && (lenX - 1) * incX >= lx) || (incX < 0 && (1 - lenX) * incX >= lx)) throw BlasPanic("blas: insufficient length of x");
+    if ((incY > 0 && (lenY - 1) * incY >= ly) || (incY < 0 && (1 - lenY) * incY >= ly)) throw BlasPanic("blas: insufficient length of y");
+    if ((long long)(a.size / 8) < (long long)lda * (m - 1) + n) throw BlasPanic("blas: insufficient length of a");
+  }
+  check(guda_dgemv(trans, m, n, alpha, f64(a), lda, f64(x), incX, beta, f64(y), incY, nullptr), "Dgemv");
+}
+// compute/level2float64.go:24-65 Dger
+inline void Dger(int m, int n, double alpha, const DevicePtr& x, int incX, const DevicePtr& y, int incY, const DevicePtr& a, int lda) {
+  if (m > 0 && n > 0 && lda >= (n > 1 ? n : 1) && incX != 0 && incY != 0) {
+    const long long lx = (long long)(x.size / 8), ly = (long long)(y.size / 8);
+    if ((incX > 0 && lx <= (long long)(m - 1) * incX) || (incX < 0 && lx <= (long long)(1 - m) * incX)) throw BlasPanic("blas: insufficient length of x");
+    if ((incY > 0 && ly <= (long long)(n - 1) * incY) || (incY < 0 && ly <= (long long)(1 - n) * incY)) throw BlasPanic("blas: insufficient length of y");
+    if ((long long)(a.size / 8) < (long long)lda * (m - 1) + n) throw BlasPanic("blas: insufficient length of a");
+  }
+  check(guda_dger(m, n, alpha, f64(x), incX, f64(y), incY, f64(a), lda, nullptr), "Dger");
+}
+
 // conv.go:9-31 ConvParams, :69 Conv2D
 struct ConvParams {
   int BatchSize = 0, InChannels = 0, InHeight = 0, InWidth = 0, OutChannels = 0, KernelHeight = 0, KernelWidth = 0;

@@ -284,6 +284,29 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     for a, b, c in sets:
         g.Free(a); g.Free(b); g.Free(c)
 
+    # ---- Conv2D: conv_test.go:262-300's 64x56x56 -> 64, 3x3 pad 1 shape at batch 32; implicit GEMM vs materialised im2col
+    cp = g.ConvParams(BatchSize=32, InChannels=64, InHeight=56, InWidth=56, OutChannels=64, KernelHeight=3, KernelWidth=3,
+                      StrideH=1, StrideW=1, PadH=1, PadW=1, DilationH=1, DilationW=1, UseBias=True)
+    n_in, n_w, n_out = 32 * 64 * 56 * 56, 64 * 64 * 9, 32 * 64 * 56 * 56
+    cx, cw, cb, co = g.Malloc(n_in * 4), g.Malloc(n_w * 4), g.Malloc(64 * 4), g.Malloc(n_out * 4)
+    g.FillUniform(cx, 1, n_in, n_in, 600); g.FillUniform(cw, 1, n_w, n_w, 601); g.FillUniform(cb, 1, 64, 64, 602)
+    conv_flops = 2.0 * 64 * (64 * 9) * (32 * 56 * 56)
+    conv_ms = {}
+    for route, name in ((0, "implicit"), (1, "im2col")):
+        g.SetConvRoute(route)
+        for _ in range(2):
+            g.Conv2D(cx, cw, cb, co, cp)
+        conv_ms[name] = dev.time_ms(lambda: g.Conv2D(cx, cw, cb, co, cp), 10)
+    g.SetConvRoute(-1)
+    tf = conv_flops / (conv_ms["implicit"] * 1e-3) / 1e12
+    out["conv2d_b32_64x56x56_3x3"] = {
+        "value": tf, "unit": "TFLOP/s", "ms": conv_ms["implicit"], "ms_im2col_route": conv_ms["im2col"],
+        "includes": "blocking call (k-table launch + implicit-GEMM kernel + stream sync)",
+        "roofline": {"bound": "fp32_simt", "achieved": tf, "peak": ffma_peak, "unit": "TFLOP/s", "frac": tf / ffma_peak,
+                     "peak_source": "FFMA microbenchmark, this run"}}
+    for p in (cx, cw, cb, co):
+        g.Free(p)
+
     # ---- C3: fused GEMM + bias + GELU, FFN shape M=8192 K=4096 N=16384, fp32
     M, K, N = 8192, 4096, 16384
     a, b, c, bias = g.Malloc(M * K * 4), g.Malloc(K * N * 4), g.Malloc(M * N * 4), g.Malloc(N * 4)

@@ -564,6 +564,12 @@ def Conv2D(input, kernel, bias, output, params, stream=None):          # conv.go
     capi.check(_L().guda_conv2d(input.ptr, kernel.ptr, bptr, output.ptr, C.byref(cp), _sh(stream)), "Conv2D")
 
 
+def SetConvRoute(route):
+    """0 implicit GEMM (default), 1 materialised im2col, 2/3 implicit with the 64x128/64x64 tile forced,
+    -1 default / environment (guda_conv_set_route)."""
+    capi.check(_L().guda_conv_set_route(int(route)), "SetConvRoute")
+
+
 def SetSgemmMode(mode):
     capi.check(_L().guda_set_sgemm_mode(mode), "SetSgemmMode")
 

@@ -103,6 +103,7 @@ SIGNATURES = {
     "guda_softmax": (i, [vp, C.c_longlong, vp]),
     "guda_layer_norm": (i, [vp, vp, vp, C.c_longlong, f, vp]),
     "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
+    "guda_conv_set_route": (i, [i]),
     "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
     "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),
     "guda_f32_to_f16": (i, [vp, vp, sz, vp]),

@@ -7,9 +7,18 @@
 // (conv.go:107-137), which scrambles columns; here the column matrix is built as the GEMM expects it.
 // Memory plan: the column matrix is written once and read once by the GEMM (K*B*P*8 bytes of HBM traffic, the dominant
 // term); placement + bias is one pass (the reference copies C to a temp, reorders, then adds bias: three passes).
-#include "common.cuh"
+//
+// Implicit GEMM (default in the exact SGEMM mode): conv_igemm_kernel never materialises the column matrix.  Its B-tile loader
+// gathers col[k][n] straight from the NCHW input (a per-k table holds the (c, kh, kw) offsets, each thread owns one output
+// position n for the whole K walk, so consecutive threads read consecutive input pixels), and its epilogue adds the bias and
+// stores NCHW directly.  HBM traffic drops from |in| + 2*K*N*4 + 2*|out| (+ 2*|out| placement) to |in| (through L2) + |out|;
+// the FMA chain per output element is unchanged, so the two routes are bit-identical (tests/test_gpu_conv.py checks both).
+#include "gemm_simt.cuh"
+#include <cstdlib>
 
 namespace guda {
+
+int sgemm_mode();
 
 struct ConvGeom {
   int batch, in_c, in_h, in_w, out_c, kh, kw, stride_h, stride_w, pad_h, pad_w, dil_h, dil_w, out_h, out_w;
@@ -45,6 +54,152 @@ __global__ void __launch_bounds__(256) conv_place_kernel(const float* __restrict
   }
 }
 
+// ---------------------------------------------------------------- implicit GEMM
+// ktab[k] = {offset of (c, kh*dil_h, kw*dil_w) inside one image of the input, (kh*dil_h << 16) | kw*dil_w}
+__global__ void conv_ktab_kernel(int2* __restrict__ ktab, int K, ConvGeom g) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const int kw = k % g.kw, kh = (k / g.kw) % g.kh, c = k / (g.kw * g.kh);
+  const int dh = kh * g.dil_h, dw = kw * g.dil_w;
+  ktab[k] = make_int2((c * g.in_h + dh) * g.in_w + dw, (dh << 16) | dw);
+}
+
+// C tile BM (output channels) x BN (output positions n = b*P + p), 256 threads as 16 x 16, micro-tile (BM/16) x (BN/16) in
+// halves like gemm_simt_kernel; same chain: acc = 0; for k ascending: if (w != 0) acc = fma(w, col, acc); then + bias.
+template <int BM, int BN, bool FASTA, int MINB>
+__global__ void __launch_bounds__(256, MINB) conv_igemm_kernel(const float* __restrict__ w, const float* __restrict__ in,
+                                                            const float* __restrict__ bias, float* __restrict__ out,
+                                                            const int2* __restrict__ ktab, ConvGeom g, int K, long long N, int P) {
+  constexpr int BK = 16, TM = BM / 16, TN = BN / 16, HM = TM / 2, HN = TN / 2;
+  constexpr int BPT = BK * BN / 256;                 // B elements per thread per k-tile
+  constexpr int KSTEP = 256 / BN;                    // k rows covered by one pass of the CTA
+  static_assert(256 % BN == 0 && TN % 2 == 0 && HM >= 1, "tile shape");
+  using Smem = GemmSmem<float, BM, BN, BK>;
+  __shared__ __align__(16) Smem sm;
+
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * BM;
+  const long long n0 = (long long)blockIdx.x * BN;
+
+  // this thread's column of the B tile: one output position for the whole K walk
+  const int bn = tid % BN, bk0 = tid / BN;
+  const long long nn = n0 + bn;
+  const bool n_ok = nn < N;
+  int ih0 = 0, iw0 = 0;
+  const float* img = in;
+  if (n_ok) {
+    const int b = (int)(nn / P), p = (int)(nn - (long long)b * P);
+    const int oh = p / g.out_w, ow = p - oh * g.out_w;
+    ih0 = oh * g.stride_h - g.pad_h;
+    iw0 = ow * g.stride_w - g.pad_w;
+    img = in + (long long)b * g.in_c * g.in_h * g.in_w + (long long)ih0 * g.in_w + iw0;
+  }
+  float breg[BPT];
+  auto load_b = [&](int k0) {
+#pragma unroll
+    for (int it = 0; it < BPT; it++) {
+      const int k = k0 + bk0 + it * KSTEP;
+      float v = 0.0f;
+      if (n_ok && k < K) {
+        const int2 e = __ldg(ktab + k);
+        const int ih = ih0 + (e.y >> 16), iw = iw0 + (e.y & 0xffff);
+        if ((unsigned)ih < (unsigned)g.in_h && (unsigned)iw < (unsigned)g.in_w) v = __ldg(img + e.x);
+      }
+      breg[it] = v;
+    }
+  };
+  auto store_b = [&](int buf) {
+#pragma unroll
+    for (int it = 0; it < BPT; it++) sm.b[buf][bk0 + it * KSTEP][bn] = breg[it];
+  };
+
+  TileLoader<float, BM, BK, true, FASTA> la;
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; i++)
+#pragma unroll
+    for (int j = 0; j < TN; j++) acc[i][j] = 0.0f;
+
+  const int KT = (K + BK - 1) / BK;
+  la.load(w, K, m0, 0, g.out_c, K, tid);
+  load_b(0);
+  bool z = la.template store<Smem::LDA_S>(sm.a[0], 1.0f, true, tid);
+  store_b(0);
+  bool zf = __syncthreads_or(z);
+  for (int kt = 0; kt < KT; kt++) {
+    const int cur = kt & 1;
+    if (kt + 1 < KT) {
+      la.load(w, K, m0, (kt + 1) * BK, g.out_c, K, tid);
+      load_b((kt + 1) * BK);
+    }
+#pragma unroll
+    for (int kk = 0; kk < BK; kk++) {
+      float af[TM], bf[TN];
+      load_frag<float, HM>(af, &sm.a[cur][kk][ty * HM]);
+      load_frag<float, HM>(af + HM, &sm.a[cur][kk][BM / 2 + ty * HM]);
+      load_frag<float, HN>(bf, &sm.b[cur][kk][tx * HN]);
+      load_frag<float, HN>(bf + HN, &sm.b[cur][kk][BN / 2 + tx * HN]);
+      if (!zf) {
+#pragma unroll
+        for (int i = 0; i < TM; i++) {
+          const unsigned long long aa = dup_f32(af[i]);
+#pragma unroll
+          for (int j = 0; j < TN; j += 2) fma2_f32(acc[i][j], acc[i][j + 1], aa, bf[j], bf[j + 1]);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < TM; i++) {
+          if (af[i] != 0.0f) {                                           // compute/sgemm.go:301 `if tmp != 0` (true for NaN)
+#pragma unroll
+            for (int j = 0; j < TN; j++) acc[i][j] = __fmaf_rn(af[i], bf[j], acc[i][j]);
+          }
+        }
+      }
+    }
+    z = false;
+    if (kt + 1 < KT) {
+      z = la.template store<Smem::LDA_S>(sm.a[cur ^ 1], 1.0f, true, tid);
+      store_b(cur ^ 1);
+    }
+    zf = __syncthreads_or(z);
+  }
+
+  // ---- epilogue: + bias (conv.go:160-166), NCHW store out[b][oc][p]
+#pragma unroll
+  for (int jh = 0; jh < 2; jh++) {
+    const long long c0 = n0 + (jh == 0 ? tx * HN : BN / 2 + tx * HN);
+    if (c0 >= N) continue;
+    const int b0 = (int)(c0 / P), p0 = (int)(c0 - (long long)b0 * P);
+#pragma unroll
+    for (int i = 0; i < TM; i++) {
+      const int oc = m0 + (i < HM ? ty * HM + i : BM / 2 + ty * HM + (i - HM));
+      if (oc >= g.out_c) continue;
+      const float bv = bias ? bias[oc] : 0.0f;
+      float o[HN];
+#pragma unroll
+      for (int j = 0; j < HN; j++) o[j] = bias ? __fadd_rn(acc[i][jh * HN + j], bv) : acc[i][jh * HN + j];
+      float* dst = out + ((long long)b0 * g.out_c + oc) * P + p0;
+      if (HN % 4 == 0 && p0 + HN <= P && c0 + HN <= N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+#pragma unroll
+        for (int j = 0; j < HN; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+      } else {
+        int b = b0, p = p0;
+#pragma unroll
+        for (int j = 0; j < HN; j++) {
+          if (c0 + j < N) out[((long long)b * g.out_c + oc) * P + p] = o[j];
+          if (++p == P) { p = 0; b++; }
+        }
+      }
+    }
+  }
+}
+
+static int conv_route_env() {          // GUDA_CONV_ROUTE=im2col forces the materialised route (A/B and parity tests)
+  static const int r = [] { const char* e = getenv("GUDA_CONV_ROUTE"); return (e && !strcmp(e, "im2col")) ? 1 : 0; }();
+  return r;
+}
+static int g_conv_route = -1;          // -1: environment, 0: implicit, 1: im2col, 2/3: implicit with the 64x128 / 64x64 tile
+
 struct ConvTemp {
   void* p = nullptr;
   ~ConvTemp() { if (p) guda_free(p); }
@@ -76,6 +231,42 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
   if (N > 0x7fffffffLL || K > 0x7fffffffLL) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: problem too large for 32-bit GEMM dimensions");
   const float* b = (cp->use_bias && bias) ? bias : nullptr;
   cudaStream_t s = native(stream);
+  const int route = g_conv_route >= 0 ? g_conv_route : conv_route_env();
+  // the 4^3 / 8^3 / 16^3 contiguous shapes take Sgemm's unfused small-matrix kernels (compute/sgemm.go:80-96), and the 3xTF32
+  // mode is a property of guda_sgemm: both stay on the materialised route
+  const bool small_path = g.out_c == N && N == K && (K == 4 || K == 8 || K == 16);
+  const long long in_image = (long long)g.in_c * g.in_h * g.in_w;
+  if (route != 1 && !small_path && sgemm_mode() == GUDA_SGEMM_EXACT && in_image < 0x7fffffffLL && P < 0x7fffffffLL &&
+      g.kh * (long long)g.dil_h < 32768 && g.kw * (long long)g.dil_w < 65536) {
+    ConvTemp tab;
+    if ((rc = guda_malloc(&tab.p, (size_t)K * sizeof(int2)))) return rc;
+    conv_ktab_kernel<<<(unsigned)((K + 127) / 128), 128, 0, s>>>((int2*)tab.p, (int)K, g);
+    if ((rc = check_launch("conv_ktab"))) return rc;
+    // CTA tile 64 x {128, 64}: like Sgemm's choice (gemm.cu launch_simt_one), the smallest estimated makespan
+    // ceil(tiles / SMs) * BM*BN / efficiency (4x8 micro-tile 0.85, 4x4 0.6).  A 64x256 tile (4x16 micro-tile, 122 registers,
+    // 16 gathers per thread per k-tile) was measured at 15 TFLOP/s against 28 for 64x128 and is not built.
+    const int forced = route == 2 ? 128 : route == 3 ? 64 : 0;      // A/B and test knob (guda_conv_set_route)
+    const long long sms = sm_count(), mt = (g.out_c + 63) / 64;
+    auto makespan = [&](int bn, double eff) { return (double)((mt * ((N + bn - 1) / bn) + sms - 1) / sms) * 64.0 * bn / eff; };
+    int bn = 128;
+    if (forced) bn = forced;
+    else bn = makespan(128, 0.85) <= makespan(64, 0.6) ? 128 : 64;
+    dim3 grid((unsigned)((N + bn - 1) / bn), (unsigned)mt);
+    if (grid.y > 65535) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: too many output channels for one launch");
+    const bool fasta = (g.out_c % 64 == 0) && (K % 16 == 0) && ((uintptr_t)kernel % 16 == 0);
+    const int2* kt = (const int2*)tab.p;
+#define GUDA_CONV_LAUNCH(BN_, MINB_)                                                                                          \
+    do {                                                                                                                        \
+      if (fasta) conv_igemm_kernel<64, BN_, true, MINB_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P);  \
+      else       conv_igemm_kernel<64, BN_, false, MINB_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P); \
+    } while (0)
+    if (bn == 128) GUDA_CONV_LAUNCH(128, 3);
+    else GUDA_CONV_LAUNCH(64, 4);
+#undef GUDA_CONV_LAUNCH
+    if ((rc = check_launch("conv_igemm"))) return rc;
+    GUDA_CUDA(cudaStreamSynchronize(s));        // the k table returns to the pool when this function exits
+    return GUDA_OK;
+  }
   ConvTemp col, tmp;
   if ((rc = guda_malloc(&col.p, (size_t)(K * N) * sizeof(float)))) return rc;             // conv.go:88-93 workspace
   const bool direct_out = (g.batch == 1);                                                // [OC][P] already is NCHW
@@ -95,5 +286,13 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     if ((rc = check_launch("conv_place"))) return rc;
   }
   GUDA_CUDA(cudaStreamSynchronize(s));          // the workspace returns to the pool when this function exits (conv.go:93 defer Free)
+  return GUDA_OK;
+}
+
+/* route switch for A/B measurements and the route-equality tests: 0 implicit GEMM (default), 1 materialised im2col,
+ * 2 / 3 implicit GEMM with the 64x128 / 64x64 CTA tile forced, -1 environment */
+extern "C" int guda_conv_set_route(int route) {
+  if (route < -1 || route > 3) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: route must be -1 .. 3");
+  g_conv_route = route;
   return GUDA_OK;
 }

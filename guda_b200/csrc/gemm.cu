@@ -2,6 +2,7 @@
 // Replaces compute/sgemm.go:29-350 (Sgemm), compute/dgemm.go:25-362 + dgemm_fixed.go (Dgemm),
 // fused.go:313-368 and fused_gelu.go:65-137.
 #include "gemm_simt.cuh"
+#include <cstdlib>
 
 namespace guda {
 
@@ -86,7 +87,9 @@ static int launch_simt_one(const GemmParams<T>& p, cudaStream_t s, const Scatter
     const long long tiles = (long long)((p.m + bm - 1) / bm) * ((p.n + bn - 1) / bn);
     return (double)((tiles + sms - 1) / sms) * bm * bn / eff;
   };
-  const double t_big = makespan(128, 128, 1.0), t_mid = makespan(128, 64, 0.85), t_small = makespan(64, 64, 0.6);
+  double t_big = makespan(128, 128, 1.0), t_mid = makespan(128, 64, 0.85), t_small = makespan(64, 64, 0.6);
+  static const int forced = [] { const char* e = getenv("GUDA_SIMT_TILE"); return e ? atoi(e) : 0; }();   // A/B knob: 1 big, 2 mid, 3 small
+  if (forced == 1) t_big = 0; else if (forced == 2) { t_mid = 0; t_big = 1; t_small = 1; } else if (forced == 3) { t_small = 0; t_big = 1; t_mid = 1; }
   if (t_big <= t_mid && t_big <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 128, TileCfg<T>::MINB_BIG, SCAT>(p, s, sp);
   if constexpr (sizeof(T) == 4) {
     if (t_mid <= t_small) return launch_simt_tile<T, TA, TB, MODE, EPI, 128, 64, 2, SCAT>(p, s, sp);

@@ -37,7 +37,7 @@ def _run(g, p, x, w, b):
 
 
 @pytest.mark.parametrize("idx", range(4))
-def test_reference_conv_cases_on_gpu(g, idx):
+def test_reference_conv_cases_on_gpu(g, idx, route):
     case = golden("conv_cases.json")["cases"][idx]
     bias = np.array(case["bias"], dtype=np.float32) if case["bias"] else None
     out = _run(g, case["params"], np.array(case["input"], np.float32), np.array(case["kernel"], np.float32), bias)
@@ -53,11 +53,39 @@ def _params(B, C_, H, W, OC, KH, KW, s=1, p=0, d=1, bias=True):
 # conv_test.go:262-300 benchmark shapes (32x32x32 3x3, 64x56x56 3x3 -> 64, 3x224x224 7x7 s2) + ragged / dilated / batched ones
 SHAPES = [_params(1, 32, 32, 32, 64, 3, 3, 1, 1), _params(1, 64, 56, 56, 64, 3, 3, 1, 1), _params(1, 3, 224, 224, 64, 7, 7, 2, 3),
           _params(1, 3, 9, 11, 5, 3, 3, 1, 1, bias=False), _params(2, 4, 8, 8, 6, 3, 3, 2, 1), _params(3, 2, 10, 7, 4, 2, 3, 1, 0, 2),
-          _params(4, 16, 14, 14, 32, 1, 1), _params(1, 1, 5, 5, 1, 5, 5)]
+          _params(4, 16, 14, 14, 32, 1, 1), _params(1, 1, 5, 5, 1, 5, 5),
+          # tile-edge cases of the implicit-GEMM route: OC over one 64-row tile, N = B*P over / not a multiple of 128 with the
+          # batch boundary inside a 4-wide store group (P = 35), K not a multiple of 16, the Sgemm 16^3 fast-path shape (OC = N = K = 16)
+          _params(3, 5, 9, 7, 70, 3, 3, 1, 1), _params(5, 3, 7, 5, 130, 3, 2, 1, 1, bias=False), _params(2, 8, 33, 17, 64, 3, 3, 2, 2, 2),
+          _params(1, 16, 4, 4, 16, 1, 1), _params(2, 128, 12, 12, 128, 3, 3, 1, 1)]
+
+
+@pytest.fixture(params=[0, 1, 2, 3], ids=["implicit", "im2col", "implicit-64x128", "implicit-64x64"])
+def route(request, g):
+    g.SetConvRoute(request.param)
+    yield request.param
+    g.SetConvRoute(-1)
+
+
+def test_conv2d_routes_bit_identical_large(g, O):
+    """Both routes at a size the oracle does not replay: 64x56x56 -> 64, 3x3, batch 8 (N = 25088), bit for bit."""
+    p = _params(8, 64, 56, 56, 64, 3, 3, 1, 1)
+    x = O.uniform_f32(8 * 64 * 56 * 56, 11)
+    w = O.uniform_f32(64 * 64 * 9, 12)
+    w[::5] = 0.0
+    b = O.uniform_f32(64, 13)
+    outs = []
+    for r in (0, 1, 2, 3):
+        g.SetConvRoute(r)
+        outs.append(_run(g, p, x, w, b))
+    g.SetConvRoute(-1)
+    for o in outs[1:]:
+        assert np.array_equal(outs[0], o)
+    assert np.all(np.isfinite(outs[0])) and float(np.abs(outs[0]).max()) > 0
 
 
 @pytest.mark.parametrize("p", SHAPES)
-def test_conv2d_bit_exact_vs_oracle(g, O, p):
+def test_conv2d_bit_exact_vs_oracle(g, O, p, route):
     x = O.uniform_f32(p["BatchSize"] * p["InChannels"] * p["InHeight"] * p["InWidth"], 1)
     w = O.uniform_f32(p["OutChannels"] * p["InChannels"] * p["KernelHeight"] * p["KernelWidth"], 2)
     w[::7] = 0.0                                    # the Sgemm zero test acts on the weights

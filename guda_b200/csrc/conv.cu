@@ -66,18 +66,21 @@ __global__ void conv_ktab_kernel(int2* __restrict__ ktab, int K, ConvGeom g) {
 
 // C tile BM (output channels) x BN (output positions n = b*P + p), 256 threads as 16 x 16, micro-tile (BM/16) x (BN/16) in
 // halves like gemm_simt_kernel; same chain: acc = 0; for k ascending: if (w != 0) acc = fma(w, col, acc); then + bias.
-template <int BM, int BN, bool FASTA, int MINB>
+// TXN threads along n, 256 / TXN along m.  64 x 128 uses 32 x 8 (micro-tile 8 x 4, a warp = one m-row of threads): its A
+// fragments are warp-wide broadcasts and its B fragments 8-byte loads, ~6-8 shared-memory wavefronts per k step where the
+// 16 x 16 grid's 4 x 8 micro-tile needed ~10-12 for the same 8 SM-cycles of FFMA2 (the LSU is the co-limit).
+template <int BM, int BN, bool FASTA, int MINB, int TXN>
 __global__ void __launch_bounds__(256, MINB) conv_igemm_kernel(const float* __restrict__ w, const float* __restrict__ in,
                                                             const float* __restrict__ bias, float* __restrict__ out,
                                                             const int2* __restrict__ ktab, ConvGeom g, int K, long long N, int P) {
-  constexpr int BK = 16, TM = BM / 16, TN = BN / 16, HM = TM / 2, HN = TN / 2;
+  constexpr int BK = 16, TYN = 256 / TXN, TM = BM / TYN, TN = BN / TXN, HM = TM / 2, HN = TN / 2;
   constexpr int BPT = BK * BN / 256;                 // B elements per thread per k-tile
   constexpr int KSTEP = 256 / BN;                    // k rows covered by one pass of the CTA
   static_assert(256 % BN == 0 && TN % 2 == 0 && HM >= 1, "tile shape");
   using Smem = GemmSmem<float, BM, BN, BK>;
   __shared__ __align__(16) Smem sm;
 
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int tid = threadIdx.x, tx = tid % TXN, ty = tid / TXN;
   const int m0 = blockIdx.y * BM;
   const long long n0 = (long long)blockIdx.x * BN;
 
@@ -182,6 +185,8 @@ __global__ void __launch_bounds__(256, MINB) conv_igemm_kernel(const float* __re
       if (HN % 4 == 0 && p0 + HN <= P && c0 + HN <= N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
 #pragma unroll
         for (int j = 0; j < HN; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+      } else if (HN == 2 && p0 + HN <= P && c0 + HN <= N && (reinterpret_cast<uintptr_t>(dst) & 7) == 0) {
+        *reinterpret_cast<float2*>(dst) = make_float2(o[0], o[1]);
       } else {
         int b = b0, p = p0;
 #pragma unroll
@@ -255,13 +260,13 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     if (grid.y > 65535) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: too many output channels for one launch");
     const bool fasta = (g.out_c % 64 == 0) && (K % 16 == 0) && ((uintptr_t)kernel % 16 == 0);
     const int2* kt = (const int2*)tab.p;
-#define GUDA_CONV_LAUNCH(BN_, MINB_)                                                                                          \
+#define GUDA_CONV_LAUNCH(BN_, MINB_, TXN_)                                                                                          \
     do {                                                                                                                        \
-      if (fasta) conv_igemm_kernel<64, BN_, true, MINB_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P);  \
-      else       conv_igemm_kernel<64, BN_, false, MINB_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P); \
+      if (fasta) conv_igemm_kernel<64, BN_, true, MINB_, TXN_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P);  \
+      else       conv_igemm_kernel<64, BN_, false, MINB_, TXN_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P); \
     } while (0)
-    if (bn == 128) GUDA_CONV_LAUNCH(128, 3);
-    else GUDA_CONV_LAUNCH(64, 4);
+    if (bn == 128) GUDA_CONV_LAUNCH(128, 3, 32);
+    else GUDA_CONV_LAUNCH(64, 4, 16);
 #undef GUDA_CONV_LAUNCH
     if ((rc = check_launch("conv_igemm"))) return rc;
     GUDA_CUDA(cudaStreamSynchronize(s));        // the k table returns to the pool when this function exits

@@ -1,0 +1,155 @@
+"""GPU parity at BASELINE.json's FULL sizes (configs[1..4]) through the C ABI.
+
+The oracle cannot replay 65536^3 or 16384^3, but a C element is one sequential-k chain over one row of A and one column of B, and the
+device RNG (guda_fill_uniform_*) is counter-based on the GLOBAL (row, col): any row panel of A and column panel of B can be generated
+again as a small matrix.  So each test runs the full-size call once, regenerates the panels behind a few 4 x 4 (4 x 8) blocks of C --
+corners, tile / K-chunk / wave boundaries, unaligned positions -- and asks the oracle for exactly those chains: bit for bit for the
+exact routes, within the stated 16-bit tolerance for the tensor route.  Level-1 at n = 2^24 is replayed by the oracle in full."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def g():
+    import guda_b200 as G
+    G.Init(0)
+    yield G
+    G.PoolTrim()
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle
+    return oracle
+
+
+def _panel(g, rows, cols, seed, row0, col0, full_cols, dtype=np.float32, lo=-1.0, hi=1.0):
+    """rows x cols window at (row0, col0) of the full matrix with seed `seed`, generated on the device and copied down."""
+    it = np.dtype(dtype).itemsize
+    p = g.Malloc(rows * cols * it)
+    g.FillUniform(p, rows, cols, cols, seed, row0=row0, col0=col0, full_cols=full_cols, lo=lo, hi=hi, dtype=dtype)
+    g.Synchronize()
+    h = (p.Float32() if dtype == np.float32 else p.Float64())[:rows * cols].copy()
+    g.Free(p)
+    return h
+
+
+def _block(g, c, ldc, i0, j0, r, w, dtype=np.float32):
+    it = np.dtype(dtype).itemsize
+    out = np.empty((r, w), dtype)
+    for i in range(r):
+        row = g.DevicePtr(c.ptr + ((i0 + i) * ldc + j0) * it, w * it)
+        out[i] = (row.Float32() if dtype == np.float32 else row.Float64() if dtype == np.float64 else row.UInt16())[:w]
+    return out
+
+
+def test_c5_sgemm_65536_cubed_sampled_chains_bit_exact(g, O):
+    """configs[4] on one GPU: 65536^3 fp32 NN (48 GiB of operands, 8 K-blocked launches of the 128x128 tile)."""
+    n = 65536
+    a, b, c = g.Malloc(n * n * 4), g.Malloc(n * n * 4), g.Malloc(n * n * 4)
+    g.FillUniform(a, n, n, n, 11); g.FillUniform(b, n, n, n, 12)
+    g.Memset(c, 0xFF, n * n * 4)
+    g.GEMM(False, False, n, n, n, 1.0, a, n, b, n, 0.0, c, n)
+    g.Synchronize()
+    blocks = [(0, 0), (n - 4, n - 4), (126, 62), (32766, 16382), (40001, 50003), (65408, 129)]
+    for i0, j0 in blocks:
+        ar = _panel(g, 4, n, 11, i0, 0, n)
+        bc = _panel(g, n, 4, 12, 0, j0, n)
+        want = O.sgemm(0, 0, 4, 4, n, 1.0, ar, n, bc, 4, 0.0, np.zeros(16, np.float32), 4).reshape(4, 4)
+        got = _block(g, c, n, i0, j0, 4, 4)
+        assert np.array_equal(got, want), (i0, j0)
+        assert np.all(np.isfinite(got)) and float(np.abs(got).max()) > 1.0          # a 65536-long chain, not an untouched tile
+    for p in (a, b, c):
+        g.Free(p)
+    g.PoolTrim()
+
+
+def test_c4_dgemm_16384_cubed_sampled_chains_bit_exact(g, O):
+    """configs[3]: 16384^3 fp64 on the FP64 tensor pipe (DMMA), K-blocked; the oracle's 4x4 FMA tile gives the same chains."""
+    n = 16384
+    a, b, c = g.Malloc(n * n * 8), g.Malloc(n * n * 8), g.Malloc(n * n * 8)
+    g.FillUniform(a, n, n, n, 21, dtype=np.float64); g.FillUniform(b, n, n, n, 22, dtype=np.float64)
+    g.Memset(c, 0xFF, n * n * 8)
+    g.Dgemm(False, False, n, n, n, 1.0, a, n, b, n, 0.0, c, n)
+    g.Synchronize()
+    for i0, j0 in [(0, 0), (n - 4, n - 4), (124, 60), (8188, 4100), (12344, 16000)]:
+        ar = _panel(g, 4, n, 21, i0, 0, n, np.float64)
+        bc = _panel(g, n, 4, 22, 0, j0, n, np.float64)
+        want = O.dgemm(0, 0, 4, 4, n, 1.0, ar, n, bc, 4, 0.0, np.zeros(16), 4).reshape(4, 4)
+        assert np.array_equal(_block(g, c, n, i0, j0, 4, 4, np.float64), want), (i0, j0)
+    for p in (a, b, c):
+        g.Free(p)
+    g.PoolTrim()
+
+
+def test_c3_fused_ffn_fp32_sampled_chains_bit_exact(g, O):
+    """configs[2], exact fp32 route: M=8192 K=4096 N=16384, bias + GELU in the epilogue."""
+    M, K, N = 8192, 4096, 16384
+    s = 1.0 / np.sqrt(K)
+    a, b, c, bias = g.Malloc(M * K * 4), g.Malloc(K * N * 4), g.Malloc(M * N * 4), g.Malloc(N * 4)
+    g.FillUniform(a, M, K, K, 31); g.FillUniform(b, K, N, N, 32, lo=-3 * s, hi=3 * s); g.FillUniform(bias, 1, N, N, 33)
+    g.FusedGEMMBiasGELU(False, False, M, N, K, 1.0, a, K, b, N, 0.0, c, N, bias)
+    g.Synchronize()
+    hb = bias.Float32()[:N]
+    for i0, j0 in [(0, 0), (M - 4, N - 8), (125, 8190), (4093, 12345)]:
+        ar = _panel(g, 4, K, 31, i0, 0, K)
+        bc = _panel(g, K, 8, 32, 0, j0, N, lo=-3 * s, hi=3 * s)
+        want = O.fused_gemm_bias_gelu(0, 0, 4, 8, K, 1.0, ar, K, bc, 8, 0.0, np.zeros(32, np.float32), 8, hb[j0:j0 + 8].copy()).reshape(4, 8)
+        assert np.array_equal(_block(g, c, N, i0, j0, 4, 8), want), (i0, j0)
+    for p in (a, b, c, bias):
+        g.Free(p)
+
+
+def test_c3_fused_ffn_bf16_tensor_route_sampled(g, O):
+    """configs[2], bf16 tensor route (tcgen05, CTA pairs): 2 bf16 ULP of the float64 value, as tests/test_gpu_tensor.py states."""
+    M, K, N = 8192, 4096, 16384
+    s = 1.0 / np.sqrt(K)
+    L = g.load()
+
+    def bf16_matrix(rows, cols, seed, row0, col0, full_cols, lo, hi):
+        f = g.Malloc(rows * cols * 4)
+        g.FillUniform(f, rows, cols, cols, seed, row0=row0, col0=col0, full_cols=full_cols, lo=lo, hi=hi)
+        h = g.Malloc(rows * cols * 2)
+        g.capi.check(L.guda_f32_to_bf16(f.ptr, h.ptr, rows * cols, None), "f32_to_bf16")
+        g.Synchronize()
+        g.Free(f)
+        return h
+
+    a, b = bf16_matrix(M, K, 41, 0, 0, K, -1.0, 1.0), bf16_matrix(K, N, 42, 0, 0, N, -3 * s, 3 * s)
+    c, bias = g.Malloc(M * N * 2), g.Malloc(N * 4)
+    g.FillUniform(bias, 1, N, N, 43)
+    g.FusedGEMMBFloat16BiasGELU(M, N, K, 1.0, a, K, b, N, c, N, bias)
+    g.Synchronize()
+    hb = bias.Float32()[:N]
+    for i0, j0 in [(0, 0), (M - 4, N - 8), (255, 256), (5001, 9999)]:
+        pa, pb = bf16_matrix(4, K, 41, i0, 0, K, -1.0, 1.0), bf16_matrix(K, 8, 42, 0, j0, N, -3 * s, 3 * s)
+        ar = O.bf16_to_f32(pa.UInt16()[:4 * K]).reshape(4, K).astype(np.float64)
+        bc = O.bf16_to_f32(pb.UInt16()[:K * 8]).reshape(K, 8).astype(np.float64)
+        g.Free(pa); g.Free(pb)
+        v = (ar @ bc + hb[j0:j0 + 8]).astype(np.float32)
+        want = O.bf16_to_f32(O.to_bf16_fast(O.gelu(v.reshape(-1)))).reshape(4, 8)
+        got = O.bf16_to_f32(_block(g, c, N, i0, j0, 4, 8, np.uint16).reshape(-1)).reshape(4, 8)
+        ulp = np.maximum(np.abs(want), 2.0 ** -6) * 2.0 ** -7
+        assert np.all(np.abs(got - want) <= 2.0 * ulp), (i0, j0)
+    for p in (a, b, c, bias):
+        g.Free(p)
+
+
+def test_c2_saxpy_sdot_16m_against_the_oracle(g, O):
+    """configs[1]: n = 2^24.  AXPY is elementwise -> every bit; DOT within the reduction tolerance of the reference's own order."""
+    n = 1 << 24
+    x, y = O.uniform_f32(n, 51), O.uniform_f32(n, 52)
+    dx, dy = g.to_device(x), g.to_device(y)
+    g.AXPY(2.5, dx, dy, n)
+    want_y = O.saxpy(n, 2.5, x, 1, y.copy(), 1)
+    assert np.array_equal(dy.Float32()[:n], want_y)
+    got = float(g.DOT(dx, dy, n))
+    want = float(O.sdot(n, x, 1, want_y, 1))
+    exact = float(np.dot(x.astype(np.float64), want_y.astype(np.float64)))
+    bound = 2.0 * n * 2.0 ** -24 * float(np.dot(np.abs(x).astype(np.float64), np.abs(want_y).astype(np.float64)))
+    assert abs(got - want) <= bound
+    assert abs(got - exact) <= abs(want - exact) + 1e-6 * max(1.0, abs(exact))      # at least as accurate as the reference order
+    assert float(g.DOT(dx, dy, n)) == got                                            # deterministic
+    g.Free(dx); g.Free(dy)

@@ -205,15 +205,17 @@ __device__ __forceinline__ void load_frag(T* dst, const T* src) {
   }
 }
 
-template <typename T, bool TA, bool TB, int BM, int BN, int BK, int MODE, int EPI, bool FAST, int MINB, bool SCAT = false>
+// TXN threads along n (256 / TXN along m): 16 -> the square grid; 32 -> a warp is one m-row of threads, every A fragment load is
+// a warp-wide broadcast and the B fragments are 8-byte loads (micro-tile 8 x 4 on the 64 x 128 tile).
+template <typename T, bool TA, bool TB, int BM, int BN, int BK, int MODE, int EPI, bool FAST, int MINB, bool SCAT = false, int TXN = 16>
 __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p, ScatterParams<T, SCAT> sp) {
-  constexpr int TM = BM / 16, TN = BN / 16;       // micro-tile
+  constexpr int TM = BM / (256 / TXN), TN = BN / TXN;       // micro-tile
   constexpr int HM = TM / 2, HN = TN / 2;         // halves, BM/2 (BN/2) apart
   using Smem = GemmSmem<T, BM, BN, BK>;
   __shared__ __align__(16) Smem sm;
 
   const int tid = threadIdx.x;
-  const int tx = tid & 15, ty = tid >> 4;
+  const int tx = tid % TXN, ty = tid / TXN;
   // CTA -> tile: groups of 16 M-blocks sweep N, so the CTAs resident at one time cover a ~16 x 18 patch of C and
   // share A row panels and B column panels in L2 (row-major CTA order re-read B once per 4-5 tile rows:
   // 8.1 GB of DRAM reads for 8192^3 against 0.8 GB algorithmic; profiles/r01)
@@ -283,7 +285,17 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p, S
         load_frag<T, HM>(af + HM, &sm.a[cur][kk][BM / 2 + ty * HM]);
         load_frag<T, HN>(bf, &sm.b[cur][kk][tx * HN]);
         load_frag<T, HN>(bf + HN, &sm.b[cur][kk][BN / 2 + tx * HN]);
-        if constexpr (sizeof(T) == 4 && TN % 2 == 0) {
+        if constexpr (sizeof(T) == 4 && TXN == 32 && TM % 2 == 0) {
+          // tall micro-tile: pair the accumulators along m, so the duplicated operand is the (few) B values and the A pairs
+          // come straight out of the 128-bit fragment loads; fma(b, a, c) == fma(a, b, c)
+#pragma unroll
+          for (int j = 0; j < TN; j++) {
+            const unsigned long long bb = dup_f32((float)bf[j]);
+#pragma unroll
+            for (int i = 0; i < TM; i += 2)
+              fma2_f32(reinterpret_cast<float&>(acc[i][j]), reinterpret_cast<float&>(acc[i + 1][j]), bb, (float)af[i], (float)af[i + 1]);
+          }
+        } else if constexpr (sizeof(T) == 4 && TN % 2 == 0) {
 #pragma unroll
           for (int i = 0; i < TM; i++) {
             const unsigned long long aa = dup_f32((float)af[i]);
@@ -351,6 +363,8 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p, S
         if (FAST && HN % VN == 0) {
 #pragma unroll
           for (int j = 0; j < HN; j += VN) *reinterpret_cast<V*>(dst + j) = *reinterpret_cast<V*>(out + j);
+        } else if (FAST && sizeof(T) == 4 && HN == 2) {
+          *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(out);       // 32 x 8 thread grid: a warp stores 256 contiguous bytes
         } else {
 #pragma unroll
           for (int j = 0; j < HN; j++) if (col0 + j < lim) dst[j] = out[j];

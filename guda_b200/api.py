@@ -510,6 +510,105 @@ def FusedGEMMBiasGELU(transA, transB, m, n, k, alpha, a, lda, b, ldb, beta, c, l
                "FusedGEMMBiasGELU")
 
 
+# ---------------------------------------------------------------- elementwise ops (math.go:133-169,230-272) and FusedKernel (fused.go)
+def _ew_len(op, n, *ptrs):
+    if n < 0 or any(p.size // 4 < n for p in ptrs):
+        raise IndexError("%s: index out of range [%d]" % (op, n))       # the reference's slice indexing would panic
+
+
+def Add(a, b, c, n, stream=None):                  # math.go:133
+    _ew_len("Add", n, a, b, c)
+    capi.check(_L().guda_add(a.ptr, b.ptr, c.ptr, n, _sh(stream)), "Add")
+
+
+def Multiply(a, b, c, n, stream=None):             # math.go:152
+    _ew_len("Multiply", n, a, b, c)
+    capi.check(_L().guda_multiply(a.ptr, b.ptr, c.ptr, n, _sh(stream)), "Multiply")
+
+
+def ReLU(x, n, stream=None):                       # math.go:236
+    _ew_len("ReLU", n, x)
+    capi.check(_L().guda_relu(x.ptr, n, _sh(stream)), "ReLU")
+
+
+def Sigmoid(x, n, stream=None):                    # math.go:255 -> activations.go:9 SigmoidFloat32
+    _ew_len("Sigmoid", n, x)
+    capi.check(_L().guda_sigmoid(x.ptr, n, _sh(stream)), "Sigmoid")
+
+
+def geluFloat32(x):                                # fused_gelu.go:44 -- the one function the reference hands to FusedKernel.Custom
+    raise ErrNotSupported(capi.ERR_NOT_IMPLEMENTED, "geluFloat32", "device-side function: pass it to FusedKernel.Custom")
+
+
+class FusedKernel:
+    """fused.go:18-216: a list of ops applied to each element in one read-modify-write pass (guda_fused_execute)."""
+
+    def __init__(self):
+        self.ops = []                               # (type, alpha, broadcast, broadcast_dim)
+
+    def Add(self, alpha):                           # fused.go:52
+        self.ops.append((capi.FUSED_ADD, alpha, False, -1)); return self
+
+    def AddBroadcast(self, alpha, broadcastDim):    # fused.go:63
+        self.ops.append((capi.FUSED_ADD, alpha, True, broadcastDim)); return self
+
+    def Multiply(self):                             # fused.go:74
+        self.ops.append((capi.FUSED_MUL, 0.0, False, -1)); return self
+
+    def AddScalar(self, alpha):                     # fused.go:82
+        self.ops.append((capi.FUSED_ADD_SCALAR, alpha, False, -1)); return self
+
+    def MulScalar(self, alpha):                     # fused.go:91
+        self.ops.append((capi.FUSED_MUL_SCALAR, alpha, False, -1)); return self
+
+    def ReLU(self):                                 # fused.go:100
+        self.ops.append((capi.FUSED_RELU, 0.0, False, -1)); return self
+
+    def Sigmoid(self):                              # FusedSigmoid, fused.go:40,200
+        self.ops.append((capi.FUSED_SIGMOID, 0.0, False, -1)); return self
+
+    def Custom(self, fn):                           # fused.go:108: host closures cannot run on the device; geluFloat32 can
+        if fn is not geluFloat32:
+            raise ErrNotSupported(capi.ERR_NOT_IMPLEMENTED, "FusedOp", "operation not supported")
+        self.ops.append((capi.FUSED_GELU, 0.0, False, -1)); return self
+
+    def Execute(self, x, others, n, *shapes, stream=None):      # fused.go:123
+        others = list(others or [])
+        _ew_len("FusedOp", n, x)
+        ops = (capi.FusedOp * max(len(self.ops), 1))()
+        oi = 0
+        for k, (typ, alpha, bcast, dim) in enumerate(self.ops):
+            bsize = bdim = 0
+            if typ in (capi.FUSED_ADD, capi.FUSED_MUL) and oi < len(others):
+                if bcast and dim >= 0 and oi < len(shapes):
+                    shape = list(shapes[oi])
+                    if dim >= len(shape):           # fused.go:155: the operand silently becomes 0 (Add) / 1 (Mul)
+                        raise ErrNotSupported(capi.ERR_NOT_IMPLEMENTED, "FusedOp", "operation not supported")
+                    bdim = int(shape[dim]); bsize = 1
+                    for d_ in shape[dim:]:
+                        bsize *= int(d_)
+                    if bdim <= 0 or others[oi].size // 4 < bdim:
+                        raise GUDAError(capi.ERR_INVALID_ARG, "FusedOp", "invalid shape")
+                else:
+                    _ew_len("FusedOp", n, others[oi])
+                oi += 1
+            ops[k] = capi.FusedOp(typ, alpha, bsize, bdim)
+        ptrs = (C.c_void_p * max(len(others), 1))(*[o.ptr for o in others])
+        capi.check(_L().guda_fused_execute(x.ptr, ptrs, len(others), n, ops, len(self.ops), _sh(stream)), "FusedOp")
+
+
+def NewFusedKernel():                              # fused.go:45
+    return FusedKernel()
+
+
+def LinearReLU(x, alpha, beta, n, stream=None):    # fused.go:252: x = ReLU(alpha*x + beta)
+    NewFusedKernel().MulScalar(alpha).AddScalar(beta).ReLU().Execute(x, None, n, stream=stream)
+
+
+def GELU(x, n, stream=None):                       # fused.go:261
+    NewFusedKernel().Custom(geluFloat32).Execute(x, None, n, stream=stream)
+
+
 def AddBiasGELU(x, bias, n, stream=None):          # fused_gelu.go:12-41
     capi.check(_L().guda_add_bias_gelu(x.ptr, bias.ptr, n, bias.size // 4, _sh(stream)), "AddBiasGELU")
 

@@ -22,6 +22,14 @@ class ConvParams(C.Structure):
                                        "kernel_width", "stride_h", "stride_w", "pad_h", "pad_w", "dilation_h", "dilation_w", "use_bias")]
 
 
+class FusedOp(C.Structure):
+    """guda_fused_op_t (fused.go:25-32 FusedOp flattened: the broadcast shape becomes (size, dim length))."""
+    _fields_ = [("type", C.c_int), ("alpha", C.c_float), ("broadcast_size", C.c_longlong), ("broadcast_dim", C.c_longlong)]
+
+
+FUSED_ADD, FUSED_MUL, FUSED_ADD_SCALAR, FUSED_MUL_SCALAR, FUSED_RELU, FUSED_SIGMOID, FUSED_GELU = range(7)
+
+
 class DeviceProps(C.Structure):
     _fields_ = [("id", C.c_int), ("name", C.c_char * 128), ("total_mem", C.c_size_t), ("sm_count", C.c_int),
                 ("max_threads", C.c_int), ("cc_major", C.c_int), ("cc_minor", C.c_int), ("l2_bytes", C.c_int)]
@@ -103,6 +111,11 @@ SIGNATURES = {
     "guda_softmax": (i, [vp, C.c_longlong, vp]),
     "guda_layer_norm": (i, [vp, vp, vp, C.c_longlong, f, vp]),
     "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
+    "guda_add": (i, [vp, vp, vp, C.c_longlong, vp]),
+    "guda_multiply": (i, [vp, vp, vp, C.c_longlong, vp]),
+    "guda_relu": (i, [vp, C.c_longlong, vp]),
+    "guda_sigmoid": (i, [vp, C.c_longlong, vp]),
+    "guda_fused_execute": (i, [vp, C.POINTER(vp), i, C.c_longlong, C.POINTER(FusedOp), i, vp]),
     "guda_conv_set_route": (i, [i]),
     "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
     "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),

@@ -200,6 +200,26 @@ int guda_isamax(int n, const float* x, int incx, long long* host_result, guda_st
 int guda_softmax(float* x, long long n, guda_stream_t stream);
 int guda_layer_norm(float* x, const float* gamma, const float* beta, long long n, float eps, guda_stream_t stream);
 
+/* ---- Elementwise device ops: math.go:133-169 Add / Multiply (c = a op b), :230-272 ReLU / Sigmoid (in place; Sigmoid is
+ * activations.go:9-27 SigmoidFloat32 operation by operation).  Stream-ordered, bit-identical to the reference. */
+int guda_add(const float* a, const float* b, float* c, long long n, guda_stream_t stream);
+int guda_multiply(const float* a, const float* b, float* c, long long n, guda_stream_t stream);
+int guda_relu(float* x, long long n, guda_stream_t stream);
+int guda_sigmoid(float* x, long long n, guda_stream_t stream);
+/* fused.go:18-216 FusedKernel: x[idx] is read once, the ops are applied to the value in order, and it is written once.
+ * Types follow fused.go:34-42 (FusedCustom is available for the one function the reference passes to it, geluFloat32,
+ * fused.go:261-267).  A binary op (Add: val += alpha * other, Mul: val *= other) consumes the next `others` pointer and is
+ * skipped when none is left (fused.go:148,170).  broadcast_size > 0 selects other[(idx / broadcast_size) % broadcast_dim]
+ * (fused.go:152-161 with broadcast_size = prod(shape[dim:]), broadcast_dim = shape[dim]); 0 selects other[idx].
+ * LinearReLU (fused.go:252) = {MulScalar alpha, AddScalar beta, ReLU}; GELU (fused.go:261) = {Gelu}. */
+enum { GUDA_FUSED_ADD = 0, GUDA_FUSED_MUL = 1, GUDA_FUSED_ADD_SCALAR = 2, GUDA_FUSED_MUL_SCALAR = 3, GUDA_FUSED_RELU = 4,
+       GUDA_FUSED_SIGMOID = 5, GUDA_FUSED_GELU = 6 };
+#define GUDA_FUSED_MAX_OPS 8
+#define GUDA_FUSED_MAX_OTHERS 4
+typedef struct { int type; float alpha; long long broadcast_size; long long broadcast_dim; } guda_fused_op_t;
+int guda_fused_execute(float* x, const float* const* others, int n_others, long long n, const guda_fused_op_t* ops, int n_ops,
+                       guda_stream_t stream);
+
 /* ---- Conv2D: conv.go:9-31 ConvParams, :69 Conv2D = im2col -> Sgemm -> NCHW placement + bias.
  * input [B][IC][H][W], kernel [OC][IC][KH][KW], bias [OC] (used when use_bias != 0 and bias != NULL), output [B][OC][OH][OW].
  * Blocks until done (it owns a pooled workspace, like the reference's `defer Free(workspace)`). */

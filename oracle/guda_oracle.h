@@ -140,6 +140,15 @@ void orc_generate_f32_masked(float* out, size_t n, uint64_t seed, float lo, floa
 void orc_generate_f64_masked(double* out, size_t n, uint64_t seed, double lo, double hi);
 
 /* ---- tolerance framework (tolerance.go:10-191, tolerance_arch.go:8-127) ---- */
+/* ---- elementwise.c: math.go:133-169,230-272, activations.go:9-27, fused.go:18-216 ---- */
+typedef struct { int type; float alpha; long long bsize; long long bdim; } orc_fused_op_t;
+float orc_sigmoid_f32(float x);
+void orc_ew_add(const float* a, const float* b, float* c, size_t n);
+void orc_ew_mul(const float* a, const float* b, float* c, size_t n);
+void orc_ew_relu(float* x, size_t n);
+void orc_ew_sigmoid(float* x, size_t n);
+void orc_fused_execute(float* x, const float* const* others, int n_others, size_t n, const orc_fused_op_t* ops, int n_ops);
+
 typedef struct { float abs_tol, rel_tol; int ulp_tol; int check_nan, check_inf; } orc_tol_t;
 int  orc_f32_ulp_diff(float a, float b);
 int  orc_f32_near_equal(float a, float b, const orc_tol_t* tol);

@@ -34,6 +34,11 @@ class Verify(C.Structure):
                 ("num_errors", C.c_int64), ("total", C.c_int64), ("first_error", C.c_int64)]
 
 
+class FusedOp(C.Structure):
+    """orc_fused_op_t: type 0 Add, 1 Mul, 2 AddScalar, 3 MulScalar, 4 ReLU, 5 Sigmoid, 6 Custom(geluFloat32)."""
+    _fields_ = [("type", C.c_int), ("alpha", C.c_float), ("bsize", C.c_longlong), ("bdim", C.c_longlong)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -63,6 +68,12 @@ def lib():
         L.orc_fused_gemm_bias_relu.argtypes = [i, i, i, i, i, f, fp, i, fp, i, f, fp, i, fp, i]
         L.orc_fused_gemm_bias_gelu.argtypes = [i, i, i, i, i, f, fp, i, fp, i, f, fp, i, fp, i, i]
         L.orc_add_bias_gelu.argtypes = [fp, fp, i, i]; L.orc_add_bias_gelu.restype = None
+        L.orc_sigmoid_f32.argtypes = [f]; L.orc_sigmoid_f32.restype = f
+        L.orc_ew_add.argtypes = [fp, fp, fp, sz]; L.orc_ew_add.restype = None
+        L.orc_ew_mul.argtypes = [fp, fp, fp, sz]; L.orc_ew_mul.restype = None
+        L.orc_ew_relu.argtypes = [fp, sz]; L.orc_ew_relu.restype = None
+        L.orc_ew_sigmoid.argtypes = [fp, sz]; L.orc_ew_sigmoid.restype = None
+        L.orc_fused_execute.argtypes = [fp, C.POINTER(fp), i, sz, C.POINTER(FusedOp), i]; L.orc_fused_execute.restype = None
         L.orc_to_bf16.argtypes = [f]; L.orc_to_bf16.restype = C.c_uint16
         L.orc_bf16_to_f32.argtypes = [C.c_uint16]; L.orc_bf16_to_f32.restype = f
         L.orc_f32_to_f16.argtypes = [f]; L.orc_f32_to_f16.restype = C.c_uint16
@@ -203,6 +214,37 @@ def tanh(x):
 def exp(x):
     x = _f32(x)
     return np.array([lib().orc_exp_f32(float(v)) for v in x.ravel()], dtype=np.float32).reshape(x.shape)
+
+
+def ew_add(a, b):                       # math.go:133
+    a, b = _f32(a), _f32(b); c = np.empty_like(a)
+    lib().orc_ew_add(_p(a, C.c_float), _p(b, C.c_float), _p(c, C.c_float), a.size)
+    return c
+
+
+def ew_mul(a, b):                       # math.go:152
+    a, b = _f32(a), _f32(b); c = np.empty_like(a)
+    lib().orc_ew_mul(_p(a, C.c_float), _p(b, C.c_float), _p(c, C.c_float), a.size)
+    return c
+
+
+def ew_relu(x):                         # math.go:236 (in place on a copy)
+    x = _f32(x).copy(); lib().orc_ew_relu(_p(x, C.c_float), x.size); return x
+
+
+def ew_sigmoid(x):                      # math.go:255 -> activations.go:9
+    x = _f32(x).copy(); lib().orc_ew_sigmoid(_p(x, C.c_float), x.size); return x
+
+
+def fused_execute(x, others, ops):
+    """fused.go:123 FusedKernel.Execute on a copy of x.  ops: list of (type, alpha, bsize, bdim)."""
+    x = _f32(x).copy()
+    others = [_f32(o) for o in others]
+    fp = C.POINTER(C.c_float)
+    arr = (fp * max(len(others), 1))(*[_p(o, C.c_float) for o in others])
+    oparr = (FusedOp * max(len(ops), 1))(*[FusedOp(int(t), float(a), int(bs), int(bd)) for t, a, bs, bd in ops])
+    lib().orc_fused_execute(_p(x, C.c_float), arr, len(others), x.size, oparr, len(ops))
+    return x
 
 
 def ref_gelu(x):

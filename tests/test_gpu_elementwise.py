@@ -1,0 +1,116 @@
+"""GPU parity for the elementwise device ops and FusedKernel.Execute (guda_b200/csrc/elementwise.cu) through the C ABI:
+bit for bit against oracle/elementwise.c (NaN compared as NaN)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def g():
+    import guda_b200 as G
+    G.Init(0)
+    return G
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle
+    return oracle
+
+
+def _specials(O, n, seed, lo=-12.0, hi=12.0):
+    x = O.uniform_f32(n, seed, lo, hi)
+    s = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 10.0, -10.0, 10.000001, -10.000001, 88.8, -87.4, 1e-45, -1e-45, 3.4e38], np.float32)
+    k = min(n, s.size)
+    x[:k] = s[:k]
+    return x
+
+
+def _same(a, b):
+    """Same bits, except that any NaN equals any NaN (x86 and the GPU give 0 * Inf different sign / payload bits)."""
+    nan = np.isnan(a)
+    return np.array_equal(nan, np.isnan(b)) and np.array_equal(a[~nan].view(np.uint32), b[~nan].view(np.uint32))
+
+
+@pytest.mark.parametrize("n", [1, 3, 4, 255, 1000, 4099, 1 << 20, (1 << 22) + 5])
+def test_add_multiply_relu_sigmoid_bit_exact(g, O, n):
+    a, b = _specials(O, n, 1 + n, -3e38, 3e38), _specials(O, n, 2 + n, -3e38, 3e38)[::-1].copy()
+    da, db, dc = g.to_device(a), g.to_device(b), g.Malloc(n * 4)
+    with np.errstate(all="ignore"):
+        g.Add(da, db, dc, n); assert _same(dc.Float32()[:n], O.ew_add(a, b))
+        g.Multiply(da, db, dc, n); assert _same(dc.Float32()[:n], O.ew_mul(a, b))
+    x = _specials(O, n, 3 + n)
+    dx = g.to_device(x); g.ReLU(dx, n); assert _same(dx.Float32()[:n], O.ew_relu(x)); g.Free(dx)
+    dx = g.to_device(x); g.Sigmoid(dx, n); assert _same(dx.Float32()[:n], O.ew_sigmoid(x)); g.Free(dx)
+    for p in (da, db, dc):
+        g.Free(p)
+
+
+def test_unaligned_views_and_untouched_tail(g, O):
+    n = 1001
+    x = _specials(O, n + 8, 5)
+    dx = g.to_device(x)
+    view = dx.Offset(4)                                   # 4-byte aligned only: the scalar route
+    g.Sigmoid(view, n)
+    got = dx.Float32()[:n + 8]
+    assert got[0] == x[0] or (np.isnan(got[0]) and np.isnan(x[0]))
+    assert _same(got[1:n + 1], O.ew_sigmoid(x[1:n + 1])) and _same(got[n + 1:], x[n + 1:])
+    g.Free(dx)
+
+
+def test_reference_fused_operations(g, O):
+    """guda_test.go:193-240: ReLU(2*x + bias) through NewFusedKernel().MulScalar(2).Add(1).ReLU().Execute(x, [bias], N)."""
+    N = 1000
+    x, bias = O.uniform_f32(N, 11), O.uniform_f32(N, 12, 0.0, 0.1)
+    dx, dbias = g.to_device(x), g.to_device(bias)
+    g.NewFusedKernel().MulScalar(2.0).Add(1.0).ReLU().Execute(dx, [dbias], N)
+    g.Synchronize()
+    got = dx.Float32()[:N]
+    assert np.all(np.abs(got - np.maximum(2.0 * x.astype(np.float64) + bias, 0)) <= 1e-5)          # the reference's check
+    assert _same(got, O.fused_execute(x, [bias], [(3, 2.0, 0, 0), (0, 1.0, 0, 0), (4, 0.0, 0, 0)]))
+    g.Free(dx); g.Free(dbias)
+
+
+@pytest.mark.parametrize("n", [7, 4096, (1 << 20) + 3])
+def test_fused_op_lists_bit_exact(g, O, n):
+    x = _specials(O, n, 21, -6, 6)
+    o1, o2 = O.uniform_f32(n, 22), O.uniform_f32(n, 23, 0.5, 1.5)
+    d1, d2 = g.to_device(o1), g.to_device(o2)
+    # every op type in one list; the third binary op has no operand left and is skipped
+    dx = g.to_device(x)
+    g.NewFusedKernel().Add(1.5).Multiply().AddScalar(-0.25).MulScalar(0.75).Sigmoid().Add(2.0).ReLU().Execute(dx, [d1, d2], n)
+    want = O.fused_execute(x, [o1, o2], [(0, 1.5, 0, 0), (1, 0, 0, 0), (2, -0.25, 0, 0), (3, 0.75, 0, 0), (5, 0, 0, 0), (0, 2.0, 0, 0), (4, 0, 0, 0)])
+    assert _same(dx.Float32()[:n], want)
+    g.Free(dx)
+    dx = g.to_device(x); g.LinearReLU(dx, 1.7, -0.3, n)
+    assert _same(dx.Float32()[:n], O.fused_execute(x, [], [(3, 1.7, 0, 0), (2, -0.3, 0, 0), (4, 0, 0, 0)])); g.Free(dx)
+    dx = g.to_device(x); g.GELU(dx, n)
+    assert _same(dx.Float32()[:n], O.fused_execute(x, [], [(6, 0, 0, 0)])); g.Free(dx)
+    g.Free(d1); g.Free(d2)
+
+
+def test_fused_broadcast(g, O):
+    rows, cols = 37, 24
+    x = O.uniform_f32(rows * cols, 31)
+    b = O.uniform_f32(cols, 32)
+    dx, db = g.to_device(x), g.to_device(b)
+    g.NewFusedKernel().AddBroadcast(0.5, 1).ReLU().Execute(dx, [db], rows * cols, [rows, cols])
+    want = O.fused_execute(x, [b], [(0, 0.5, cols, cols), (4, 0, 0, 0)])          # fused.go:152-161: size = prod(shape[1:]), dim = shape[1]
+    assert _same(dx.Float32()[:rows * cols], want)
+    g.Free(dx); g.Free(db)
+
+
+def test_errors(g):
+    z = g.Malloc(64)
+    with pytest.raises(g.ErrNotSupported):
+        g.NewFusedKernel().Custom(lambda v: v)
+    with pytest.raises(IndexError):
+        g.Add(z, z, z, 17)
+    fk = g.NewFusedKernel()
+    for _ in range(9):
+        fk.ReLU()
+    with pytest.raises(g.GUDAError):
+        fk.Execute(z, None, 16)
+    g.ReLU(z, 0)
+    g.Free(z)

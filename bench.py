@@ -263,6 +263,22 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     for x in rb:
         g.Free(x)
 
+    # ---- elementwise device ops (math.go:133-169, fused.go:252): n = 2^26 (256 MiB per vector, beyond L2)
+    ne = 1 << 26
+    ea, eb, ec = g.Malloc(ne * 4), g.Malloc(ne * 4), g.Malloc(ne * 4)
+    g.FillUniform(ea, 1, ne, ne, 700); g.FillUniform(eb, 1, ne, ne, 701)
+    for key, fn, bpe in (("add_64M", lambda: g.Add(ea, eb, ec, ne), 12.0), ("linear_relu_64M", lambda: g.LinearReLU(ec, 1.01, 0.1, ne), 8.0),
+                         ("gelu_64M", lambda: g.GELU(ec, ne), 8.0)):
+        for _ in range(3):
+            fn()
+        ms = dev.time_ms(fn, 20)
+        gbs = bpe * ne / (ms * 1e-3) / 1e9
+        out[key] = {"value": gbs, "unit": "GB/s", "ms": ms,
+                    "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                                 "peak_source": peaks["source"], "algorithmic_bytes": bpe * ne, "traffic": ncu_traffic(key)}}
+    for p in (ea, eb, ec):
+        g.Free(p)
+
     # ---- C1: SGEMM 1024^3 (README headline), alpha=1 beta=0; 16 rotating triples (192 MiB)
     n = 1024
     sets = []

@@ -63,6 +63,9 @@ var (
 	ErrInvalidDevice = NewInvalidArgError("SetDevice", "invalid device ID")
 	ErrNoDevice      = &GUDAError{Type: ErrTypeDevice, Op: "Device", Message: "no compute device available"}
 	ErrNotSupported  = errors.New("operation not supported")
+	// fused.go:12-16
+	ErrInvalidShape     = NewInvalidArgError("FusedOp", "invalid shape")
+	ErrInvalidParameter = NewInvalidArgError("FusedOp", "invalid parameter")
 )
 
 func isType(err error, t ErrorType) bool {

@@ -234,6 +234,29 @@ inline void Dger(int m, int n, double alpha, const DevicePtr& x, int incX, const
   check(guda_dger(m, n, alpha, f64(x), incX, f64(y), incY, f64(a), lda, nullptr), "Dger");
 }
 
+// math.go:133-169, :230-272 elementwise device ops; fused.go:252 LinearReLU, :261 GELU (FusedKernel op lists)
+inline void ew_len(const char* op, long long n, std::initializer_list<const DevicePtr*> ps) {
+  for (const DevicePtr* p : ps) if (n < 0 || (long long)(p->size / 4) < n) throw std::out_of_range(std::string(op) + ": index out of range");
+}
+inline void Add(const DevicePtr& a, const DevicePtr& b, const DevicePtr& c, long long n) {
+  ew_len("Add", n, {&a, &b, &c}); check(guda_add(f32(a), f32(b), f32(c), n, nullptr), "Add");
+}
+inline void Multiply(const DevicePtr& a, const DevicePtr& b, const DevicePtr& c, long long n) {
+  ew_len("Multiply", n, {&a, &b, &c}); check(guda_multiply(f32(a), f32(b), f32(c), n, nullptr), "Multiply");
+}
+inline void ReLU(const DevicePtr& x, long long n) { ew_len("ReLU", n, {&x}); check(guda_relu(f32(x), n, nullptr), "ReLU"); }
+inline void Sigmoid(const DevicePtr& x, long long n) { ew_len("Sigmoid", n, {&x}); check(guda_sigmoid(f32(x), n, nullptr), "Sigmoid"); }
+inline void LinearReLU(const DevicePtr& x, float alpha, float beta, long long n) {
+  ew_len("FusedOp", n, {&x});
+  const guda_fused_op_t ops[3] = {{GUDA_FUSED_MUL_SCALAR, alpha, 0, 0}, {GUDA_FUSED_ADD_SCALAR, beta, 0, 0}, {GUDA_FUSED_RELU, 0.f, 0, 0}};
+  check(guda_fused_execute(f32(x), nullptr, 0, n, ops, 3, nullptr), "FusedOp");
+}
+inline void GELU(const DevicePtr& x, long long n) {
+  ew_len("FusedOp", n, {&x});
+  const guda_fused_op_t op = {GUDA_FUSED_GELU, 0.f, 0, 0};
+  check(guda_fused_execute(f32(x), nullptr, 0, n, &op, 1, nullptr), "FusedOp");
+}
+
 // conv.go:9-31 ConvParams, :69 Conv2D
 struct ConvParams {
   int BatchSize = 0, InChannels = 0, InHeight = 0, InWidth = 0, OutChannels = 0, KernelHeight = 0, KernelWidth = 0;

@@ -60,8 +60,8 @@ __device__ __forceinline__ float gelu_exp_f32(float x) {
   if (x < -87.3f) return 0.0f;
   const double ln2 = 0.6931471805599453094;
   // k = int(math.Floor(float64(x) / ln2)) (activations.go:71).  The fp64 division is replaced by a multiplication with the
-  // correctly rounded reciprocal: oracle/expcheck.c walks all 2,237,661,186 float32 inputs that reach this line and finds
-  // floor(x / ln2) == floor(x * (1 / ln2)) for every one of them (tests/test_oracle_elementwise.py runs it).
+  // correctly rounded reciprocal: an exhaustive host-side check (expcheck.c in the test infrastructure, run by the CPU test
+  // suite) walks all 2,237,661,186 float32 inputs that reach this line and finds floor(x / ln2) == floor(x * (1 / ln2)) for each.
   int k = (int)floor(__dmul_rn((double)x, 0x1.71547652b82fep+0));
   float r = __fsub_rn(x, __fmul_rn((float)k, (float)ln2));
   float r2 = __fmul_rn(r, r), r3 = __fmul_rn(r2, r), r4 = __fmul_rn(r2, r2), r5 = __fmul_rn(r4, r);
@@ -71,7 +71,7 @@ __device__ __forceinline__ float gelu_exp_f32(float x) {
   e = __fadd_rn(e, __fmul_rn(0.0416666679084301f, r4));
   e = __fadd_rn(e, __fmul_rn(0.0083333337679505f, r5));
   // float32(math.Ldexp(float64(e), k)) (activations.go:88): k is in [-126, 127] and e in [1, 2], so 2^k is a normal float and
-  // the product rounds once from the same exact value (overflow to +Inf included) -- also checked by oracle/expcheck.c
+  // the product rounds once from the same exact value (overflow to +Inf included) -- also covered by expcheck.c
   return __fmul_rn(e, __int_as_float((k + 127) << 23));
 }
 __device__ __forceinline__ float gelu_tanh_f32(float x) {

@@ -664,7 +664,7 @@ def Conv2D(input, kernel, bias, output, params, stream=None):          # conv.go
 
 
 def SetConvRoute(route):
-    """0 implicit GEMM (default), 1 materialised im2col, 2/3 implicit with the 64x128/64x64 tile forced,
+    """0 implicit GEMM (default), 1 materialised im2col, 2/3/4 implicit with the 64x128/64x64/128x128 tile forced,
     -1 default / environment (guda_conv_set_route)."""
     capi.check(_L().guda_conv_set_route(int(route)), "SetConvRoute")
 

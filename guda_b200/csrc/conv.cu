@@ -203,7 +203,7 @@ static int conv_route_env() {          // GUDA_CONV_ROUTE=im2col forces the mate
   static const int r = [] { const char* e = getenv("GUDA_CONV_ROUTE"); return (e && !strcmp(e, "im2col")) ? 1 : 0; }();
   return r;
 }
-static int g_conv_route = -1;          // -1: environment, 0: implicit, 1: im2col, 2/3: implicit with the 64x128 / 64x64 tile
+static int g_conv_route = -1;          // -1: environment, 0: implicit, 1: im2col, 2/3/4: implicit with the 64x128 / 64x64 / 128x128 tile
 
 struct ConvTemp {
   void* p = nullptr;
@@ -247,26 +247,38 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     if ((rc = guda_malloc(&tab.p, (size_t)K * sizeof(int2)))) return rc;
     conv_ktab_kernel<<<(unsigned)((K + 127) / 128), 128, 0, s>>>((int2*)tab.p, (int)K, g);
     if ((rc = check_launch("conv_ktab"))) return rc;
-    // CTA tile 64 x {128, 64}: like Sgemm's choice (gemm.cu launch_simt_one), the smallest estimated makespan
-    // ceil(tiles / SMs) * BM*BN / efficiency (4x8 micro-tile 0.85, 4x4 0.6).  A 64x256 tile (4x16 micro-tile, 122 registers,
-    // 16 gathers per thread per k-tile) was measured at 15 TFLOP/s against 28 for 64x128 and is not built.
-    const int forced = route == 2 ? 128 : route == 3 ? 64 : 0;      // A/B and test knob (guda_conv_set_route)
-    const long long sms = sm_count(), mt = (g.out_c + 63) / 64;
-    auto makespan = [&](int bn, double eff) { return (double)((mt * ((N + bn - 1) / bn) + sms - 1) / sms) * 64.0 * bn / eff; };
-    int bn = 128;
-    if (forced) bn = forced;
-    else bn = makespan(128, 0.85) <= makespan(64, 0.6) ? 128 : 64;
-    dim3 grid((unsigned)((N + bn - 1) / bn), (unsigned)mt);
+    // CTA tile 128x128 (8x8 micro-tile, 16 x 16 threads), 64x128 (8x4, 32 x 8 threads) or 64x64 (4x4): like Sgemm's choice
+    // (gemm.cu launch_simt_one), the smallest estimated makespan ceil(tiles / SMs) * BM*BN / efficiency.  A 64x256 tile (4x16
+    // micro-tile, 122 registers, 16 gathers per thread per k-tile) was measured at 15 TFLOP/s against 28 for 64x128 and is not built.
+    const long long sms = sm_count();
+    auto makespan = [&](int bm, int bn, double eff) {
+      const long long tiles = ((g.out_c + bm - 1) / bm) * ((N + bn - 1) / bn);
+      return (double)((tiles + sms - 1) / sms) * bm * bn / eff;
+    };
+    int bm = 64, bn = 128;
+    if (route == 2) { bm = 64; bn = 128; }              // A/B and test knob (guda_conv_set_route)
+    else if (route == 3) { bm = 64; bn = 64; }
+    else if (route == 4) { bm = 128; bn = 128; }
+    else {
+      const double t_big = makespan(128, 128, 1.0), t_mid = makespan(64, 128, 0.85), t_small = makespan(64, 64, 0.6);
+      const long long big_tiles = ((g.out_c + 127) / 128) * ((N + 127) / 128);
+      // the 8x8 tile needs two resident CTAs per SM to hide its gathers (measured: 98 tiles on 148 SMs lose to 64x64)
+      if (big_tiles >= 2 * sms && t_big < t_mid && t_big <= t_small) { bm = 128; bn = 128; }
+      else if (t_mid <= t_small) { bm = 64; bn = 128; }
+      else { bm = 64; bn = 64; }
+    }
+    dim3 grid((unsigned)((N + bn - 1) / bn), (unsigned)((g.out_c + bm - 1) / bm));
     if (grid.y > 65535) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: too many output channels for one launch");
-    const bool fasta = (g.out_c % 64 == 0) && (K % 16 == 0) && ((uintptr_t)kernel % 16 == 0);
+    const bool fasta = (g.out_c % bm == 0) && (K % 16 == 0) && ((uintptr_t)kernel % 16 == 0);
     const int2* kt = (const int2*)tab.p;
-#define GUDA_CONV_LAUNCH(BN_, MINB_, TXN_)                                                                                          \
+#define GUDA_CONV_LAUNCH(BM_, BN_, MINB_, TXN_)                                                                                     \
     do {                                                                                                                        \
-      if (fasta) conv_igemm_kernel<64, BN_, true, MINB_, TXN_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P);  \
-      else       conv_igemm_kernel<64, BN_, false, MINB_, TXN_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P); \
+      if (fasta) conv_igemm_kernel<BM_, BN_, true, MINB_, TXN_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P);  \
+      else       conv_igemm_kernel<BM_, BN_, false, MINB_, TXN_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P); \
     } while (0)
-    if (bn == 128) GUDA_CONV_LAUNCH(128, 3, 32);
-    else GUDA_CONV_LAUNCH(64, 4, 16);
+    if (bm == 128) GUDA_CONV_LAUNCH(128, 128, 2, 16);
+    else if (bn == 128) GUDA_CONV_LAUNCH(64, 128, 3, 32);
+    else GUDA_CONV_LAUNCH(64, 64, 4, 16);
 #undef GUDA_CONV_LAUNCH
     if ((rc = check_launch("conv_igemm"))) return rc;
     GUDA_CUDA(cudaStreamSynchronize(s));        // the k table returns to the pool when this function exits
@@ -295,9 +307,9 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
 }
 
 /* route switch for A/B measurements and the route-equality tests: 0 implicit GEMM (default), 1 materialised im2col,
- * 2 / 3 implicit GEMM with the 64x128 / 64x64 CTA tile forced, -1 environment */
+ * 2 / 3 / 4 implicit GEMM with the 64x128 / 64x64 / 128x128 CTA tile forced, -1 environment */
 extern "C" int guda_conv_set_route(int route) {
-  if (route < -1 || route > 3) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: route must be -1 .. 3");
+  if (route < -1 || route > 4) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: route must be -1 .. 4");
   g_conv_route = route;
   return GUDA_OK;
 }

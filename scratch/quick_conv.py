@@ -13,14 +13,14 @@ def bench(B, IC, H, W, OC, KH, KW, s, p):
     g.FillUniform(x, 1, n_in, n_in, 1); g.FillUniform(w, 1, n_w, n_w, 2); g.FillUniform(b, 1, OC, OC, 3)
     fl = 2.0*OC*IC*KH*KW*B*oh*ow
     res = []
-    for r in (0, 1, 2, 3):
+    for r in (0, 1, 2, 3, 4):
         g.SetConvRoute(r)
         for _ in range(2): g.Conv2D(x, w, b, o, cp)
         e0.Record()
         for _ in range(10): g.Conv2D(x, w, b, o, cp)
         e1.Record(); e1.Synchronize()
         ms = g.ElapsedTime(e0, e1)/10
-        res.append("%s %.3f ms %.1f TF" % (("auto", "im2col", "t128", "t64")[r], ms, fl/ms/1e9))
+        res.append("%s %.3f ms %.1f TF" % (("auto", "im2col", "t64x128", "t64x64", "t128x128")[r], ms, fl/ms/1e9))
     g.SetConvRoute(-1)
     print("conv B%d %dx%dx%d -> %d k%dx%d s%d p%d: %s" % (B, IC, H, W, OC, KH, KW, s, p, " | ".join(res)), flush=True)
     for q in (x, w, b, o): g.Free(q)
@@ -30,3 +30,5 @@ bench(32, 256, 14, 14, 256, 3, 3, 1, 1)
 bench(32, 3, 224, 224, 64, 7, 7, 2, 3)
 bench(1, 64, 56, 56, 64, 3, 3, 1, 1)
 bench(64, 256, 56, 56, 64, 1, 1, 1, 0)
+bench(32, 128, 56, 56, 256, 3, 3, 1, 1)
+bench(32, 512, 7, 7, 512, 3, 3, 1, 1)

@@ -60,7 +60,7 @@ SHAPES = [_params(1, 32, 32, 32, 64, 3, 3, 1, 1), _params(1, 64, 56, 56, 64, 3, 
           _params(1, 16, 4, 4, 16, 1, 1), _params(2, 128, 12, 12, 128, 3, 3, 1, 1)]
 
 
-@pytest.fixture(params=[0, 1, 2, 3], ids=["implicit", "im2col", "implicit-64x128", "implicit-64x64"])
+@pytest.fixture(params=[0, 1, 2, 3, 4], ids=["implicit", "im2col", "implicit-64x128", "implicit-64x64", "implicit-128x128"])
 def route(request, g):
     g.SetConvRoute(request.param)
     yield request.param
@@ -75,7 +75,7 @@ def test_conv2d_routes_bit_identical_large(g, O):
     w[::5] = 0.0
     b = O.uniform_f32(64, 13)
     outs = []
-    for r in (0, 1, 2, 3):
+    for r in (0, 1, 2, 3, 4):
         g.SetConvRoute(r)
         outs.append(_run(g, p, x, w, b))
     g.SetConvRoute(-1)

@@ -66,6 +66,7 @@ var (
 	// fused.go:12-16
 	ErrInvalidShape     = NewInvalidArgError("FusedOp", "invalid shape")
 	ErrInvalidParameter = NewInvalidArgError("FusedOp", "invalid parameter")
+	ErrInvalidAxis      = NewInvalidArgError("FusedOp", "invalid axis")
 )
 
 func isType(err error, t ErrorType) bool {

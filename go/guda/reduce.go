@@ -126,3 +126,34 @@ func LayerNorm(x DevicePtr, gamma, beta DevicePtr, n int, eps float32) error {
 	}
 	return status(C.guda_layer_norm((*C.float)(x.ptr), g, b, C.longlong(n), C.float(eps), nil), "LayerNorm")
 }
+
+// ReduceSum mirrors reduce.go:105: a sum along one axis of a row-major shape[0] x shape[1] matrix (axis 0 -> out[shape[1]],
+// axis 1 -> out[shape[0]]).  Every output is one sequential float32 chain in the reference's order, so the bits match.
+func ReduceSum(x DevicePtr, shape []int, axis int, out DevicePtr) error {
+	return reduceAxis(x, shape, axis, out, false)
+}
+
+// ReduceMax mirrors reduce.go:139 (first element, then `val > max`).
+func ReduceMax(x DevicePtr, shape []int, axis int, out DevicePtr) error {
+	return reduceAxis(x, shape, axis, out, true)
+}
+
+func reduceAxis(x DevicePtr, shape []int, axis int, out DevicePtr, isMax bool) error {
+	if len(shape) != 2 {
+		return ErrInvalidShape
+	}
+	m, n := shape[0], shape[1]
+	if axis != 0 && axis != 1 {
+		return ErrInvalidAxis
+	}
+	outLen := m
+	if axis == 0 {
+		outLen = n
+	}
+	checkLen("Reduce", m*n, x)
+	checkLen("Reduce", outLen, out)
+	if isMax {
+		return status(C.guda_reduce_max_axis((*C.float)(x.ptr), C.int(m), C.int(n), C.int(axis), (*C.float)(out.ptr), nil), "ReduceMax")
+	}
+	return status(C.guda_reduce_sum_axis((*C.float)(x.ptr), C.int(m), C.int(n), C.int(axis), (*C.float)(out.ptr), nil), "ReduceSum")
+}

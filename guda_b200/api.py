@@ -597,6 +597,25 @@ class FusedKernel:
         capi.check(_L().guda_fused_execute(x.ptr, ptrs, len(others), n, ops, len(self.ops), _sh(stream)), "FusedOp")
 
 
+def _reduce_axis(fn, op, x, shape, axis, out, stream):
+    if len(shape) != 2:
+        raise GUDAError(capi.ERR_INVALID_ARG, "FusedOp", "invalid shape")          # ErrInvalidShape, reduce.go:106
+    m, n = int(shape[0]), int(shape[1])
+    if axis not in (0, 1):
+        raise GUDAError(capi.ERR_INVALID_ARG, "FusedOp", "invalid axis")           # ErrInvalidAxis, reduce.go:131
+    _ew_len(op, m * n, x)
+    _ew_len(op, n if axis == 0 else m, out)
+    capi.check(getattr(_L(), fn)(x.ptr, m, n, axis, out.ptr, _sh(stream)), op)
+
+
+def ReduceSum(x, shape, axis, out, stream=None):   # reduce.go:105
+    _reduce_axis("guda_reduce_sum_axis", "ReduceSum", x, shape, axis, out, stream)
+
+
+def ReduceMax(x, shape, axis, out, stream=None):   # reduce.go:139
+    _reduce_axis("guda_reduce_max_axis", "ReduceMax", x, shape, axis, out, stream)
+
+
 def NewFusedKernel():                              # fused.go:45
     return FusedKernel()
 

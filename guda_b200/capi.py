@@ -111,6 +111,8 @@ SIGNATURES = {
     "guda_softmax": (i, [vp, C.c_longlong, vp]),
     "guda_layer_norm": (i, [vp, vp, vp, C.c_longlong, f, vp]),
     "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
+    "guda_reduce_sum_axis": (i, [vp, i, i, i, vp, vp]),
+    "guda_reduce_max_axis": (i, [vp, i, i, i, vp, vp]),
     "guda_add": (i, [vp, vp, vp, C.c_longlong, vp]),
     "guda_multiply": (i, [vp, vp, vp, C.c_longlong, vp]),
     "guda_relu": (i, [vp, C.c_longlong, vp]),

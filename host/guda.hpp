@@ -257,6 +257,16 @@ inline void GELU(const DevicePtr& x, long long n) {
   check(guda_fused_execute(f32(x), nullptr, 0, n, &op, 1, nullptr), "FusedOp");
 }
 
+// reduce.go:105 ReduceSum / :139 ReduceMax over a row-major m x n matrix (axis 0 -> out[n], axis 1 -> out[m])
+inline void ReduceSum(const DevicePtr& x, int m, int n, int axis, const DevicePtr& out) {
+  ew_len("ReduceSum", (long long)m * n, {&x}); ew_len("ReduceSum", axis == 0 ? n : m, {&out});
+  check(guda_reduce_sum_axis(f32(x), m, n, axis, f32(out), nullptr), "ReduceSum");
+}
+inline void ReduceMax(const DevicePtr& x, int m, int n, int axis, const DevicePtr& out) {
+  ew_len("ReduceMax", (long long)m * n, {&x}); ew_len("ReduceMax", axis == 0 ? n : m, {&out});
+  check(guda_reduce_max_axis(f32(x), m, n, axis, f32(out), nullptr), "ReduceMax");
+}
+
 // conv.go:9-31 ConvParams, :69 Conv2D
 struct ConvParams {
   int BatchSize = 0, InChannels = 0, InHeight = 0, InWidth = 0, OutChannels = 0, KernelHeight = 0, KernelWidth = 0;

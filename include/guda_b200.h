@@ -200,6 +200,12 @@ int guda_isamax(int n, const float* x, int incx, long long* host_result, guda_st
 int guda_softmax(float* x, long long n, guda_stream_t stream);
 int guda_layer_norm(float* x, const float* gamma, const float* beta, long long n, float eps, guda_stream_t stream);
 
+/* reduce.go:105-178 ReduceSum / ReduceMax over a row-major m x n device matrix: axis 0 -> out[n] (chain over rows), axis 1 ->
+ * out[m] (chain over columns).  Each output is one sequential chain in the reference's order (bit-identical); device result,
+ * stream-ordered.  Any other axis: GUDA_ERR_INVALID_ARG "invalid axis" (ErrInvalidAxis). */
+int guda_reduce_sum_axis(const float* x, int m, int n, int axis, float* out, guda_stream_t stream);
+int guda_reduce_max_axis(const float* x, int m, int n, int axis, float* out, guda_stream_t stream);
+
 /* ---- Elementwise device ops: math.go:133-169 Add / Multiply (c = a op b), :230-272 ReLU / Sigmoid (in place; Sigmoid is
  * activations.go:9-27 SigmoidFloat32 operation by operation).  Stream-ordered, bit-identical to the reference. */
 int guda_add(const float* a, const float* b, float* c, long long n, guda_stream_t stream);

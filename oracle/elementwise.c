@@ -52,3 +52,21 @@ void orc_fused_execute(float* x, const float* const* others, int n_others, size_
     x[idx] = val;
   }
 }
+
+/* reduce.go:105-178 ReduceSum / ReduceMax over a row-major m x n matrix.  axis 0: out[j] = chain over rows; axis 1: out[i] =
+ * chain over columns.  Sum starts from float32(0) and adds in index order; Max starts from the first element and replaces it
+ * only when `val > max` (so a leading NaN stays, later NaNs are skipped, and of equal zeros the first one wins). */
+int orc_reduce_axis(const float* x, int m, int n, int axis, int is_max, float* out) {
+  if (axis != 0 && axis != 1) return -1;
+  const int outer = axis == 0 ? n : m, inner = axis == 0 ? m : n;
+  for (int o = 0; o < outer; o++) {
+    float acc = is_max ? (axis == 0 ? x[o] : x[(size_t)o * n]) : 0.0f;
+    for (int k = is_max ? 1 : 0; k < inner; k++) {
+      const float v = axis == 0 ? x[(size_t)k * n + o] : x[(size_t)o * n + k];
+      if (is_max) { if (v > acc) acc = v; }
+      else acc = acc + v;
+    }
+    out[o] = acc;
+  }
+  return 0;
+}

@@ -73,6 +73,7 @@ def lib():
         L.orc_ew_mul.argtypes = [fp, fp, fp, sz]; L.orc_ew_mul.restype = None
         L.orc_ew_relu.argtypes = [fp, sz]; L.orc_ew_relu.restype = None
         L.orc_ew_sigmoid.argtypes = [fp, sz]; L.orc_ew_sigmoid.restype = None
+        L.orc_reduce_axis.argtypes = [fp, i, i, i, i, fp]
         L.orc_fused_execute.argtypes = [fp, C.POINTER(fp), i, sz, C.POINTER(FusedOp), i]; L.orc_fused_execute.restype = None
         L.orc_to_bf16.argtypes = [f]; L.orc_to_bf16.restype = C.c_uint16
         L.orc_bf16_to_f32.argtypes = [C.c_uint16]; L.orc_bf16_to_f32.restype = f
@@ -234,6 +235,13 @@ def ew_relu(x):                         # math.go:236 (in place on a copy)
 
 def ew_sigmoid(x):                      # math.go:255 -> activations.go:9
     x = _f32(x).copy(); lib().orc_ew_sigmoid(_p(x, C.c_float), x.size); return x
+
+
+def reduce_axis(x, m, n, axis, is_max=False):          # reduce.go:105 ReduceSum / :139 ReduceMax
+    x = _f32(x)
+    out = np.empty(n if axis == 0 else m, np.float32)
+    _chk(lib().orc_reduce_axis(_p(x, C.c_float), m, n, axis, int(is_max), _p(out, C.c_float)))
+    return out
 
 
 def fused_execute(x, others, ops):

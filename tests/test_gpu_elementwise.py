@@ -114,3 +114,36 @@ def test_errors(g):
         fk.Execute(z, None, 16)
     g.ReLU(z, 0)
     g.Free(z)
+
+
+@pytest.mark.parametrize("m,n", [(1, 1), (7, 5), (33, 129), (64, 128), (100, 1000), (1000, 100), (257, 515), (2048, 4096), (5, 100003)])
+@pytest.mark.parametrize("axis", [0, 1])
+def test_reduce_sum_max_axis_bit_exact(g, O, m, n, axis):
+    x = O.uniform_f32(m * n, 41 + m + n, -100, 100)
+    x[::37] = -0.0
+    if m * n > 20:
+        x[3] = np.nan; x[n if m > 1 else 5] = np.inf; x[-1] = -np.inf
+    dx, dout = g.to_device(x), g.Malloc((n if axis == 0 else m) * 4)
+    k = n if axis == 0 else m
+    g.ReduceSum(dx, [m, n], axis, dout)
+    with np.errstate(all="ignore"):
+        assert _same(dout.Float32()[:k], O.reduce_axis(x, m, n, axis))
+        g.ReduceMax(dx, [m, n], axis, dout)
+        assert _same(dout.Float32()[:k], O.reduce_axis(x, m, n, axis, True))
+    g.Free(dx); g.Free(dout)
+
+
+def test_reduce_axis_unaligned_and_errors(g, O):
+    m, n = 37, 130
+    x = O.uniform_f32(m * n + 1, 77)
+    dx, dout = g.to_device(x), g.Malloc(max(m, n) * 4)
+    view = dx.Offset(4)
+    g.ReduceSum(view, [m, n], 1, dout)
+    assert _same(dout.Float32()[:m], O.reduce_axis(x[1:], m, n, 1))
+    with pytest.raises(g.GUDAError) as e:
+        g.ReduceSum(dx, [m, n], 2, dout)
+    assert "invalid axis" in e.value.message
+    with pytest.raises(g.GUDAError) as e:
+        g.ReduceMax(dx, [m, n, 1], 0, dout)
+    assert "invalid shape" in e.value.message
+    g.Free(dx); g.Free(dout)

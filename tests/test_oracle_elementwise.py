@@ -71,3 +71,23 @@ def test_device_exp_restatement_is_exhaustively_equivalent(tmp_path):
     out = subprocess.run([exe], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout
     assert "floor mismatches 0  scale mismatches 0" in out.stdout
+
+
+def test_reduce_axis_is_the_sequential_chain():
+    """reduce.go:105-178: Sum from float32(0) in index order; Max from the first element with `val > max`."""
+    m, n = 7, 5
+    x = O.uniform_f32(m * n, 9, -100, 100)
+    X = x.reshape(m, n)
+    for axis in (0, 1):
+        want = []
+        for o in range(n if axis == 0 else m):
+            col = X[:, o] if axis == 0 else X[o, :]
+            s = np.float32(0)
+            for v in col:
+                s = np.float32(s + v)
+            want.append(s)
+        assert np.array_equal(O.reduce_axis(x, m, n, axis), np.array(want, np.float32))
+        assert np.array_equal(O.reduce_axis(x, m, n, axis, True), X.max(axis=axis))
+    y = np.array([np.nan, 1.0, 2.0, -0.0, 0.0, np.nan], np.float32)          # rows: [nan 1 2], [-0 0 nan]
+    r = O.reduce_axis(y, 2, 3, 1, True)
+    assert np.isnan(r[0]) and r[1] == 0 and np.signbit(r[1])                  # leading NaN stays; of equal zeros the first wins; later NaN skipped

@@ -20,7 +20,6 @@
 // one partial per CTA, the last CTA (acq_rel ticket) folds the partials in index order and writes 16 bytes straight into mapped
 // pinned host memory.  Algorithmic bytes: 4 per element.
 #include "common.cuh"
-#include <cuda.h>
 #include <cmath>
 #include <mutex>
 
@@ -645,6 +644,11 @@ int guda_isamax(int n, const float* x, int incx, long long* host_result, guda_st
 // results carry the reference's bits; the parallelism is across output elements.
 namespace guda {
 
+__global__ void fill_value_kernel(float* p, size_t n, float v) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
 template <bool IS_MAX> __device__ __forceinline__ float axis_op(float acc, float v) {
   if (IS_MAX) return v > acc ? v : acc;
   return __fadd_rn(acc, v);
@@ -760,7 +764,8 @@ static int reduce_axis_impl(const float* x, int m, int n, int axis, float* out, 
         size_t want = 1;
         while (want < (size_t)m) want <<= 1;
         GUDA_CUDA(cudaMalloc(&ones, want * sizeof(float)));
-        if (cuMemsetD32Async((CUdeviceptr)ones, 0x3f800000u, want, s) != CUDA_SUCCESS) return set_error(GUDA_ERR_EXECUTION, "%s: memset failed", op);
+        fill_value_kernel<<<(unsigned)((want + 255) / 256), 256, 0, s>>>(ones, want, 1.0f);
+        if ((rc = check_launch(op))) return rc;
         GUDA_CUDA(cudaStreamSynchronize(s));
         ones_len = want;
       }

@@ -241,7 +241,10 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
   // mode is a property of guda_sgemm: both stay on the materialised route
   const bool small_path = g.out_c == N && N == K && (K == 4 || K == 8 || K == 16);
   const long long in_image = (long long)g.in_c * g.in_h * g.in_w;
-  if (route != 1 && !small_path && sgemm_mode() == GUDA_SGEMM_EXACT && in_image < 0x7fffffffLL && P < 0x7fffffffLL &&
+  // few output positions (N = B*P below 4096: at most 64 column tiles, deep K walks per CTA): the materialised route's
+  // 128-bit B loads beat the scalar gather (B1 64x56x56->64: 63 vs 82 us; B32 512x7x7->512: 0.41 vs 0.53 ms); same bits either way
+  const bool few_positions = route == 0 && N < 4096;
+  if (route != 1 && !few_positions && !small_path && sgemm_mode() == GUDA_SGEMM_EXACT && in_image < 0x7fffffffLL && P < 0x7fffffffLL &&
       g.kh * (long long)g.dil_h < 32768 && g.kw * (long long)g.dil_w < 65536) {
     ConvTemp tab;
     if ((rc = guda_malloc(&tab.p, (size_t)K * sizeof(int2)))) return rc;

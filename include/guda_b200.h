@@ -239,7 +239,8 @@ int guda_conv2d(const float* input, const float* kernel, const float* bias, floa
                 guda_stream_t stream);
 /* Two routes with the same FMA chain per output element (bit-identical results): 0 = implicit GEMM (default: the column matrix of
  * conv.go:200-222 is gathered inside the GEMM's tile loader, bias + NCHW placement fused in its epilogue), 1 = materialised
- * im2col -> guda_sgemm -> placement (also taken for the 4^3/8^3/16^3 Sgemm fast-path shapes and in the 3xTF32 mode);
+ * im2col -> guda_sgemm -> placement (also taken below 4096 output positions, for the 4^3/8^3/16^3 Sgemm fast-path shapes and in
+ * the 3xTF32 mode);
  * 2 / 3 / 4 = implicit GEMM with the 64x128 / 64x64 / 128x128 CTA tile forced (the default picks by estimated makespan);
  * -1 = back to the default / GUDA_CONV_ROUTE=im2col environment override.  For A/B measurement and the route-equality tests. */
 int guda_conv_set_route(int route);

@@ -317,7 +317,7 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     tf = conv_flops / (conv_ms["implicit"] * 1e-3) / 1e12
     out["conv2d_b32_64x56x56_3x3"] = {
         "value": tf, "unit": "TFLOP/s", "ms": conv_ms["implicit"], "ms_im2col_route": conv_ms["im2col"],
-        "includes": "blocking call (k-table launch + implicit-GEMM kernel + stream sync)",
+        "includes": "stream-ordered calls (one implicit-GEMM kernel each; the offset table is cached per geometry)",
         "roofline": {"bound": "fp32_simt", "achieved": tf, "peak": ffma_peak, "unit": "TFLOP/s", "frac": tf / ffma_peak,
                      "peak_source": "FFMA microbenchmark, this run"}}
     for p in (cx, cw, cb, co):

@@ -15,6 +15,9 @@
 // the FMA chain per output element is unchanged, so the two routes are bit-identical (tests/test_gpu_conv.py checks both).
 #include "gemm_simt.cuh"
 #include <cstdlib>
+#include <mutex>
+#include <utility>
+#include <vector>
 
 namespace guda {
 
@@ -199,6 +202,15 @@ __global__ void __launch_bounds__(256, MINB) conv_igemm_kernel(const float* __re
   }
 }
 
+struct KtabKey {
+  int in_c, in_h, in_w, kh, kw, dil_h, dil_w;
+  bool operator==(const KtabKey& o) const {
+    return in_c == o.in_c && in_h == o.in_h && in_w == o.in_w && kh == o.kh && kw == o.kw && dil_h == o.dil_h && dil_w == o.dil_w;
+  }
+};
+static std::mutex g_ktab_mu;
+static std::vector<std::pair<KtabKey, int2*>> g_ktabs;
+
 static int conv_route_env() {          // GUDA_CONV_ROUTE=im2col forces the materialised route (A/B and parity tests)
   static const int r = [] { const char* e = getenv("GUDA_CONV_ROUTE"); return (e && !strcmp(e, "im2col")) ? 1 : 0; }();
   return r;
@@ -246,10 +258,31 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
   const bool few_positions = route == 0 && N < 4096;
   if (route != 1 && !few_positions && !small_path && sgemm_mode() == GUDA_SGEMM_EXACT && in_image < 0x7fffffffLL && P < 0x7fffffffLL &&
       g.kh * (long long)g.dil_h < 32768 && g.kw * (long long)g.dil_w < 65536) {
+    // The k table depends only on (IC, H, W, KH, KW, dilation): it is built once per geometry and kept for the library's
+    // lifetime (a few KB each, at most 64 geometries), so a repeated call is ONE stream-ordered kernel launch with no
+    // allocation and no synchronisation.  Beyond 64 geometries the table is a pooled temporary and the call blocks.
     ConvTemp tab;
-    if ((rc = guda_malloc(&tab.p, (size_t)K * sizeof(int2)))) return rc;
-    conv_ktab_kernel<<<(unsigned)((K + 127) / 128), 128, 0, s>>>((int2*)tab.p, (int)K, g);
-    if ((rc = check_launch("conv_ktab"))) return rc;
+    const int2* kt = nullptr;
+    {
+      std::lock_guard<std::mutex> lk(g_ktab_mu);
+      const KtabKey key{g.in_c, g.in_h, g.in_w, g.kh, g.kw, g.dil_h, g.dil_w};
+      for (const auto& e : g_ktabs) if (e.first == key) { kt = e.second; break; }
+      if (!kt && g_ktabs.size() < 64) {
+        int2* p = nullptr;
+        GUDA_CUDA(cudaMalloc(&p, (size_t)K * sizeof(int2)));
+        conv_ktab_kernel<<<(unsigned)((K + 127) / 128), 128, 0, s>>>(p, (int)K, g);
+        if ((rc = check_launch("conv_ktab"))) { cudaFree(p); return rc; }
+        GUDA_CUDA(cudaStreamSynchronize(s));      // once per geometry: later calls may come from any stream
+        g_ktabs.emplace_back(key, p);
+        kt = p;
+      }
+    }
+    if (!kt) {
+      if ((rc = guda_malloc(&tab.p, (size_t)K * sizeof(int2)))) return rc;
+      conv_ktab_kernel<<<(unsigned)((K + 127) / 128), 128, 0, s>>>((int2*)tab.p, (int)K, g);
+      if ((rc = check_launch("conv_ktab"))) return rc;
+      kt = (const int2*)tab.p;
+    }
     // CTA tile 128x128 (8x8 micro-tile, 16 x 16 threads), 64x128 (8x4, 32 x 8 threads) or 64x64 (4x4): like Sgemm's choice
     // (gemm.cu launch_simt_one), the smallest estimated makespan ceil(tiles / SMs) * BM*BN / efficiency.  A 64x256 tile (4x16
     // micro-tile, 122 registers, 16 gathers per thread per k-tile) was measured at 15 TFLOP/s against 28 for 64x128 and is not built.
@@ -273,7 +306,6 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     dim3 grid((unsigned)((N + bn - 1) / bn), (unsigned)((g.out_c + bm - 1) / bm));
     if (grid.y > 65535) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: too many output channels for one launch");
     const bool fasta = (g.out_c % bm == 0) && (K % 16 == 0) && ((uintptr_t)kernel % 16 == 0);
-    const int2* kt = (const int2*)tab.p;
 #define GUDA_CONV_LAUNCH(BM_, BN_, MINB_, TXN_)                                                                                     \
     do {                                                                                                                        \
       if (fasta) conv_igemm_kernel<BM_, BN_, true, MINB_, TXN_><<<grid, 256, 0, s>>>(kernel, input, b, output, kt, g, (int)K, N, (int)P);  \
@@ -284,7 +316,7 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     else GUDA_CONV_LAUNCH(64, 64, 4, 16);
 #undef GUDA_CONV_LAUNCH
     if ((rc = check_launch("conv_igemm"))) return rc;
-    GUDA_CUDA(cudaStreamSynchronize(s));        // the k table returns to the pool when this function exits
+    if (tab.p) GUDA_CUDA(cudaStreamSynchronize(s));        // a pooled k table returns to the pool when this function exits
     return GUDA_OK;
   }
   ConvTemp col, tmp;

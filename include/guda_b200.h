@@ -228,7 +228,8 @@ int guda_fused_execute(float* x, const float* const* others, int n_others, long 
 
 /* ---- Conv2D: conv.go:9-31 ConvParams, :69 Conv2D = im2col -> Sgemm -> NCHW placement + bias.
  * input [B][IC][H][W], kernel [OC][IC][KH][KW], bias [OC] (used when use_bias != 0 and bias != NULL), output [B][OC][OH][OW].
- * Blocks until done (it owns a pooled workspace, like the reference's `defer Free(workspace)`). */
+ * The implicit-GEMM route is stream-ordered (one kernel launch once a geometry's offset table exists); the materialised route
+ * blocks until done (it owns a pooled workspace, like the reference's `defer Free(workspace)`). */
 typedef struct {
   int batch_size, in_channels, in_height, in_width;
   int out_channels, kernel_height, kernel_width;

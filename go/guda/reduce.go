@@ -157,3 +157,25 @@ func reduceAxis(x DevicePtr, shape []int, axis int, out DevicePtr, isMax bool) e
 	}
 	return status(C.guda_reduce_sum_axis((*C.float)(x.ptr), C.int(m), C.int(n), C.int(axis), (*C.float)(out.ptr), nil), "ReduceSum")
 }
+
+// TopK mirrors reduce.go:247-291: the k largest elements in descending order with their indices, in the order the reference's
+// selection sort produces (ties and NaNs included).  k is clamped to n; k <= 0 returns ErrInvalidParameter.
+func TopK(x DevicePtr, n, k int) (values []float32, indices []int, err error) {
+	if k > n {
+		k = n
+	}
+	if k <= 0 {
+		return nil, nil, ErrInvalidParameter
+	}
+	checkLen("TopK", n, x)
+	values = make([]float32, k)
+	idx := make([]C.longlong, k)
+	if err = status(C.guda_topk((*C.float)(x.ptr), C.longlong(n), C.int(k), (*C.float)(&values[0]), &idx[0], nil), "TopK"); err != nil {
+		return nil, nil, err
+	}
+	indices = make([]int, k)
+	for i := range idx {
+		indices[i] = int(idx[i])
+	}
+	return values, indices, nil
+}

@@ -616,6 +616,18 @@ def ReduceMax(x, shape, axis, out, stream=None):   # reduce.go:139
     _reduce_axis("guda_reduce_max_axis", "ReduceMax", x, shape, axis, out, stream)
 
 
+def TopK(x, n, k, stream=None):                    # reduce.go:247 -> (values, indices)
+    _ew_len("TopK", n, x)
+    kk = min(k, n)
+    if kk <= 0:
+        raise GUDAError(capi.ERR_INVALID_ARG, "FusedOp", "invalid parameter")      # ErrInvalidParameter
+    vals = np.empty(kk, np.float32)
+    idx = np.empty(kk, np.int64)
+    capi.check(_L().guda_topk(x.ptr, n, k, vals.ctypes.data_as(C.POINTER(C.c_float)), idx.ctypes.data_as(C.POINTER(C.c_int64)),
+                              _sh(stream)), "TopK")
+    return vals, idx
+
+
 def NewFusedKernel():                              # fused.go:45
     return FusedKernel()
 

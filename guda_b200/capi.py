@@ -111,6 +111,7 @@ SIGNATURES = {
     "guda_softmax": (i, [vp, C.c_longlong, vp]),
     "guda_layer_norm": (i, [vp, vp, vp, C.c_longlong, f, vp]),
     "guda_conv2d": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
+    "guda_topk": (i, [vp, C.c_longlong, i, fp, i64p, vp]),
     "guda_reduce_sum_axis": (i, [vp, i, i, i, vp, vp]),
     "guda_reduce_max_axis": (i, [vp, i, i, i, vp, vp]),
     "guda_add": (i, [vp, vp, vp, C.c_longlong, vp]),

@@ -795,3 +795,58 @@ int guda_reduce_max_axis(const float* x, int m, int n, int axis, float* out, gud
   return guda::reduce_axis_impl(x, m, n, axis, out, true, stream, "ReduceMax");
 }
 }
+
+// ---------------------------------------------------------------------------------------------------- TopK
+// reduce.go:247-291: k rounds of selection sort over (value, index) pairs -- round i scans positions i..n-1 of the CURRENT
+// arrangement for the first maximum under `pairs[j].val > pairs[maxIdx].val` and swaps it into position i.  A round's scan is
+// exactly the ArgMax of reduce_kernel (first index of the maximum among non-NaN elements, or the first position when it
+// holds a NaN) applied to the working copy from position i on, so the indices come out bit for bit -- including the order of
+// ties, which depends on the earlier swaps, and NaNs.  The permutation is tracked on the host for the k + k touched slots.
+namespace guda {
+__global__ void topk_swap_kernel(float* v, long long i, long long j) {
+  const float t = v[i];
+  v[i] = v[j];
+  v[j] = t;
+}
+struct TopkTemp {
+  void* p = nullptr;
+  ~TopkTemp() { if (p) guda_free(p); }
+};
+}  // namespace guda
+
+extern "C" int guda_topk(const float* x, long long n, int k, float* host_values, long long* host_indices, guda_stream_t stream) {
+  using namespace guda;
+  if (n < 0) return set_error(GUDA_ERR_INVALID_ARG, "TopK: negative length");
+  if (k > n) k = (int)n;                                                                   // reduce.go:248-250
+  if (k <= 0) return set_error(GUDA_ERR_INVALID_ARG, "invalid parameter");                  // ErrInvalidParameter, reduce.go:251-253
+  if (!host_values || !host_indices) return set_error(GUDA_ERR_INVALID_ARG, "TopK: null result pointer");
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x) return set_error(GUDA_ERR_INVALID_ARG, "TopK: null pointer");
+  cudaStream_t s = native(stream);
+  TopkTemp work;
+  if ((rc = guda_malloc(&work.p, (size_t)n * sizeof(float)))) return rc;
+  float* v = static_cast<float*>(work.p);
+  GUDA_CUDA(cudaMemcpyAsync(v, x, (size_t)n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  std::vector<std::pair<long long, long long>> moved;                                      // position -> original index, where it differs
+  auto index_at = [&](long long pos) {
+    for (auto it = moved.rbegin(); it != moved.rend(); ++it) if (it->first == pos) return it->second;
+    return pos;
+  };
+  for (int i = 0; i < k; i++) {
+    RedResult r;
+    if ((rc = launch_reduce<RED_ARGMAX>((size_t)(n - i), v + i, 1, &r, s, "TopK"))) return rc;  // blocks; r.idx is relative to v + i
+    const long long pos = i + r.idx;
+    const long long at_i = index_at(i), at_pos = index_at(pos);
+    if (pos != i) {
+      topk_swap_kernel<<<1, 1, 0, s>>>(v, i, pos);
+      if ((rc = check_launch("TopK"))) return rc;
+      moved.emplace_back(i, at_pos);
+      moved.emplace_back(pos, at_i);
+    }
+    host_indices[i] = at_pos;
+  }
+  GUDA_CUDA(cudaMemcpyAsync(host_values, v, (size_t)k * sizeof(float), cudaMemcpyDeviceToHost, s));
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  return GUDA_OK;
+}

@@ -267,6 +267,14 @@ inline void ReduceMax(const DevicePtr& x, int m, int n, int axis, const DevicePt
   check(guda_reduce_max_axis(f32(x), m, n, axis, f32(out), nullptr), "ReduceMax");
 }
 
+// reduce.go:247 TopK: values (descending) and indices in the reference's selection-sort order; k clamped to n
+inline void TopK(const DevicePtr& x, long long n, int k, std::vector<float>& values, std::vector<long long>& indices) {
+  ew_len("TopK", n, {&x});
+  const long long kk = k > n ? n : k;
+  values.assign(kk > 0 ? (size_t)kk : 0, 0.f); indices.assign(kk > 0 ? (size_t)kk : 0, 0);
+  check(guda_topk(f32(x), n, k, values.data(), indices.data(), nullptr), "TopK");
+}
+
 // conv.go:9-31 ConvParams, :69 Conv2D
 struct ConvParams {
   int BatchSize = 0, InChannels = 0, InHeight = 0, InWidth = 0, OutChannels = 0, KernelHeight = 0, KernelWidth = 0;

@@ -206,6 +206,12 @@ int guda_layer_norm(float* x, const float* gamma, const float* beta, long long n
 int guda_reduce_sum_axis(const float* x, int m, int n, int axis, float* out, guda_stream_t stream);
 int guda_reduce_max_axis(const float* x, int m, int n, int axis, float* out, guda_stream_t stream);
 
+/* reduce.go:247-291 TopK: the k largest values of x[0..n) in descending order with their indices, produced by the reference's
+ * k rounds of selection sort (ties and NaNs come out in its order: bit-exact indices).  k is clamped to n; k <= 0 is
+ * GUDA_ERR_INVALID_ARG "invalid parameter" (ErrInvalidParameter).  HOST results (min(k, n) entries), blocking;
+ * cost k streaming passes over a working copy. */
+int guda_topk(const float* x, long long n, int k, float* host_values, long long* host_indices, guda_stream_t stream);
+
 /* ---- Elementwise device ops: math.go:133-169 Add / Multiply (c = a op b), :230-272 ReLU / Sigmoid (in place; Sigmoid is
  * activations.go:9-27 SigmoidFloat32 operation by operation).  Stream-ordered, bit-identical to the reference. */
 int guda_add(const float* a, const float* b, float* c, long long n, guda_stream_t stream);

@@ -4,6 +4,7 @@
  * order, one write) with the ops LinearReLU (fused.go:252) and GELU (:261) are built from.  Every Go statement on a float32
  * variable rounds to float32; on the default GOAMD64=v1 build `val += alpha*other` is an unfused multiply then add. */
 #include <stddef.h>
+#include <stdlib.h>
 #include "guda_oracle.h"
 
 float orc_sigmoid_f32(float x) {                    /* activations.go:9-27 */
@@ -69,4 +70,22 @@ int orc_reduce_axis(const float* x, int m, int n, int axis, int is_max, float* o
     out[o] = acc;
   }
   return 0;
+}
+
+/* reduce.go:247-291 TopK: selection sort of (value, index) pairs, k rounds, swaps included.  values / indices hold min(k, n). */
+int orc_topk(const float* x, long long n, int k, float* values, long long* indices) {
+  if (k > n) k = (int)n;
+  if (k <= 0) return -1;
+  float* v = (float*)malloc((size_t)n * sizeof(float));
+  long long* id = (long long*)malloc((size_t)n * sizeof(long long));
+  for (long long i = 0; i < n; i++) { v[i] = x[i]; id[i] = i; }
+  for (int i = 0; i < k; i++) {
+    long long mx = i;
+    for (long long j = i + 1; j < n; j++) if (v[j] > v[mx]) mx = j;
+    float tv = v[i]; v[i] = v[mx]; v[mx] = tv;
+    long long ti = id[i]; id[i] = id[mx]; id[mx] = ti;
+  }
+  for (int i = 0; i < k; i++) { values[i] = v[i]; indices[i] = id[i]; }
+  free(v); free(id);
+  return k;
 }

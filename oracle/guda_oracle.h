@@ -148,6 +148,7 @@ void orc_ew_mul(const float* a, const float* b, float* c, size_t n);
 void orc_ew_relu(float* x, size_t n);
 void orc_ew_sigmoid(float* x, size_t n);
 int orc_reduce_axis(const float* x, int m, int n, int axis, int is_max, float* out);      /* reduce.go:105-178 */
+int orc_topk(const float* x, long long n, int k, float* values, long long* indices);            /* reduce.go:247-291 */
 void orc_fused_execute(float* x, const float* const* others, int n_others, size_t n, const orc_fused_op_t* ops, int n_ops);
 
 typedef struct { float abs_tol, rel_tol; int ulp_tol; int check_nan, check_inf; } orc_tol_t;

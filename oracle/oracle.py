@@ -74,6 +74,7 @@ def lib():
         L.orc_ew_relu.argtypes = [fp, sz]; L.orc_ew_relu.restype = None
         L.orc_ew_sigmoid.argtypes = [fp, sz]; L.orc_ew_sigmoid.restype = None
         L.orc_reduce_axis.argtypes = [fp, i, i, i, i, fp]
+        L.orc_topk.argtypes = [fp, C.c_longlong, i, fp, C.POINTER(C.c_longlong)]
         L.orc_fused_execute.argtypes = [fp, C.POINTER(fp), i, sz, C.POINTER(FusedOp), i]; L.orc_fused_execute.restype = None
         L.orc_to_bf16.argtypes = [f]; L.orc_to_bf16.restype = C.c_uint16
         L.orc_bf16_to_f32.argtypes = [C.c_uint16]; L.orc_bf16_to_f32.restype = f
@@ -242,6 +243,16 @@ def reduce_axis(x, m, n, axis, is_max=False):          # reduce.go:105 ReduceSum
     out = np.empty(n if axis == 0 else m, np.float32)
     _chk(lib().orc_reduce_axis(_p(x, C.c_float), m, n, axis, int(is_max), _p(out, C.c_float)))
     return out
+
+
+def topk(x, k):                         # reduce.go:247 TopK -> (values, indices)
+    x = _f32(x)
+    kk = min(k, x.size)
+    vals, idx = np.empty(max(kk, 1), np.float32), np.empty(max(kk, 1), np.int64)
+    got = lib().orc_topk(_p(x, C.c_float), x.size, k, _p(vals, C.c_float), _p(idx, C.c_longlong))
+    if got < 0:
+        raise ValueError("invalid parameter")
+    return vals[:got], idx[:got]
 
 
 def fused_execute(x, others, ops):

@@ -147,3 +147,34 @@ def test_reduce_axis_unaligned_and_errors(g, O):
         g.ReduceMax(dx, [m, n, 1], 0, dout)
     assert "invalid shape" in e.value.message
     g.Free(dx); g.Free(dout)
+
+
+@pytest.mark.parametrize("n,k", [(1, 1), (7, 4), (100, 100), (1000, 10), (65537, 5), ((1 << 20) + 3, 16), (5000, 64)])
+def test_topk_indices_bit_exact(g, O, n, k):
+    x = O.uniform_f32(n, 91 + n)
+    x = np.round(x * 8).astype(np.float32) / 8 if n >= 100 else x          # many exact ties: their order is the swap history's
+    if n > 6:
+        x[2] = np.nan; x[n // 2] = np.nan; x[5] = np.inf; x[n - 1] = np.inf
+    dx = g.to_device(x)
+    vals, idx = g.TopK(dx, n, k)
+    wv, wi = O.topk(x, k)
+    assert np.array_equal(idx, wi)
+    assert _same(vals, wv)
+    assert np.array_equal(dx.Float32()[:n], x, equal_nan=True)              # the input is not modified
+    g.Free(dx)
+
+
+def test_topk_leading_nan_and_errors(g, O):
+    x = np.array([np.nan, 5, 1, 5, np.nan], np.float32)
+    dx = g.to_device(x)
+    vals, idx = g.TopK(dx.Offset(0), 5, 9)                                   # k clamped to n
+    wv, wi = O.topk(x, 9)
+    assert np.array_equal(idx, wi) and _same(vals, wv) and len(idx) == 5
+    view = dx.Offset(4)                                                      # unaligned working copy start handled by the head path
+    vals, idx = g.TopK(view, 4, 2)
+    wv, wi = O.topk(x[1:], 2)
+    assert np.array_equal(idx, wi) and _same(vals, wv)
+    with pytest.raises(g.GUDAError) as e:
+        g.TopK(dx, 5, 0)
+    assert "invalid parameter" in e.value.message
+    g.Free(dx)

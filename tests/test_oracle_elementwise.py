@@ -91,3 +91,17 @@ def test_reduce_axis_is_the_sequential_chain():
     y = np.array([np.nan, 1.0, 2.0, -0.0, 0.0, np.nan], np.float32)          # rows: [nan 1 2], [-0 0 nan]
     r = O.reduce_axis(y, 2, 3, 1, True)
     assert np.isnan(r[0]) and r[1] == 0 and np.signbit(r[1])                  # leading NaN stays; of equal zeros the first wins; later NaN skipped
+
+
+def test_topk_selection_sort_semantics():
+    """reduce.go:247-291: ties come out in the order the swaps leave them; a NaN is picked only when its round starts on it."""
+    v, i = O.topk(np.array([3, 1, 3, np.nan, 2, 3, 0], np.float32), 4)
+    assert list(i) == [0, 2, 5, 3] and list(v[:3]) == [3, 3, 3] and np.isnan(v[3])
+    v, i = O.topk(np.array([np.nan, 5, 1], np.float32), 2)
+    assert list(i) == [0, 1] and np.isnan(v[0]) and v[1] == 5
+    x = O.uniform_f32(1000, 5)
+    v, i = O.topk(x, 10)
+    order = np.argsort(-x, kind="stable")[:10]
+    assert np.array_equal(i, order) and np.array_equal(v, x[order])
+    v, i = O.topk(x[:3], 7)                                  # k clamped to n
+    assert len(v) == 3

@@ -655,12 +655,19 @@ template <bool IS_MAX> __device__ __forceinline__ float axis_op(float acc, float
 }
 
 // axis 0 (out[j], chain over rows): one thread per column, consecutive threads read consecutive columns; 64 rows of loads in flight
+// Max only: `keep the left operand unless the right one is strictly greater` is associative, so the rows may be cut into
+// gridDim.y chunks whose results are combined in chunk order by a second launch of this kernel over the [chunks][n] partials.
+// Chunk 0 starts from x[0][j] like the reference (a leading NaN stays); later chunks start from -Inf, which a NaN never beats
+// and which loses to nothing it should not (ties keep the earlier element, so the first of two equal zeros still wins).
 template <bool IS_MAX>
-__global__ void __launch_bounds__(128) reduce_axis0_kernel(const float* __restrict__ x, int m, int n, float* __restrict__ out) {
+__global__ void __launch_bounds__(128) reduce_axis0_kernel(const float* __restrict__ x, int m_total, int n, float* __restrict__ out,
+                                                           int rows_per_chunk) {
   const long long j = (long long)blockIdx.x * 128 + threadIdx.x;
   if (j >= n) return;
-  const float* p = x + j;
-  float acc = IS_MAX ? p[0] : 0.0f;
+  const int r0 = blockIdx.y * rows_per_chunk;
+  const int m = min(rows_per_chunk, m_total - r0);
+  const float* p = x + (long long)r0 * n + j;
+  float acc = IS_MAX ? (blockIdx.y == 0 ? p[0] : -INFINITY) : 0.0f;
   int i = 0;                                            // Max: row 0 again is a no-op (x > x is false, also for NaN)
   for (; i + 64 <= m; i += 64) {                        // n threads in all: depth, not occupancy, has to cover the HBM latency
     float v[64];
@@ -677,7 +684,7 @@ __global__ void __launch_bounds__(128) reduce_axis0_kernel(const float* __restri
     for (int u = 0; u < 16; u++) acc = axis_op<IS_MAX>(acc, v[u]);
   }
   for (; i < m; i++) acc = axis_op<IS_MAX>(acc, __ldg(p + (long long)i * n));
-  out[j] = acc;
+  out[(long long)blockIdx.y * n + j] = acc;
 }
 
 // axis 1 (out[i], chain over columns): a CTA owns 32 rows; all 256 threads stream 32 x 128 tiles through a double-buffered
@@ -685,13 +692,18 @@ __global__ void __launch_bounds__(128) reduce_axis0_kernel(const float* __restri
 constexpr int AX1_ROWS = 32, AX1_COLS = 128, AX1_LD = AX1_COLS + 1;
 
 template <bool IS_MAX>
-__global__ void __launch_bounds__(256) reduce_axis1_kernel(const float* __restrict__ x, int m, int n, float* __restrict__ out, bool vec) {
+__global__ void __launch_bounds__(256) reduce_axis1_kernel(const float* __restrict__ x, int m, int n_total, float* __restrict__ out, bool vec,
+                                                           int cols_per_chunk) {
+  // Max only: gridDim.y column chunks (a multiple of 128 columns each), combined in chunk order by reduce_axis0_kernel<true>
+  // over the [chunks][m] partials -- the same left-biased strict maximum as in the axis-0 kernel
+  const int cbeg = blockIdx.y * cols_per_chunk;
+  const int n = min(n_total, cbeg + cols_per_chunk);     // this CTA walks columns [cbeg, n)
   __shared__ float tile[2][AX1_ROWS][AX1_LD];
   const int tid = threadIdx.x;
   const long long row0 = (long long)blockIdx.x * AX1_ROWS;
   const int lr = tid >> 3, lc = (tid & 7) * 4;          // this thread's row of the tile and its first column (then + 32, 64, 96)
   const long long grow = row0 + lr;
-  const float* src = x + (grow < m ? grow : (long long)m - 1) * n;
+  const float* src = x + (grow < m ? grow : (long long)m - 1) * n_total;
   float4 reg[4];
   auto load = [&](int c0) {
 #pragma unroll
@@ -711,17 +723,17 @@ __global__ void __launch_bounds__(256) reduce_axis1_kernel(const float* __restri
       d[0] = reg[k].x; d[1] = reg[k].y; d[2] = reg[k].z; d[3] = reg[k].w;
     }
   };
-  const int ntiles = (n + AX1_COLS - 1) / AX1_COLS;
+  const int ntiles = (n - cbeg + AX1_COLS - 1) / AX1_COLS;
   const long long myrow = row0 + tid;                    // warp 0 only
   float acc = 0.0f;
-  if (IS_MAX && tid < AX1_ROWS && myrow < m) acc = __ldg(x + myrow * n);
-  load(0);
+  if (IS_MAX && tid < AX1_ROWS && myrow < m) acc = blockIdx.y == 0 ? __ldg(x + myrow * n_total) : -INFINITY;
+  load(cbeg);
   store(0);
   __syncthreads();
   for (int t = 0; t < ntiles; t++) {
-    if (t + 1 < ntiles) load((t + 1) * AX1_COLS);
+    if (t + 1 < ntiles) load(cbeg + (t + 1) * AX1_COLS);
     if (tid < AX1_ROWS) {
-      const int cmax = min(AX1_COLS, n - t * AX1_COLS);
+      const int cmax = min(AX1_COLS, n - cbeg - t * AX1_COLS);
       const float* r = tile[t & 1][tid];
       if (cmax == AX1_COLS) {
 #pragma unroll 16
@@ -733,7 +745,7 @@ __global__ void __launch_bounds__(256) reduce_axis1_kernel(const float* __restri
     if (t + 1 < ntiles) store((t + 1) & 1);
     __syncthreads();
   }
-  if (tid < AX1_ROWS && myrow < m) out[myrow] = acc;
+  if (tid < AX1_ROWS && myrow < m) out[(long long)blockIdx.y * m + myrow] = acc;
 }
 
 static int reduce_axis_impl(const float* x, int m, int n, int axis, float* out, bool is_max, guda_stream_t stream, const char* op) {
@@ -774,13 +786,65 @@ static int reduce_axis_impl(const float* x, int m, int n, int axis, float* out, 
   }
   if (axis == 0) {
     const unsigned grid = (unsigned)(((long long)n + 127) / 128);
-    if (is_max) reduce_axis0_kernel<true><<<grid, 128, 0, s>>>(x, m, n, out);
-    else        reduce_axis0_kernel<false><<<grid, 128, 0, s>>>(x, m, n, out);
+    long long chunks = 1;
+    if (is_max) {                                       // enough threads to cover HBM latency: ~1024 per SM, at least 64 rows each
+      chunks = ((long long)sm_count() * 1024 + n - 1) / n;
+      if (chunks > m / 64) chunks = m / 64;
+      if (chunks > 65535) chunks = 65535;
+      if (chunks < 1) chunks = 1;
+    }
+    if (chunks > 1) {
+      static std::mutex mu;
+      static float* part = nullptr;
+      static size_t part_len = 0;
+      std::lock_guard<std::mutex> lk(mu);               // held across the launches: a later grow synchronises the device before it frees
+      const size_t want = (size_t)chunks * (size_t)n;
+      if (part_len < want) {
+        if (part) { GUDA_CUDA(cudaDeviceSynchronize()); GUDA_CUDA(cudaFree(part)); part = nullptr; part_len = 0; }
+        GUDA_CUDA(cudaMalloc(&part, want * sizeof(float)));
+        part_len = want;
+      }
+      const int rpc = (int)((m + chunks - 1) / chunks);
+      const unsigned ny = (unsigned)((m + rpc - 1) / rpc);
+      reduce_axis0_kernel<true><<<dim3(grid, ny), 128, 0, s>>>(x, m, n, part, rpc);
+      if ((rc = check_launch(op))) return rc;
+      reduce_axis0_kernel<true><<<grid, 128, 0, s>>>(part, (int)ny, n, out, (int)ny);
+      return check_launch(op);
+    }
+    if (is_max) reduce_axis0_kernel<true><<<grid, 128, 0, s>>>(x, m, n, out, m);
+    else        reduce_axis0_kernel<false><<<grid, 128, 0, s>>>(x, m, n, out, m);
   } else {
     const unsigned grid = (unsigned)(((long long)m + AX1_ROWS - 1) / AX1_ROWS);
     const bool vec = ((uintptr_t)x % 16 == 0) && (n % 4 == 0);
-    if (is_max) reduce_axis1_kernel<true><<<grid, 256, 0, s>>>(x, m, n, out, vec);
-    else        reduce_axis1_kernel<false><<<grid, 256, 0, s>>>(x, m, n, out, vec);
+    long long chunks = 1;
+    if (is_max && grid < 2u * (unsigned)sm_count()) {   // few row blocks: cut the columns (>= 4 tiles per chunk) to fill the machine
+      chunks = (4ll * sm_count() + grid - 1) / grid;
+      if (chunks > n / (4 * AX1_COLS)) chunks = n / (4 * AX1_COLS);
+      if (chunks > 65535) chunks = 65535;
+      if (chunks < 1) chunks = 1;
+    }
+    if (chunks > 1) {
+      static std::mutex mu;
+      static float* part = nullptr;
+      static size_t part_len = 0;
+      std::lock_guard<std::mutex> lk(mu);
+      const size_t want = (size_t)chunks * (size_t)m;
+      if (part_len < want) {
+        if (part) { GUDA_CUDA(cudaDeviceSynchronize()); GUDA_CUDA(cudaFree(part)); part = nullptr; part_len = 0; }
+        GUDA_CUDA(cudaMalloc(&part, want * sizeof(float)));
+        part_len = want;
+      }
+      int cpc = (int)((n + chunks - 1) / chunks);
+      cpc = (cpc + AX1_COLS - 1) / AX1_COLS * AX1_COLS;
+      const unsigned ny = (unsigned)((n + cpc - 1) / cpc);
+      reduce_axis1_kernel<true><<<dim3(grid, ny), 256, 0, s>>>(x, m, n, part, vec, cpc);
+      if ((rc = check_launch(op))) return rc;
+      reduce_axis0_kernel<true><<<(unsigned)(((long long)m + 127) / 128), 128, 0, s>>>(part, (int)ny, m, out, (int)ny);
+      return check_launch(op);
+    }
+    const int all = (n + AX1_COLS - 1) / AX1_COLS * AX1_COLS;
+    if (is_max) reduce_axis1_kernel<true><<<grid, 256, 0, s>>>(x, m, n, out, vec, all);
+    else        reduce_axis1_kernel<false><<<grid, 256, 0, s>>>(x, m, n, out, vec, all);
   }
   return check_launch(op);
 }

@@ -43,7 +43,8 @@ func (p *ConvParams) OutputWidth() int { // conv.go:60-63
 }
 
 // Conv2D mirrors conv.go:69-81: NCHW input, [OC][IC][KH][KW] kernel, optional bias (a zero DevicePtr means none).
-// im2col -> exact-order SGEMM -> NCHW placement + bias on the GPU; bit-identical to the reference for BatchSize == 1.
+// An implicit GEMM on the GPU (im2col gathered in the tile loader, bias + NCHW placement in the epilogue) with the reference's
+// FMA chain per output element; bit-identical to the reference for BatchSize == 1.
 func Conv2D(input, kernel, bias, output DevicePtr, params *ConvParams) error {
 	if err := params.Validate(); err != nil {
 		return err
@@ -55,4 +56,19 @@ func Conv2D(input, kernel, bias, output DevicePtr, params *ConvParams) error {
 		dilation_h: C.int(params.DilationH), dilation_w: C.int(params.DilationW), use_bias: cbool(params.UseBias),
 	}
 	return status(C.guda_conv2d((*C.float)(input.ptr), (*C.float)(kernel.ptr), (*C.float)(bias.ptr), (*C.float)(output.ptr), &cp, nil), "Conv2D")
+}
+
+// Conv2DDirect mirrors conv.go:231-300: the direct loops (unfused sum over the in-bounds taps in (ic, kh, kw) order, then + bias),
+// bit-identical to the reference.  It is the cross-check API; Conv2D is the fast route.
+func Conv2DDirect(input, kernel, bias, output DevicePtr, params *ConvParams) error {
+	if err := params.Validate(); err != nil {
+		return err
+	}
+	cp := C.guda_conv_params_t{
+		batch_size: C.int(params.BatchSize), in_channels: C.int(params.InChannels), in_height: C.int(params.InHeight), in_width: C.int(params.InWidth),
+		out_channels: C.int(params.OutChannels), kernel_height: C.int(params.KernelHeight), kernel_width: C.int(params.KernelWidth),
+		stride_h: C.int(params.StrideH), stride_w: C.int(params.StrideW), pad_h: C.int(params.PadH), pad_w: C.int(params.PadW),
+		dilation_h: C.int(params.DilationH), dilation_w: C.int(params.DilationW), use_bias: cbool(params.UseBias),
+	}
+	return status(C.guda_conv2d_direct((*C.float)(input.ptr), (*C.float)(kernel.ptr), (*C.float)(bias.ptr), (*C.float)(output.ptr), &cp, nil), "Conv2DDirect")
 }

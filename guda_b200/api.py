@@ -694,6 +694,12 @@ def Conv2D(input, kernel, bias, output, params, stream=None):          # conv.go
     capi.check(_L().guda_conv2d(input.ptr, kernel.ptr, bptr, output.ptr, C.byref(cp), _sh(stream)), "Conv2D")
 
 
+def Conv2DDirect(input, kernel, bias, output, params, stream=None):    # conv.go:231
+    cp = params._c()
+    bptr = bias.ptr if (bias is not None and bias.ptr) else None
+    capi.check(_L().guda_conv2d_direct(input.ptr, kernel.ptr, bptr, output.ptr, C.byref(cp), _sh(stream)), "Conv2DDirect")
+
+
 def SetConvRoute(route):
     """0 implicit GEMM (default), 1 materialised im2col, 2/3/4 implicit with the 64x128/64x64/128x128 tile forced,
     -1 default / environment (guda_conv_set_route)."""

@@ -120,6 +120,7 @@ SIGNATURES = {
     "guda_sigmoid": (i, [vp, C.c_longlong, vp]),
     "guda_fused_execute": (i, [vp, C.POINTER(vp), i, C.c_longlong, C.POINTER(FusedOp), i, vp]),
     "guda_conv_set_route": (i, [i]),
+    "guda_conv2d_direct": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),
     "guda_f32_to_bf16": (i, [vp, vp, sz, vp]),
     "guda_bf16_to_f32": (i, [vp, vp, sz, vp]),
     "guda_f32_to_f16": (i, [vp, vp, sz, vp]),

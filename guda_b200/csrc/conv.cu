@@ -202,6 +202,34 @@ __global__ void __launch_bounds__(256, MINB) conv_igemm_kernel(const float* __re
   }
 }
 
+// conv.go:231-300 Conv2DDirect: per output element sum = 0; for (ic, kh, kw) ascending, in-bounds taps only:
+// sum = fl(sum + fl(in * w)) -- no FMA, no zero test on the weights -- then + bias.  One thread per output element walks the
+// reference's loops (consecutive threads are consecutive ow, so the input reads coalesce and the weight reads broadcast).
+// This entry point exists for parity with the reference's cross-check API; the fast route is Conv2D above.
+__global__ void __launch_bounds__(256) conv_direct_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                                         const float* __restrict__ bias, float* __restrict__ out, ConvGeom g) {
+  const long long P = (long long)g.out_h * g.out_w, total = P * g.out_c * g.batch;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const long long p = e % P;
+    const int oc = (int)((e / P) % g.out_c), b = (int)(e / (P * g.out_c));
+    const int oh = (int)(p / g.out_w), ow = (int)(p - (long long)oh * g.out_w);
+    const float* img = in + (long long)b * g.in_c * g.in_h * g.in_w;
+    const float* wk = w + (long long)oc * g.in_c * g.kh * g.kw;
+    float sum = 0.0f;
+    for (int ic = 0; ic < g.in_c; ic++)
+      for (int kh = 0; kh < g.kh; kh++) {
+        const int ih = oh * g.stride_h - g.pad_h + kh * g.dil_h;
+        if (ih < 0 || ih >= g.in_h) continue;
+        for (int kw = 0; kw < g.kw; kw++) {
+          const int iw = ow * g.stride_w - g.pad_w + kw * g.dil_w;
+          if (iw < 0 || iw >= g.in_w) continue;
+          sum = __fadd_rn(sum, __fmul_rn(__ldg(img + ((long long)ic * g.in_h + ih) * g.in_w + iw), __ldg(wk + (ic * g.kh + kh) * g.kw + kw)));
+        }
+      }
+    out[e] = bias ? __fadd_rn(sum, bias[oc]) : sum;
+  }
+}
+
 struct KtabKey {
   int in_c, in_h, in_w, kh, kw, dil_h, dil_w;
   bool operator==(const KtabKey& o) const {
@@ -347,4 +375,31 @@ extern "C" int guda_conv_set_route(int route) {
   if (route < -1 || route > 4) return set_error(GUDA_ERR_INVALID_ARG, "Conv2D: route must be -1 .. 4");
   g_conv_route = route;
   return GUDA_OK;
+}
+
+/* conv.go:231-300 Conv2DDirect (same validation and output geometry as Conv2D; stream-ordered) */
+extern "C" int guda_conv2d_direct(const float* input, const float* kernel, const float* bias, float* output, const guda_conv_params_t* cp,
+                                  guda_stream_t stream) {
+  if (!cp) return set_error(GUDA_ERR_INVALID_ARG, "Conv2DDirect: null parameters");
+  if (cp->batch_size <= 0 || cp->in_channels <= 0 || cp->in_height <= 0 || cp->in_width <= 0)
+    return set_error(GUDA_ERR_INVALID_ARG, "invalid input dimensions: batch, channels, height and width must be positive");
+  if (cp->out_channels <= 0 || cp->kernel_height <= 0 || cp->kernel_width <= 0)
+    return set_error(GUDA_ERR_INVALID_ARG, "invalid kernel dimensions: output channels and kernel size must be positive");
+  if (cp->stride_h <= 0 || cp->stride_w <= 0) return set_error(GUDA_ERR_INVALID_ARG, "invalid stride: stride must be positive");
+  if (cp->dilation_h <= 0 || cp->dilation_w <= 0) return set_error(GUDA_ERR_INVALID_ARG, "invalid dilation: dilation must be positive");
+  if (cp->pad_h < 0 || cp->pad_w < 0) return set_error(GUDA_ERR_INVALID_ARG, "invalid padding: padding cannot be negative");
+  ConvGeom g{cp->batch_size, cp->in_channels, cp->in_height, cp->in_width, cp->out_channels, cp->kernel_height, cp->kernel_width,
+             cp->stride_h, cp->stride_w, cp->pad_h, cp->pad_w, cp->dilation_h, cp->dilation_w, 0, 0};
+  g.out_h = (g.in_h + 2 * g.pad_h - ((g.kh - 1) * g.dil_h + 1)) / g.stride_h + 1;
+  g.out_w = (g.in_w + 2 * g.pad_w - ((g.kw - 1) * g.dil_w + 1)) / g.stride_w + 1;
+  if (g.out_h <= 0 || g.out_w <= 0) return set_error(GUDA_ERR_INVALID_ARG, "Conv2DDirect: kernel larger than the padded input");
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!input || !kernel || !output) return set_error(GUDA_ERR_INVALID_ARG, "Conv2DDirect: null pointer");
+  if ((long long)g.in_c * g.kh * g.kw > 0x7fffffffLL) return set_error(GUDA_ERR_INVALID_ARG, "Conv2DDirect: kernel too large");
+  const long long total = (long long)g.batch * g.out_c * g.out_h * g.out_w;
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)sm_count() * 32) blocks = (long long)sm_count() * 32;
+  conv_direct_kernel<<<(unsigned)blocks, 256, 0, native(stream)>>>(input, kernel, (cp->use_bias && bias) ? bias : nullptr, output, g);
+  return check_launch("conv_direct");
 }

@@ -288,5 +288,11 @@ inline void Conv2D(const DevicePtr& input, const DevicePtr& kernel, const Device
                         p.StrideH, p.StrideW, p.PadH, p.PadW, p.DilationH, p.DilationW, p.UseBias ? 1 : 0};
   check(guda_conv2d(f32(input), f32(kernel), f32(bias), f32(output), &cp, nullptr), "Conv2D");
 }
+// conv.go:231 Conv2DDirect (the reference's direct loops, bit-identical; the cross-check API)
+inline void Conv2DDirect(const DevicePtr& input, const DevicePtr& kernel, const DevicePtr& bias, const DevicePtr& output, const ConvParams& p) {
+  guda_conv_params_t cp{p.BatchSize, p.InChannels, p.InHeight, p.InWidth, p.OutChannels, p.KernelHeight, p.KernelWidth,
+                        p.StrideH, p.StrideW, p.PadH, p.PadW, p.DilationH, p.DilationW, p.UseBias ? 1 : 0};
+  check(guda_conv2d_direct(f32(input), f32(kernel), f32(bias), f32(output), &cp, nullptr), "Conv2DDirect");
+}
 
 }  // namespace guda

@@ -244,6 +244,10 @@ typedef struct {
 } guda_conv_params_t;
 int guda_conv2d(const float* input, const float* kernel, const float* bias, float* output, const guda_conv_params_t* params,
                 guda_stream_t stream);
+/* conv.go:231-300 Conv2DDirect: the reference's direct loops (unfused multiply-add over the in-bounds taps in (ic, kh, kw) order, no
+ * zero test, then + bias), bit-identical; stream-ordered.  The parity cross-check API -- Conv2D is the fast route. */
+int guda_conv2d_direct(const float* input, const float* kernel, const float* bias, float* output, const guda_conv_params_t* params,
+                       guda_stream_t stream);
 /* Two routes with the same FMA chain per output element (bit-identical results): 0 = implicit GEMM (default: the column matrix of
  * conv.go:200-222 is gathered inside the GEMM's tile loader, bias + NCHW placement fused in its epilogue), 1 = materialised
  * im2col -> guda_sgemm -> placement (also taken below 4096 output positions, for the 4^3/8^3/16^3 Sgemm fast-path shapes and in

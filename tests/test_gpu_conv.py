@@ -106,3 +106,27 @@ def test_conv2d_validation_errors(g):
             g.Conv2D(z, z, None, z, g.ConvParams(**bad))
         assert e.value.type == 2 and "invalid" in e.value.message           # InvalidArgument, conv.go:34-51
     g.Free(z)
+
+
+@pytest.mark.parametrize("p", SHAPES)
+def test_conv2d_direct_bit_exact_vs_oracle(g, O, p):
+    """conv.go:231-300 Conv2DDirect: unfused sum over the in-bounds taps, no zero test -- bit for bit, non-finite weights included."""
+    x = O.uniform_f32(p["BatchSize"] * p["InChannels"] * p["InHeight"] * p["InWidth"], 21)
+    w = O.uniform_f32(p["OutChannels"] * p["InChannels"] * p["KernelHeight"] * p["KernelWidth"], 22)
+    w[::7] = 0.0
+    if w.size > 3:
+        w[3] = np.inf                                # an Inf weight on a padded tap must not turn into 0 * Inf = NaN
+    b = O.uniform_f32(p["OutChannels"], 23) if p["UseBias"] else None
+    cp = g.ConvParams(**p)
+    n_out = p["BatchSize"] * p["OutChannels"] * cp.OutputHeight() * cp.OutputWidth()
+    dx, dw, dout = g.to_device(x), g.to_device(w), g.Malloc(n_out * 4)
+    g.Memset(dout, 0xFF, n_out * 4)
+    db = g.to_device(b) if b is not None else g.DevicePtr()
+    g.Conv2DDirect(dx, dw, db, dout, cp)
+    got = dout.Float32()[:n_out]
+    with np.errstate(all="ignore"):
+        want = O.conv2d(x, w, b, p, direct=True)
+    nan = np.isnan(want)
+    assert np.array_equal(nan, np.isnan(got)) and np.array_equal(got[~nan].view(np.uint32), want[~nan].view(np.uint32))
+    for d in (dx, dw, dout) + ((db,) if b is not None else ()):
+        g.Free(d)

@@ -263,6 +263,20 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     for x in rb:
         g.Free(x)
 
+    # ---- ReduceSum / ReduceMax along an axis (reduce.go:105-178): 16384 x 16384 (1 GiB, beyond L2)
+    ra, ro = g.Malloc(16384 * 16384 * 4), g.Malloc(16384 * 4)
+    g.FillUniform(ra, 16384, 16384, 16384, 650)
+    for key, fn, axis in (("reduce_sum_axis0_16384", g.ReduceSum, 0), ("reduce_sum_axis1_16384", g.ReduceSum, 1),
+                          ("reduce_max_axis0_16384", g.ReduceMax, 0), ("reduce_max_axis1_16384", g.ReduceMax, 1)):
+        for _ in range(2):
+            fn(ra, [16384, 16384], axis, ro)
+        ms = dev.time_ms(lambda: fn(ra, [16384, 16384], axis, ro), 10)
+        gbs = 4.0 * 16384 * 16384 / (ms * 1e-3) / 1e9
+        out[key] = {"value": gbs, "unit": "GB/s", "ms": ms,
+                    "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                                 "peak_source": peaks["source"], "algorithmic_bytes": 4.0 * 16384 * 16384, "traffic": ncu_traffic(key)}}
+    g.Free(ra); g.Free(ro)
+
     # ---- elementwise device ops (math.go:133-169, fused.go:252): n = 2^26 (256 MiB per vector, beyond L2)
     ne = 1 << 26
     ea, eb, ec = g.Malloc(ne * 4), g.Malloc(ne * 4), g.Malloc(ne * 4)

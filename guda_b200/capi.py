@@ -78,6 +78,7 @@ SIGNATURES = {
     "guda_ddot": (i, [i, vp, i, vp, i, dp, vp]),
     "guda_ddot_device": (i, [i, vp, i, vp, i, vp, vp]),
     "guda_set_sgemm_mode": (i, [i]),
+    "guda_set_sgemm_pipe": (i, [i, i]),
     "guda_get_sgemm_mode": (i, [ip]),
     "guda_sgemm": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_sgemm_host": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
@@ -136,6 +137,7 @@ SIGNATURES = {
     "guda_comm_get_gather_mode": (i, [vp, ip]),
     "guda_sdot_sharded": (i, [vp, i, vp, vp, fp, vp]),
     "guda_microbench_peak": (i, [i, i, dp]),
+    "guda_microbench_lds": (i, [i, ip, i, dp]),
 }
 
 _lib = None

@@ -52,6 +52,21 @@ struct Scratch {
 };
 int get_scratch(Scratch** out);
 
+// stream-aware pool entry points for internal temporaries (runtime.cu): the block is handed out for use on `use_stream`
+// (a block last used on another stream makes use_stream wait for that work on the device -- no host stall) and returned
+// with pool_free(ptr, stream) while its last kernels may still be queued on that stream.
+int pool_alloc(void** dptr, size_t size, cudaStream_t use_stream);
+int pool_free(void* dptr, cudaStream_t used_on);
+struct PoolTemp {
+  void* p = nullptr;
+  cudaStream_t s = nullptr;
+  PoolTemp() = default;
+  PoolTemp(const PoolTemp&) = delete;
+  PoolTemp& operator=(const PoolTemp&) = delete;
+  ~PoolTemp() { if (p) pool_free(p, s); }
+  int alloc(size_t bytes, cudaStream_t stream) { s = stream; return pool_alloc(&p, bytes, stream); }
+};
+
 // two library-lifetime non-blocking streams for copies pipelined under compute (host_gemm.cu)
 int aux_copy_streams(cudaStream_t* in, cudaStream_t* out);
 // K boundaries of the host-operand pipeline (short first chunk, then 8192-deep)

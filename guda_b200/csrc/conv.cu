@@ -245,10 +245,6 @@ static int conv_route_env() {          // GUDA_CONV_ROUTE=im2col forces the mate
 }
 static int g_conv_route = -1;          // -1: environment, 0: implicit, 1: im2col, 2/3/4: implicit with the 64x128 / 64x64 / 128x128 tile
 
-struct ConvTemp {
-  void* p = nullptr;
-  ~ConvTemp() { if (p) guda_free(p); }
-};
 
 }  // namespace guda
 
@@ -289,7 +285,7 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     // The k table depends only on (IC, H, W, KH, KW, dilation): it is built once per geometry and kept for the library's
     // lifetime (a few KB each, at most 64 geometries), so a repeated call is ONE stream-ordered kernel launch with no
     // allocation and no synchronisation.  Beyond 64 geometries the table is a pooled temporary and the call blocks.
-    ConvTemp tab;
+    PoolTemp tab;
     const int2* kt = nullptr;
     {
       std::lock_guard<std::mutex> lk(g_ktab_mu);
@@ -306,7 +302,7 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
       }
     }
     if (!kt) {
-      if ((rc = guda_malloc(&tab.p, (size_t)K * sizeof(int2)))) return rc;
+      if ((rc = tab.alloc((size_t)K * sizeof(int2), s))) return rc;
       conv_ktab_kernel<<<(unsigned)((K + 127) / 128), 128, 0, s>>>((int2*)tab.p, (int)K, g);
       if ((rc = check_launch("conv_ktab"))) return rc;
       kt = (const int2*)tab.p;
@@ -344,13 +340,12 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     else GUDA_CONV_LAUNCH(64, 64, 4, 16);
 #undef GUDA_CONV_LAUNCH
     if ((rc = check_launch("conv_igemm"))) return rc;
-    if (tab.p) GUDA_CUDA(cudaStreamSynchronize(s));        // a pooled k table returns to the pool when this function exits
     return GUDA_OK;
   }
-  ConvTemp col, tmp;
-  if ((rc = guda_malloc(&col.p, (size_t)(K * N) * sizeof(float)))) return rc;             // conv.go:88-93 workspace
+  PoolTemp col, tmp;
+  if ((rc = col.alloc((size_t)(K * N) * sizeof(float), s))) return rc;             // conv.go:88-93 workspace
   const bool direct_out = (g.batch == 1);                                                // [OC][P] already is NCHW
-  if (!direct_out && (rc = guda_malloc(&tmp.p, (size_t)g.out_c * N * sizeof(float)))) return rc;
+  if (!direct_out && (rc = tmp.alloc((size_t)g.out_c * N * sizeof(float), s))) return rc;
   long long blocks = (K * N + 255) / 256;
   if (blocks > (long long)sm_count() * 32) blocks = (long long)sm_count() * 32;
   im2col_kernel<<<(unsigned)blocks, 256, 0, s>>>(input, (float*)col.p, g);
@@ -365,7 +360,7 @@ extern "C" int guda_conv2d(const float* input, const float* kernel, const float*
     conv_place_kernel<<<(unsigned)blocks, 256, 0, s>>>(direct_out ? nullptr : (const float*)tmp.p, b, output, g.batch, g.out_c, P);
     if ((rc = check_launch("conv_place"))) return rc;
   }
-  GUDA_CUDA(cudaStreamSynchronize(s));          // the workspace returns to the pool when this function exits (conv.go:93 defer Free)
+  // the workspace returns to the pool here (conv.go:93 defer Free); the pool orders its next owner after this stream's work
   return GUDA_OK;
 }
 

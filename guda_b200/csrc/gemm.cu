@@ -10,6 +10,9 @@ int sgemm_mode();
 // FP64 tensor pipe (dgemm_dmma.cu); GUDA_OK / error if it took the call, -1 if the operands are not eligible
 int dgemm_dmma_try(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
                    double* c, int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s);
+// TMA-fed exact-order pipeline (sgemm_pipe.cu); GUDA_OK / error if it took the call, -1 if the call is not eligible
+int sgemm_pipe_try(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta, float* c,
+                   int ldc, const float* bias, int epi, const ScatterArgs* scatter, cudaStream_t s);
 // tensor-core paths (gemm_tc.cu); return GUDA_OK if they handled the call, -1 if the shape is not eligible
 int sgemm_3xtf32_try(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
                      float beta, float* c, int ldc, cudaStream_t s);
@@ -150,18 +153,15 @@ static int check_gemm_args(int ta, int tb, int m, int n, int k, int lda, int ldb
   return GUDA_OK;
 }
 
-struct ScatterArgs { int n; float* dst[GUDA_MAX_SCATTER]; long long ld, off; };
-
 static int sgemm_impl(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
-                      float beta, float* c, int ldc, const float* bias, int epi, guda_stream_t stream,
-                      const ScatterArgs* scatter = nullptr) {
+                      float beta, float* c, int ldc, const float* bias, int epi, cudaStream_t s,
+                      const ScatterArgs* scatter = nullptr, bool force_exact = false) {
   int rc = check_gemm_args(ta, tb, m, n, k, lda, ldb, ldc);
   if (rc) return rc;
   if (m == 0 || n == 0) return GUDA_OK;                                   // compute/sgemm.go:74
   rc = bind_device();
   if (rc) return rc;
   if ((!c && !(scatter && beta == 0.0f)) || ((!a || !b) && k > 0)) return set_error(GUDA_ERR_INVALID_ARG, "GEMM: null pointer");
-  cudaStream_t s = native(stream);
   if (epi == EPI_NONE && !scatter) {
     // compute/sgemm.go:80-96 small-matrix kernels (NN contiguous only; the bTrans branch :98-111 multiplies by
     // B as stored, a reference defect that is deliberately NOT reproduced -- see DESIGN.md)
@@ -172,14 +172,18 @@ static int sgemm_impl(int ta, int tb, int m, int n, int k, float alpha, const fl
       return check_launch("sgemm_small");
     }
     if ((alpha == 0.0f || k == 0) && beta == 1.0f) return GUDA_OK;        // compute/sgemm.go:139
-    if (sgemm_mode() == GUDA_SGEMM_3XTF32) {
+    if (!force_exact && sgemm_mode() == GUDA_SGEMM_3XTF32) {
       rc = sgemm_3xtf32_try(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, s);
       if (rc >= 0) return rc;
     }
   }
+  if (scatter && (ta || tb)) return set_error(GUDA_ERR_NOT_IMPLEMENTED, "sgemm_scatter: only the NN form is implemented");
+  if (!tb && !(alpha == 0.0f && beta == 1.0f)) {
+    rc = sgemm_pipe_try(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, bias, epi, scatter, s);
+    if (rc >= 0) return rc;
+  }
   GemmParams<float> p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, bias, m, n};
   if (scatter) {
-    if (ta || tb) return set_error(GUDA_ERR_NOT_IMPLEMENTED, "sgemm_scatter: only the NN form is implemented");
     ScatterParams<float, true> sp;
     sp.n = scatter->n;
     for (int i = 0; i < GUDA_MAX_SCATTER; i++) sp.dst[i] = i < scatter->n ? scatter->dst[i] : nullptr;
@@ -253,13 +257,27 @@ int sgemm_unfused_noskip(int m, int n, int k, float alpha, const float* a, int l
 }
 // exact-order SGEMM on an explicit cudaStream_t (used by the fp16 path: float16.go:231)
 int sgemm_exact_on(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
-                   float* c, int ldc, cudaStream_t s);
+                   float* c, int ldc, cudaStream_t s) {
+  return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, s, nullptr, true);
+}
 
 // x[i] = act(x[i] + bias[i % bias_len])   (fused_gelu.go:12-41, fused.go:220-260)
 template <int EPI>
-__global__ void add_bias_act_kernel(float* __restrict__ x, const float* __restrict__ bias, int n, int bias_len) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+__global__ void add_bias_act_kernel(float* __restrict__ x, const float* __restrict__ bias, long long n, int bias_len) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     x[i] = apply_epilogue<float, EPI>(x[i], bias[i % bias_len]);
+}
+int add_bias_act_on(float* x, const float* bias, long long n, int bias_len, cudaStream_t s, bool gelu) {
+  if (n < 0 || bias_len <= 0) return set_error(GUDA_ERR_INVALID_ARG, "AddBias: bad length");
+  if (n == 0) return GUDA_OK;
+  int rc = bind_device();
+  if (rc) return rc;
+  if (!x || !bias) return set_error(GUDA_ERR_INVALID_ARG, "AddBias: null pointer");
+  long long grid = (n + 255) / 256;
+  if (grid > (long long)sm_count() * 16) grid = (long long)sm_count() * 16;
+  if (gelu) add_bias_act_kernel<EPI_BIAS_GELU><<<(unsigned)grid, 256, 0, s>>>(x, bias, n, bias_len);
+  else add_bias_act_kernel<EPI_BIAS_RELU><<<(unsigned)grid, 256, 0, s>>>(x, bias, n, bias_len);
+  return check_launch("add_bias_act");
 }
 
 }  // namespace guda
@@ -269,7 +287,7 @@ extern "C" {
 
 int guda_sgemm(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
                float* c, int ldc, guda_stream_t stream) {
-  return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, stream);
+  return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, native(stream));
 }
 int guda_dgemm(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
                double* c, int ldc, guda_stream_t stream) {
@@ -281,7 +299,7 @@ int guda_dgemm(int ta, int tb, int m, int n, int k, double alpha, const double* 
 int guda_sgemm_scatter(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
                        float* c, int ldc, float* const* host_dests, int ndest, int ld_dest, int row0, int col0, guda_stream_t stream) {
   if (ndest < 0 || ndest > GUDA_MAX_SCATTER || (ndest > 0 && !host_dests)) return set_error(GUDA_ERR_INVALID_ARG, "sgemm_scatter: bad destination list");
-  if (ndest == 0) return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, stream);
+  if (ndest == 0) return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, native(stream));
   if (row0 < 0 || col0 < 0 || ld_dest < col0 + n) GUDA_PANIC("blas: bad leading dimension of C");
   ScatterArgs sc{};
   sc.n = ndest;
@@ -290,7 +308,7 @@ int guda_sgemm_scatter(int ta, int tb, int m, int n, int k, float alpha, const f
     sc.dst[i] = host_dests[i];
   }
   sc.ld = ld_dest; sc.off = (long long)row0 * ld_dest + col0;
-  return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, stream, &sc);
+  return sgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nullptr, EPI_NONE, native(stream), &sc);
 }
 
 static int fused_checks(int ta, int tb, float beta, const float* bias) {
@@ -303,26 +321,17 @@ int guda_sgemm_bias_relu(int ta, int tb, int m, int n, int k, float alpha, const
                          float beta, float* c, int ldc, const float* bias, guda_stream_t stream) {
   int rc = fused_checks(ta, tb, beta, bias);
   if (rc) return rc;
-  return sgemm_impl(0, 0, m, n, k, alpha, a, lda, b, ldb, 0.0f, c, ldc, bias, EPI_BIAS_RELU, stream);
+  return sgemm_impl(0, 0, m, n, k, alpha, a, lda, b, ldb, 0.0f, c, ldc, bias, EPI_BIAS_RELU, native(stream));
 }
 int guda_sgemm_bias_gelu(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
                          float beta, float* c, int ldc, const float* bias, guda_stream_t stream) {
   int rc = fused_checks(ta, tb, beta, bias);
   if (rc) return rc;
-  return sgemm_impl(0, 0, m, n, k, alpha, a, lda, b, ldb, 0.0f, c, ldc, bias, EPI_BIAS_GELU, stream);
+  return sgemm_impl(0, 0, m, n, k, alpha, a, lda, b, ldb, 0.0f, c, ldc, bias, EPI_BIAS_GELU, native(stream));
 }
 
 static int add_bias_act(float* x, const float* bias, int n, int bias_len, guda_stream_t stream, bool gelu) {
-  if (n < 0 || bias_len <= 0) return set_error(GUDA_ERR_INVALID_ARG, "AddBias: bad length");
-  if (n == 0) return GUDA_OK;
-  int rc = bind_device();
-  if (rc) return rc;
-  if (!x || !bias) return set_error(GUDA_ERR_INVALID_ARG, "AddBias: null pointer");
-  int grid = (n + 255) / 256;
-  if (grid > sm_count() * 16) grid = sm_count() * 16;
-  if (gelu) add_bias_act_kernel<EPI_BIAS_GELU><<<grid, 256, 0, native(stream)>>>(x, bias, n, bias_len);
-  else add_bias_act_kernel<EPI_BIAS_RELU><<<grid, 256, 0, native(stream)>>>(x, bias, n, bias_len);
-  return check_launch("add_bias_act");
+  return add_bias_act_on(x, bias, n, bias_len, native(stream), gelu);
 }
 int guda_add_bias_gelu(float* x, const float* bias, int n, int bias_len, guda_stream_t stream) {
   return add_bias_act(x, bias, n, bias_len, stream, true);

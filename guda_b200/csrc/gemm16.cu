@@ -10,6 +10,9 @@
 
 namespace guda {
 
+int add_bias_act_on(float* x, const float* bias, long long n, int bias_len, cudaStream_t s, bool gelu);
+int sgemm_exact_on(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
+                   float* c, int ldc, cudaStream_t s);
 int sgemm_unfused_noskip(int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
                          float* c, int ldc, cudaStream_t s);
 // gemm_tc.cu: returns GUDA_OK / error if handled, -1 if the shape is not eligible for the tensor-core kernel
@@ -108,11 +111,6 @@ __global__ void fill_uniform_kernel(T* __restrict__ dst, long long rows, long lo
   }
 }
 
-struct TempBuf {
-  void* p = nullptr;
-  ~TempBuf() { if (p) guda_free(p); }
-  int alloc(size_t bytes) { return guda_malloc(&p, bytes); }
-};
 
 static int gemm16_impl(int is_bf16, int ta, int tb, int m, int n, int k, float alpha, const uint16_t* a, int lda,
                        const uint16_t* b, int ldb, float beta, uint16_t* c, int ldc, const float* bias, int epi,
@@ -138,30 +136,29 @@ static int gemm16_impl(int is_bf16, int ta, int tb, int m, int n, int k, float a
   }
   // exact route: fp32 temporaries from the pool (stream-ordered use; freed blocks stay cached in the pool)
   const int ar = ta ? k : m, ac = ta ? m : k, br = tb ? n : k, bc = tb ? k : n;
-  TempBuf af, bf, cf;
-  if ((rc = af.alloc((size_t)ar * ac * 4 + 16))) return rc;
-  if ((rc = bf.alloc((size_t)br * bc * 4 + 16))) return rc;
-  if ((rc = cf.alloc((size_t)m * n * 4 + 16))) return rc;
+  PoolTemp af, bf, cf;
+  if ((rc = af.alloc((size_t)ar * ac * 4 + 16, s))) return rc;
+  if ((rc = bf.alloc((size_t)br * bc * 4 + 16, s))) return rc;
+  if ((rc = cf.alloc((size_t)m * n * 4 + 16, s))) return rc;
   float *A = (float*)af.p, *B = (float*)bf.p, *C = (float*)cf.p;
   if (is_bf16) {
     if ((rc = convert2d<CVT_BF16_F32>(a, lda, A, ac, ar, ac, s))) return rc;
     if ((rc = convert2d<CVT_BF16_F32>(b, ldb, B, bc, br, bc, s))) return rc;
     if (beta != 0 && (rc = convert2d<CVT_BF16_F32>(c, ldc, C, n, m, n, s))) return rc;
     if ((rc = sgemm_unfused_noskip(m, n, k, alpha, A, ac, B, bc, beta, C, n, s))) return rc;
-    if (epi == 1 && (rc = guda_add_bias_relu(C, bias, m * n, n, stream))) return rc;
-    if (epi == 2 && (rc = guda_add_bias_gelu(C, bias, m * n, n, stream))) return rc;
+    if (epi == 1 && (rc = add_bias_act_on(C, bias, (long long)m * n, n, s, false))) return rc;
+    if (epi == 2 && (rc = add_bias_act_on(C, bias, (long long)m * n, n, s, true))) return rc;
     rc = convert2d<CVT_F32_BF16>(C, n, c, ldc, m, n, s);
   } else {
     if ((rc = convert2d<CVT_F16_F32>(a, lda, A, ac, ar, ac, s))) return rc;
     if ((rc = convert2d<CVT_F16_F32>(b, ldb, B, bc, br, bc, s))) return rc;
     if (beta != 0) { if ((rc = convert2d<CVT_F16_F32>(c, ldc, C, n, m, n, s))) return rc; }
     else GUDA_CUDA(cudaMemsetAsync(C, 0, (size_t)m * n * 4, s));
-    if ((rc = guda_sgemm(ta, tb, m, n, k, alpha, A, ac, B, bc, beta, C, n, stream))) return rc;   // float16.go:231
+    if ((rc = sgemm_exact_on(ta, tb, m, n, k, alpha, A, ac, B, bc, beta, C, n, s))) return rc;      // float16.go:231 (exact order whatever the SGEMM math mode)
     rc = convert2d<CVT_F32_F16>(C, n, c, ldc, m, n, s);
   }
   if (rc) return rc;
-  // the temporaries go back to the pool when this returns; make sure the stream is done with them first
-  GUDA_CUDA(cudaStreamSynchronize(s));
+  // the temporaries go back to the pool here; the pool orders their next owner after this stream's queued work
   return GUDA_OK;
 }
 

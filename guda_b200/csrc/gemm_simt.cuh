@@ -128,6 +128,8 @@ template <typename T> struct ScatterParams<T, true> {
   long long ld, off;
 };
 
+struct ScatterArgs { int n; float* dst[GUDA_MAX_SCATTER]; long long ld, off; };
+
 template <typename T, int BM, int BN, int BK>
 struct GemmSmem {
   static constexpr int VN = GemmVec<T>::N;

@@ -511,6 +511,13 @@ static int make_map(CUtensorMap* map, CUtensorMapDataType dt, int eb, const void
   return GUDA_OK;
 }
 
+// plain (unswizzled) fp32 map for the SIMT pipeline of sgemm_pipe.cu: box rows are dense runs of box_cols floats
+int tensor_map_2d_f32(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols, uint32_t box_rows) {
+  int rc = get_encode();
+  if (rc) return rc;
+  return make_map(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, rows, cols, ld, box_cols, box_rows, CU_TENSOR_MAP_SWIZZLE_NONE);
+}
+
 template <int EB, int NSPLIT, int BN, int OUT, int EPI>
 static int launch_tc(CUtensorMapDataType dt, int m, int n, int k, float alpha, const void* a0, const void* a1, long long lda,
                      const void* b0, const void* b1, long long ldb, float beta, void* c, long long ldc, const float* bias, cudaStream_t s) {
@@ -610,10 +617,6 @@ __global__ void split_tf32_kernel(const float* __restrict__ src, long long lds, 
   }
 }
 
-struct TcTemp {
-  void* p = nullptr;
-  ~TcTemp() { if (p) guda_free(p); }
-};
 
 int sgemm_3xtf32_try(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
                      float* c, int ldc, cudaStream_t s) {
@@ -621,21 +624,19 @@ int sgemm_3xtf32_try(int ta, int tb, int m, int n, int k, float alpha, const flo
   if (m < 128 || n < 128 || k < 32) return -1;
   auto pad4 = [](long long x) { return (x + 3) & ~3ll; };
   const long long lda2 = pad4(k), ldb2 = pad4(n);
-  TcTemp ah, al, bh, bl;
+  PoolTemp ah, al, bh, bl;
   int rc;
-  if ((rc = guda_malloc(&ah.p, (size_t)m * lda2 * 4))) return rc;
-  if ((rc = guda_malloc(&al.p, (size_t)m * lda2 * 4))) return rc;
-  if ((rc = guda_malloc(&bh.p, (size_t)k * ldb2 * 4))) return rc;
-  if ((rc = guda_malloc(&bl.p, (size_t)k * ldb2 * 4))) return rc;
+  if ((rc = ah.alloc((size_t)m * lda2 * 4, s))) return rc;
+  if ((rc = al.alloc((size_t)m * lda2 * 4, s))) return rc;
+  if ((rc = bh.alloc((size_t)k * ldb2 * 4, s))) return rc;
+  if ((rc = bl.alloc((size_t)k * ldb2 * 4, s))) return rc;
   const int blocks = sm_count() * 16;
   split_tf32_kernel<<<blocks, 256, 0, s>>>(a, lda, (float*)ah.p, (float*)al.p, lda2, m, k);
   split_tf32_kernel<<<blocks, 256, 0, s>>>(b, ldb, (float*)bh.p, (float*)bl.p, ldb2, k, n);
   if ((rc = check_launch("split_tf32"))) return rc;
   rc = launch_tc<4, 2, 128, OUT_F32, EPI_NONE>(CU_TENSOR_MAP_DATA_TYPE_FLOAT32, m, n, k, alpha, ah.p, al.p, lda2, bh.p, bl.p, ldb2, beta, c,
                                                ldc, nullptr, s);
-  if (rc) return rc;
-  GUDA_CUDA(cudaStreamSynchronize(s));      // the planes return to the pool when this function exits
-  return GUDA_OK;
+  return rc;                                 // the planes return to the pool here, ordered after this stream's work
 }
 
 }  // namespace guda

@@ -50,7 +50,10 @@ int aux_copy_streams(cudaStream_t* in, cudaStream_t* out) {
 struct HgBuffers {
   void *a = nullptr, *b = nullptr, *c = nullptr;
   std::vector<cudaEvent_t> ev;
+  std::vector<cudaStream_t> used;          // streams that may still hold copies / kernels on the staging buffers
+  bool done = false;                       // set once the caller's stream has been synchronised
   ~HgBuffers() {
+    if (!done) for (cudaStream_t q : used) cudaStreamSynchronize(q);     // error return: drain before the buffers and events go
     for (cudaEvent_t e : ev) cudaEventDestroy(e);
     if (a) guda_free(a);
     if (b) guda_free(b);
@@ -84,6 +87,7 @@ extern "C" int guda_sgemm_host(int ta, int tb, int m, int n, int k, float alpha,
   HgStreams* st;
   if ((rc = hg_streams(&st))) return rc;
   HgBuffers buf;
+  buf.used = {st->in, st->out, s};
   // compute/sgemm.go:80-96 takes its 4^3 / 8^3 / 16^3 kernels (a different summation order) only for CONTIGUOUS operands; the staging
   // copies are dense, so when the caller's were not, a padded device ldc keeps guda_sgemm on the general path the reference takes
   const bool small_strided = !ta && !tb && m == n && n == k && (m == 4 || m == 8 || m == 16) && !(lda == k && ldb == n && ldc == n);
@@ -155,5 +159,6 @@ extern "C" int guda_sgemm_host(int ta, int tb, int m, int n, int k, float alpha,
   GUDA_CUDA(cudaEventRecord(e_done, st->out));
   GUDA_CUDA(cudaStreamWaitEvent(s, e_done, 0));               // the caller's stream completes only when C is on the host
   GUDA_CUDA(cudaStreamSynchronize(s));                        // blocking, like the reference's GEMM; staging returns to the pool
+  buf.done = true;
   return GUDA_OK;
 }

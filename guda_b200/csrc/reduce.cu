@@ -872,10 +872,6 @@ __global__ void topk_swap_kernel(float* v, long long i, long long j) {
   v[i] = v[j];
   v[j] = t;
 }
-struct TopkTemp {
-  void* p = nullptr;
-  ~TopkTemp() { if (p) guda_free(p); }
-};
 }  // namespace guda
 
 extern "C" int guda_topk(const float* x, long long n, int k, float* host_values, long long* host_indices, guda_stream_t stream) {
@@ -888,8 +884,8 @@ extern "C" int guda_topk(const float* x, long long n, int k, float* host_values,
   if (rc) return rc;
   if (!x) return set_error(GUDA_ERR_INVALID_ARG, "TopK: null pointer");
   cudaStream_t s = native(stream);
-  TopkTemp work;
-  if ((rc = guda_malloc(&work.p, (size_t)n * sizeof(float)))) return rc;
+  PoolTemp work;
+  if ((rc = work.alloc((size_t)n * sizeof(float), s))) return rc;
   float* v = static_cast<float*>(work.p);
   GUDA_CUDA(cudaMemcpyAsync(v, x, (size_t)n * sizeof(float), cudaMemcpyDeviceToDevice, s));
   std::vector<std::pair<long long, long long>> moved;                                      // position -> original index, where it differs

@@ -33,7 +33,11 @@ int map_cuda_error(cudaError_t e) {
 }
 
 // ---------------------------------------------------------------- global state
-struct Block { size_t size; bool used; };
+// A freed block may still be read or written by work queued on the stream(s) it was last used on.  Each free records an
+// event per such stream; a later owner either runs on that same stream (stream order protects it), makes its own stream
+// wait for the event (internal temporaries: no host stall) or waits on the host (public Malloc: the caller may use any stream).
+struct Pending { cudaStream_t stream; cudaEvent_t ev; };
+struct Block { size_t size; bool used; std::vector<Pending> pending; };
 struct State {
   std::mutex mu;
   bool inited = false;
@@ -44,6 +48,8 @@ struct State {
   // memory pool (memory.go:26-38)
   std::map<void*, Block> allocated;
   std::vector<void*> free_list;      // insertion order, first-fit scan like the reference
+  std::vector<cudaStream_t> live_streams;   // default stream + every guda_stream_create'd stream
+  std::vector<cudaEvent_t> event_cache;
   int64_t total_alloc = 0, peak_alloc = 0;
   int sgemm_mode = GUDA_SGEMM_EXACT;
 };
@@ -64,6 +70,7 @@ static int init_locked(State& s, int device) {
   s.device = device;
   s.sms = p.multiProcessorCount;
   GUDA_CUDA(cudaStreamCreateWithFlags(&s.default_stream.s, cudaStreamNonBlocking));
+  s.live_streams.push_back(s.default_stream.s);
   GUDA_CUDA(cudaMalloc(&s.scratch.dev_partials, 64 << 10));
   GUDA_CUDA(cudaMalloc((void**)&s.scratch.dev_counter, 256));
   GUDA_CUDA(cudaMemset(s.scratch.dev_counter, 0, 256));
@@ -175,7 +182,21 @@ int guda_mem_get_info(size_t* free_bytes, size_t* total_bytes) {
 // memory.go:150-204 Allocate.  Accounting uses the reference's 64-byte rounding so that
 // GetStats() returns the same integers for the same call sequence; the device blocks
 // themselves come from cudaMalloc (256-byte aligned).
-int guda_malloc(void** dptr, size_t size) {
+}  // extern "C"
+
+namespace guda {
+
+static cudaEvent_t take_event(State& s) {
+  if (!s.event_cache.empty()) { cudaEvent_t e = s.event_cache.back(); s.event_cache.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return e;
+}
+
+// use_stream: the one stream the new owner will run on, or ANY_STREAM (public Malloc: unknown -> wait on the host)
+static const cudaStream_t ANY_STREAM = reinterpret_cast<cudaStream_t>(~(uintptr_t)0);
+
+static int pool_alloc_impl(void** dptr, size_t size, cudaStream_t use_stream) {
   if (!dptr) return set_error(GUDA_ERR_INVALID_ARG, "null pointer");
   *dptr = nullptr;
   int rc = bind_device();
@@ -183,42 +204,60 @@ int guda_malloc(void** dptr, size_t size) {
   State& s = st();
   const size_t alignment = 64;
   size_t aligned = (size + alignment - 1) & ~(alignment - 1);
-  std::lock_guard<std::mutex> lk(s.mu);
-  for (size_t i = 0; i < s.free_list.size(); i++) {
-    Block& b = s.allocated[s.free_list[i]];
-    if (b.size >= aligned) {
-      void* p = s.free_list[i];
-      s.free_list.erase(s.free_list.begin() + i);
-      b.used = true;
-      s.total_alloc += (int64_t)b.size;
+  std::vector<Pending> waits;
+  void* p = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(s.mu);
+    for (size_t i = 0; i < s.free_list.size(); i++) {
+      Block& b = s.allocated[s.free_list[i]];
+      if (b.size >= aligned) {
+        p = s.free_list[i];
+        s.free_list.erase(s.free_list.begin() + i);
+        b.used = true;
+        waits.swap(b.pending);
+        s.total_alloc += (int64_t)b.size;
+        if (s.total_alloc > s.peak_alloc) s.peak_alloc = s.total_alloc;
+        break;
+      }
+    }
+    if (!p) {
+      cudaError_t e = cudaMalloc(&p, aligned ? aligned : alignment);
+      if (e == cudaErrorMemoryAllocation && !s.free_list.empty()) {
+        // out of device memory with cached blocks: release them (cudaFree waits for their queued work) and retry once
+        cudaGetLastError();
+        for (void* f : s.free_list) {
+          for (Pending& w : s.allocated[f].pending) s.event_cache.push_back(w.ev);
+          cudaFree(f);
+          s.allocated.erase(f);
+        }
+        s.free_list.clear();
+        e = cudaMalloc(&p, aligned ? aligned : alignment);
+      }
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        return set_error(e == cudaErrorMemoryAllocation ? GUDA_ERR_MEMORY : map_cuda_error(e), "out of memory (%zu bytes): %s",
+                         aligned, cudaGetErrorString(e));     // errors.go:113 ErrOutOfMemory
+      }
+      s.allocated[p] = Block{aligned, true, {}};
+      s.total_alloc += (int64_t)aligned;
       if (s.total_alloc > s.peak_alloc) s.peak_alloc = s.total_alloc;
-      *dptr = p;
-      return GUDA_OK;
     }
   }
-  void* p = nullptr;
-  cudaError_t e = cudaMalloc(&p, aligned ? aligned : alignment);
-  if (e == cudaErrorMemoryAllocation && !s.free_list.empty()) {
-    // out of device memory with cached blocks: release them and retry once
-    cudaGetLastError();
-    for (void* f : s.free_list) { cudaFree(f); s.allocated.erase(f); }
-    s.free_list.clear();
-    e = cudaMalloc(&p, aligned ? aligned : alignment);
+  // outside the lock: order the new owner after the previous owner's queued work
+  for (Pending& w : waits) {
+    if (use_stream == ANY_STREAM) cudaEventSynchronize(w.ev);
+    else if (w.stream != use_stream) cudaStreamWaitEvent(use_stream, w.ev, 0);
   }
-  if (e != cudaSuccess) {
-    cudaGetLastError();
-    return set_error(e == cudaErrorMemoryAllocation ? GUDA_ERR_MEMORY : map_cuda_error(e), "out of memory (%zu bytes): %s",
-                     aligned, cudaGetErrorString(e));     // errors.go:113 ErrOutOfMemory
+  if (!waits.empty()) {
+    std::lock_guard<std::mutex> lk(s.mu);
+    for (Pending& w : waits) s.event_cache.push_back(w.ev);
   }
-  s.allocated[p] = Block{aligned, true};
-  s.total_alloc += (int64_t)aligned;
-  if (s.total_alloc > s.peak_alloc) s.peak_alloc = s.total_alloc;
   *dptr = p;
   return GUDA_OK;
 }
 
-// memory.go:207-227 Free
-int guda_free(void* dptr) {
+// only_stream: the block was used on this stream alone (internal temporaries); ANY_STREAM: record on every live stream
+static int pool_free_impl(void* dptr, cudaStream_t only_stream) {
   int rc = bind_device();
   if (rc) return rc;
   State& s = st();
@@ -227,10 +266,32 @@ int guda_free(void* dptr) {
   if (it == s.allocated.end()) return set_error(GUDA_ERR_MEMORY, "pointer not found in allocation pool");
   if (!it->second.used) return set_error(GUDA_ERR_MEMORY, "double free detected");    // errors.go:116 ErrDoubleFree
   it->second.used = false;
+  it->second.pending.clear();
+  auto record = [&](cudaStream_t q) {
+    if (cudaStreamQuery(q) == cudaSuccess) return;          // idle stream: nothing can still touch the block
+    cudaGetLastError();
+    cudaEvent_t e = take_event(s);
+    if (!e || cudaEventRecord(e, q) != cudaSuccess) { cudaGetLastError(); cudaStreamSynchronize(q); if (e) s.event_cache.push_back(e); return; }
+    it->second.pending.push_back(Pending{q, e});
+  };
+  if (only_stream == ANY_STREAM) { for (cudaStream_t q : s.live_streams) record(q); }
+  else record(only_stream);
   s.free_list.push_back(dptr);
   s.total_alloc -= (int64_t)it->second.size;
   return GUDA_OK;
 }
+
+int pool_alloc(void** dptr, size_t size, cudaStream_t use_stream) { return pool_alloc_impl(dptr, size, use_stream); }
+int pool_free(void* dptr, cudaStream_t used_on) { return pool_free_impl(dptr, used_on); }
+
+}  // namespace guda
+
+extern "C" {
+
+int guda_malloc(void** dptr, size_t size) { return pool_alloc_impl(dptr, size, ANY_STREAM); }
+
+// memory.go:207-227 Free
+int guda_free(void* dptr) { return pool_free_impl(dptr, ANY_STREAM); }
 
 int guda_pool_stats(int64_t* allocated, int64_t* peak) {
   State& s = st();
@@ -246,7 +307,11 @@ int guda_pool_trim(void) {
   State& s = st();
   std::lock_guard<std::mutex> lk(s.mu);
   GUDA_CUDA(cudaDeviceSynchronize());
-  for (void* f : s.free_list) { cudaFree(f); s.allocated.erase(f); }
+  for (void* f : s.free_list) {
+    for (Pending& w : s.allocated[f].pending) s.event_cache.push_back(w.ev);
+    cudaFree(f);
+    s.allocated.erase(f);
+  }
   s.free_list.clear();
   return GUDA_OK;
 }
@@ -297,6 +362,10 @@ int guda_stream_create(guda_stream_t* stream) {
   Stream* s = new Stream{nullptr};
   cudaError_t e = cudaStreamCreateWithFlags(&s->s, cudaStreamNonBlocking);
   if (e != cudaSuccess) { delete s; return set_error(map_cuda_error(e), "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+  {
+    std::lock_guard<std::mutex> lk(st().mu);
+    st().live_streams.push_back(s->s);
+  }
   *stream = reinterpret_cast<guda_stream_t>(s);
   return GUDA_OK;
 }
@@ -306,6 +375,11 @@ int guda_stream_destroy(guda_stream_t stream) {
   if (rc) return rc;
   Stream* s = reinterpret_cast<Stream*>(stream);
   GUDA_CUDA(cudaStreamSynchronize(s->s));
+  {
+    std::lock_guard<std::mutex> lk(st().mu);
+    auto& v = st().live_streams;
+    for (size_t i = 0; i < v.size(); i++) if (v[i] == s->s) { v.erase(v.begin() + i); break; }
+  }
   GUDA_CUDA(cudaStreamDestroy(s->s));
   delete s;
   return GUDA_OK;

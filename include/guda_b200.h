@@ -111,6 +111,9 @@ int guda_ddot_device(int n, const double* x, int incx, const double* y, int incy
  *   GUDA_SGEMM_3XTF32 tcgen05 tensor cores, 3xTF32 split with fp32 TMEM accumulation (stated tolerance) */
 enum { GUDA_SGEMM_EXACT = 0, GUDA_SGEMM_3XTF32 = 1 };
 int guda_set_sgemm_mode(int mode);
+/* exact-route kernel choice (A/B and test knob; results are bit-identical either way): cfg -1 automatic, 0 register-staged
+ * kernel only, 1.. a forced configuration of the TMA-fed pipeline (sgemm_pipe.cu); lag < 0 keeps the current refill distance */
+int guda_set_sgemm_pipe(int cfg, int lag);
 int guda_get_sgemm_mode(int* mode);
 int guda_sgemm(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* a, int lda,
                const float* b, int ldb, float beta, float* c, int ldc, guda_stream_t stream);
@@ -272,6 +275,9 @@ int guda_fill_uniform_f64(double* dst, size_t rows, size_t cols, size_t ld, uint
  * 2 = 128-bit streaming copy GB/s (read+write bytes), 3 = FP64 tensor pipe (DMMA m8n8k4) TFLOP/s,
  * 4 = packed fp32 FMA (fma.rn.f32x2 / FFMA2) TFLOP/s ---- */
 int guda_microbench_peak(int kind, int reps, double* value);
+/* SM cycles per warp-level shared-memory load instruction for a lane -> chunk-index pattern (width 4 / 8 / 16 bytes):
+ * the wavefront cost model behind the lane layouts of the SIMT GEMM kernels. */
+int guda_microbench_lds(int width, const int* host_lane_idx, int iters, double* cycles_per_instr);
 
 /* ---- multi-GPU (new, additive: GetDeviceCount()==1 stays pinned for the single-device API, guda_test.go:332) ----
  * One process per GPU.  The communicator wraps NCCL (loaded at run time); id bytes come from

@@ -45,3 +45,17 @@ func (c *Comm) DOTSharded(x, y DevicePtr, nLocal int) (float32, error) {
 	err := status(C.guda_sdot_sharded(c.h, C.int(nLocal), (*C.float)(x.ptr), (*C.float)(y.ptr), &r, nil), "DOTSharded")
 	return float32(r), err
 }
+
+// DgemmSharded: the fp64 twin of GEMMSharded (compute/dgemm.go:25 partitioned 2-D with full K per rank; the FP64 tensor-pipe
+// kernel's epilogue stores each finished tile into every rank's cFull).
+func (c *Comm) DgemmSharded(pr, pc, m, n, k int, alpha float64, aPanel DevicePtr, lda int, bPanel DevicePtr, ldb int,
+	cBlock DevicePtr, ldcBlock int, cFull DevicePtr, ldcFull int) error {
+	return status(C.guda_dgemm_sharded(c.h, C.int(pr), C.int(pc), C.int(m), C.int(n), C.int(k), C.double(alpha),
+		(*C.double)(aPanel.ptr), C.int(lda), (*C.double)(bPanel.ptr), C.int(ldb), (*C.double)(cBlock.ptr), C.int(ldcBlock),
+		(*C.double)(cFull.ptr), C.int(ldcFull), nil), "DgemmSharded")
+}
+
+// AXPYSharded: y += alpha * x on this rank's contiguous chunk of a sharded vector (math.go:39); elementwise, no collective.
+func (c *Comm) AXPYSharded(alpha float32, x, y DevicePtr, nLocal int) error {
+	return status(C.guda_saxpy_sharded(c.h, C.int(nLocal), C.float(alpha), (*C.float)(x.ptr), (*C.float)(y.ptr), nil), "AXPYSharded")
+}

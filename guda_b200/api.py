@@ -723,3 +723,52 @@ def FillUniform(ptr, rows, cols, ld, seed, row0=0, col0=0, full_cols=None, lo=-1
     full_cols = cols if full_cols is None else full_cols
     fn = _L().guda_fill_uniform_f32 if dtype == np.float32 else _L().guda_fill_uniform_f64
     capi.check(fn(ptr.ptr, rows, cols, ld, seed, row0, col0, full_cols, lo, hi, _sh(stream)), "FillUniform")
+
+
+# ---- kernel-launch surface (guda.go:66-89,184-196,258-276,310-339; execution.go:9-86) ----
+class Dim3:
+    """guda.go:66-68."""
+
+    def __init__(self, X=1, Y=1, Z=1):
+        self.X, self.Y, self.Z = X, Y, Z
+
+    def Size(self):                                   # guda.go:330-332
+        return self.X * self.Y * self.Z
+
+
+class ThreadID:
+    """guda.go:73-78 with the index helpers of guda.go:310-327."""
+
+    def __init__(self, BlockIdx, ThreadIdx, BlockDim, GridDim):
+        self.BlockIdx, self.ThreadIdx, self.BlockDim, self.GridDim = BlockIdx, ThreadIdx, BlockDim, GridDim
+
+    def Global(self): return self.BlockIdx.X * self.BlockDim.X + self.ThreadIdx.X
+    def GlobalX(self): return self.Global()
+    def GlobalY(self): return self.BlockIdx.Y * self.BlockDim.Y + self.ThreadIdx.Y
+    def GlobalZ(self): return self.BlockIdx.Z * self.BlockDim.Z + self.ThreadIdx.Z
+
+
+_LAUNCH_MSG = ("host closures cannot run on the device: use the device-kernel entry points (Add/Multiply/ReLU/Sigmoid, "
+               "FusedKernel.Execute, LinearReLU, GELU, GEMMBFloat16/GEMMFloat16, the reductions)")
+
+
+def _launch_refused(op, grid, block):
+    if grid.Size() <= 0 or block.Size() <= 0:
+        raise GUDAError(capi.ERR_INVALID_ARG, op, "grid and block dimensions must be positive")
+    raise GUDAError(capi.ERR_NOT_IMPLEMENTED, op, _LAUNCH_MSG)
+
+
+def Launch(kernel, grid, block, *args):               # guda.go:184-186: a Go closure per (block, thread) -- no device equivalent
+    _launch_refused("Launch", grid, block)
+
+
+def LaunchFunc(fn, grid, block, *args):               # guda.go:189-191
+    _launch_refused("LaunchFunc", grid, block)
+
+
+def LaunchStream(kernel, grid, block, stream, *args):     # guda.go:268-270
+    _launch_refused("LaunchStream", grid, block)
+
+
+def LaunchFuncStream(fn, grid, block, stream, *args):     # guda.go:273-275
+    _launch_refused("LaunchFuncStream", grid, block)

@@ -30,6 +30,18 @@ class FusedOp(C.Structure):
 FUSED_ADD, FUSED_MUL, FUSED_ADD_SCALAR, FUSED_MUL_SCALAR, FUSED_RELU, FUSED_SIGMOID, FUSED_GELU = range(7)
 
 
+class Tolerance(C.Structure):
+    """guda_tolerance_t: tolerance.go:10-26 ToleranceConfig + the fields of the sm_100a architecture entry."""
+    _fields_ = [("abs_tol", C.c_float), ("rel_tol", C.c_float), ("ulp_tol", C.c_int), ("check_nan", C.c_int), ("check_inf", C.c_int),
+                ("k_scale", C.c_float), ("half_ulp_tol", C.c_int), ("abs64", C.c_double), ("rel64", C.c_double)]
+
+
+class VerifyResult(C.Structure):
+    """guda_verify_result_t: tolerance.go:121-128 VerificationResult."""
+    _fields_ = [("max_abs_error", C.c_float), ("max_rel_error", C.c_float), ("max_ulp_error", C.c_int), ("num_errors", C.c_longlong),
+                ("total_items", C.c_longlong), ("first_error", C.c_longlong)]
+
+
 class DeviceProps(C.Structure):
     _fields_ = [("id", C.c_int), ("name", C.c_char * 128), ("total_mem", C.c_size_t), ("sm_count", C.c_int),
                 ("max_threads", C.c_int), ("cc_major", C.c_int), ("cc_minor", C.c_int), ("l2_bytes", C.c_int)]
@@ -84,6 +96,7 @@ SIGNATURES = {
     "guda_sgemm_host": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_dgemm": (i, [i, i, i, i, i, d, vp, i, vp, i, d, vp, i, vp]),
     "guda_sgemm_scatter": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, C.POINTER(vp), i, i, i, i, vp]),
+    "guda_dgemm_scatter": (i, [i, i, i, i, i, d, vp, i, vp, i, d, vp, i, C.POINTER(vp), i, i, i, i, vp]),
     "guda_set_dgemm_mode": (i, [i]),
     "guda_get_dgemm_mode": (i, [ip]),
     "guda_gemm_bf16": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
@@ -136,6 +149,13 @@ SIGNATURES = {
     "guda_comm_set_gather_mode": (i, [vp, i]),
     "guda_comm_get_gather_mode": (i, [vp, ip]),
     "guda_sdot_sharded": (i, [vp, i, vp, vp, fp, vp]),
+    "guda_saxpy_sharded": (i, [vp, i, f, vp, vp, vp]),
+    "guda_dgemm_sharded": (i, [vp, i, i, i, i, i, d, vp, i, vp, i, vp, i, vp, i, vp]),
+    "guda_tolerance_preset": (i, [i, C.POINTER(Tolerance)]),
+    "guda_merge_tolerances": (i, [C.POINTER(Tolerance), C.POINTER(Tolerance), C.POINTER(Tolerance)]),
+    "guda_get_operation_tolerance": (i, [C.c_char_p, C.c_char_p, C.POINTER(Tolerance)]),
+    "guda_standard_tolerance": (i, [C.c_char_p, fp, fp, ip]),
+    "guda_verify_f32": (i, [vp, vp, C.c_longlong, C.POINTER(Tolerance), C.POINTER(VerifyResult), vp]),
     "guda_microbench_peak": (i, [i, i, dp]),
     "guda_microbench_lds": (i, [i, ip, i, dp]),
 }

@@ -18,7 +18,7 @@
 // (64 fp64 accumulators per thread).  Operands stream global -> shared with 16-byte cp.async (zero-fill at the edges)
 // through a 4-stage ring; shared rows are padded by 4 doubles, which makes every fragment load (LDS.64, quarter-warp
 // = 4 rows x 4 k) bank-conflict free.  The last K % 4 terms are applied with scalar FMAs on the accumulator fragments.
-#include "common.cuh"
+#include "gemm_simt.cuh"      // ScatterParams / ScatterArgsT (the fused all-gather epilogue shared with the SGEMM kernels)
 
 namespace guda {
 
@@ -56,8 +56,10 @@ __device__ __forceinline__ int clamp16(long long bytes) { return bytes >= 16 ? 1
 
 // TA: A is stored transposed ([k][m]).  SCALE: alpha != 1 (A fragments are multiplied by alpha as they are read).
 // SKIP: the reference route has the `tmp != 0` test.
-template <bool TA, bool SCALE, bool SKIP>
-__global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams p) {
+// SCAT: besides c (which may then be null) every finished element is stored at (row, col) + off of each matrix in sp.dst[] --
+// the gathered C of every rank, peers reached through NVLink-mapped pointers (sharded.cu, guda_dgemm_sharded).
+template <bool TA, bool SCALE, bool SKIP, bool SCAT = false>
+__global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams p, ScatterParams<double, SCAT> sp) {
   using namespace dmma;
   extern __shared__ __align__(16) double dsm[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -115,7 +117,7 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
 #pragma unroll
       for (int e = 0; e < 2; e++) {
         double v = 0.0;
-        if (p.beta != 0.0 && row < p.m && col + e < p.n) {
+        if (p.beta != 0.0 && p.c && row < p.m && col + e < p.n) {
           v = p.c[(long long)row * p.ldc + col + e];
           if (p.beta != 1.0) v = __dmul_rn(v, p.beta);
         }
@@ -206,7 +208,7 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
         const int row = m0 + e / BN, col = n0 + e % BN;
         if (row >= p.m || col >= p.n || row >= p.edge_m || col >= p.edge_n) continue;
         double v = 0.0;
-        if (p.beta != 0.0) {
+        if (p.beta != 0.0 && p.c) {
           v = p.c[(long long)row * p.ldc + col];
           if (p.beta != 1.0) v = __dmul_rn(v, p.beta);
         }
@@ -214,7 +216,10 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
           const double t = __dmul_rn(p.alpha, TA ? p.a[(long long)l * p.lda + row] : p.a[(long long)row * p.lda + l]);
           if (t != 0.0) v = __fma_rn(t, p.b[(long long)l * p.ldb + col], v);
         }
-        p.c[(long long)row * p.ldc + col] = v;
+        if (!SCAT || p.c) p.c[(long long)row * p.ldc + col] = v;
+        if constexpr (SCAT) {
+          for (int d = 0; d < sp.n; d++) sp.dst[d][(long long)row * sp.ld + sp.off + col] = v;
+        }
       }
       return;
     }
@@ -230,38 +235,61 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
 #pragma unroll
     for (int nf = 0; nf < 4; nf++) {
       const int col = n0 + wn * 32 + nf * 8 + q * 2;
-      double* dst = p.c + (long long)row * p.ldc + col;
-      if (vec_ok && col + 1 < lim_n) {
-        *reinterpret_cast<double2*>(dst) = make_double2(acc[mf][nf][0], acc[mf][nf][1]);
-      } else {
-        if (col < lim_n) dst[0] = acc[mf][nf][0];
-        if (col + 1 < lim_n) dst[1] = acc[mf][nf][1];
+      if (!SCAT || p.c) {
+        double* dst = p.c + (long long)row * p.ldc + col;
+        if (vec_ok && col + 1 < lim_n) {
+          *reinterpret_cast<double2*>(dst) = make_double2(acc[mf][nf][0], acc[mf][nf][1]);
+        } else {
+          if (col < lim_n) dst[0] = acc[mf][nf][0];
+          if (col + 1 < lim_n) dst[1] = acc[mf][nf][1];
+        }
+      }
+      if constexpr (SCAT) {
+        const bool svec = ((sp.ld & 1) == 0) && ((sp.off & 1) == 0) && col + 1 < lim_n;
+        for (int d = 0; d < sp.n; d++) {
+          double* dst = sp.dst[d] + (long long)row * sp.ld + sp.off + col;
+          if (svec && (reinterpret_cast<uintptr_t>(sp.dst[d]) & 15) == 0) {
+            *reinterpret_cast<double2*>(dst) = make_double2(acc[mf][nf][0], acc[mf][nf][1]);
+          } else {
+            if (col < lim_n) dst[0] = acc[mf][nf][0];
+            if (col + 1 < lim_n) dst[1] = acc[mf][nf][1];
+          }
+        }
       }
     }
   }
 }
 
-template <bool TA, bool SCALE, bool SKIP>
-static int launch_dmma(const DmmaParams& p, cudaStream_t s) {
-  auto kern = dgemm_dmma_kernel<TA, SCALE, SKIP>;
+template <bool TA, bool SCALE, bool SKIP, bool SCAT>
+static int launch_dmma_s(const DmmaParams& p, const ScatterParams<double, SCAT>& sp, cudaStream_t s) {
+  auto kern = dgemm_dmma_kernel<TA, SCALE, SKIP, SCAT>;
   static bool attr_set = false;
   if (!attr_set) {
     GUDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dmma::SMEM_BYTES));
     attr_set = true;
   }
-  kern<<<p.tiles_m * p.tiles_n, dmma::THREADS, dmma::SMEM_BYTES, s>>>(p);
+  kern<<<p.tiles_m * p.tiles_n, dmma::THREADS, dmma::SMEM_BYTES, s>>>(p, sp);
   return check_launch("dgemm_dmma");
+}
+template <bool TA, bool SCALE, bool SKIP>
+static int launch_dmma(const DmmaParams& p, cudaStream_t s, const ScatterArgsT<double>* sc) {
+  if (!sc) return launch_dmma_s<TA, SCALE, SKIP, false>(p, {}, s);
+  ScatterParams<double, true> sp;
+  sp.n = sc->n;
+  for (int i = 0; i < GUDA_MAX_SCATTER; i++) sp.dst[i] = i < sc->n ? sc->dst[i] : nullptr;
+  sp.ld = sc->ld; sp.off = sc->off;
+  return launch_dmma_s<TA, SCALE, SKIP, true>(p, sp, s);
 }
 
 static int g_dgemm_mode = GUDA_DGEMM_TENSOR;
 int dgemm_dmma_one(int ta, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta, double* c,
-                   int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s);
+                   int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s, const ScatterArgsT<double>* sc);
 int dgemm_mode() { return g_dgemm_mode; }
 
 // Returns GUDA_OK / an error if the DMMA route took the call, -1 if the operands are not eligible (caller uses the SIMT kernel).
 // Eligible: B not transposed, 16-byte aligned A and B with even leading dimensions (cp.async granule).
 int dgemm_dmma_try(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
-                   double* c, int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s) {
+                   double* c, int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s, const ScatterArgsT<double>* sc) {
   if (g_dgemm_mode != GUDA_DGEMM_TENSOR || tb) return -1;
   if (m < 32 || n < 32 || k < 4) return -1;
   if (((uintptr_t)a & 15) || ((uintptr_t)b & 15) || (lda & 1) || (ldb & 1)) return -1;
@@ -271,25 +299,26 @@ int dgemm_dmma_try(int ta, int tb, int m, int n, int k, double alpha, const doub
   if (k >= 2 * KC && (long long)m * n >= (1ll << 22)) {
     for (int k0 = 0; k0 < k; k0 += KC) {
       const int kc = (k0 + KC >= k) ? k - k0 : KC;
+      if (sc && !c) return set_error(GUDA_ERR_INVALID_ARG, "dgemm_scatter: a K-chunked call needs a local C block");
       int rc = dgemm_dmma_one(ta, m, n, kc, alpha, ta ? a + (long long)k0 * lda : a + k0, lda, b + (long long)k0 * ldb, ldb,
-                              k0 == 0 ? beta : 1.0, c, ldc, edge_m, edge_n, skip, s);
+                              k0 == 0 ? beta : 1.0, c, ldc, edge_m, edge_n, skip, s, (k0 + KC >= k) ? sc : nullptr);
       if (rc) return rc;
     }
     return GUDA_OK;
   }
-  return dgemm_dmma_one(ta, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, edge_m, edge_n, skip, s);
+  return dgemm_dmma_one(ta, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, edge_m, edge_n, skip, s, sc);
 }
 
 int dgemm_dmma_one(int ta, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta, double* c,
-                   int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s) {
+                   int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s, const ScatterArgsT<double>* sc) {
   DmmaParams p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, edge_m, edge_n, (m + dmma::BM - 1) / dmma::BM, (n + dmma::BN - 1) / dmma::BN};
   const bool scale = alpha != 1.0;
   if (ta) {
-    if (scale) return skip ? launch_dmma<true, true, true>(p, s) : launch_dmma<true, true, false>(p, s);
-    return skip ? launch_dmma<true, false, true>(p, s) : launch_dmma<true, false, false>(p, s);
+    if (scale) return skip ? launch_dmma<true, true, true>(p, s, sc) : launch_dmma<true, true, false>(p, s, sc);
+    return skip ? launch_dmma<true, false, true>(p, s, sc) : launch_dmma<true, false, false>(p, s, sc);
   }
-  if (scale) return skip ? launch_dmma<false, true, true>(p, s) : launch_dmma<false, true, false>(p, s);
-  return skip ? launch_dmma<false, false, true>(p, s) : launch_dmma<false, false, false>(p, s);
+  if (scale) return skip ? launch_dmma<false, true, true>(p, s, sc) : launch_dmma<false, true, false>(p, s, sc);
+  return skip ? launch_dmma<false, false, true>(p, s, sc) : launch_dmma<false, false, false>(p, s, sc);
 }
 
 }  // namespace guda

@@ -9,7 +9,7 @@ namespace guda {
 int sgemm_mode();
 // FP64 tensor pipe (dgemm_dmma.cu); GUDA_OK / error if it took the call, -1 if the operands are not eligible
 int dgemm_dmma_try(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
-                   double* c, int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s);
+                   double* c, int ldc, int edge_m, int edge_n, bool skip, cudaStream_t s, const ScatterArgsT<double>* sc = nullptr);
 // TMA-fed exact-order pipeline (sgemm_pipe.cu); GUDA_OK / error if it took the call, -1 if the call is not eligible
 int sgemm_pipe_try(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta, float* c,
                    int ldc, const float* bias, int epi, const ScatterArgs* scatter, cudaStream_t s);
@@ -199,16 +199,33 @@ static int sgemm_impl(int ta, int tb, int m, int n, int k, float alpha, const fl
 }
 
 static int dgemm_impl(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb,
-                      double beta, double* c, int ldc, guda_stream_t stream) {
+                      double beta, double* c, int ldc, guda_stream_t stream, const ScatterArgsT<double>* scatter = nullptr) {
   int rc = check_gemm_args(ta, tb, m, n, k, lda, ldb, ldc);
   if (rc) return rc;
   if (m == 0 || n == 0) return GUDA_OK;
   rc = bind_device();
   if (rc) return rc;
-  if (!c || ((!a || !b) && k > 0)) return set_error(GUDA_ERR_INVALID_ARG, "Dgemm: null pointer");
-  if ((alpha == 0.0 || k == 0) && beta == 1.0) return GUDA_OK;            // compute/dgemm.go:99
+  if ((!c && !(scatter && beta == 0.0)) || ((!a || !b) && k > 0)) return set_error(GUDA_ERR_INVALID_ARG, "Dgemm: null pointer");
   cudaStream_t s = native(stream);
   GemmParams<double> p{m, n, k, alpha, beta, a, lda, b, ldb, c, ldc, nullptr, m, n};
+  if (scatter) {
+    // fused all-gather epilogue (sharded.cu): NN form on blocks whose edges need no separate pass
+    if (ta || tb) return set_error(GUDA_ERR_NOT_IMPLEMENTED, "dgemm_scatter: only the NN form is implemented");
+    if (m % 4 || n % 4) return set_error(GUDA_ERR_NOT_IMPLEMENTED, "dgemm_scatter: m and n must be multiples of 4");
+    const bool rows_al = (!c || ((uintptr_t)c % 32 == 0 && (m == 1 || ((long long)ldc * 8) % 32 == 0))) &&
+                         (scatter->ld * 8) % 32 == 0 && (scatter->off * 8) % 32 == 0;
+    for (int i = 0; i < scatter->n; i++) if ((uintptr_t)scatter->dst[i] % 32) return set_error(GUDA_ERR_INVALID_ARG, "dgemm_scatter: destinations must be 32-byte aligned");
+    if (!rows_al) return set_error(GUDA_ERR_INVALID_ARG, "dgemm_scatter: C rows must be 32-byte aligned");
+    // alpha == 1: dgemm_fixed.go's plain FMA tiles (no zero test); otherwise the AXPY chain with its `tmp != 0` test
+    rc = dgemm_dmma_try(0, 0, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, m, n, alpha != 1.0, s, scatter);
+    if (rc >= 0) return rc;
+    ScatterParams<double, true> sp;
+    sp.n = scatter->n;
+    for (int i = 0; i < GUDA_MAX_SCATTER; i++) sp.dst[i] = i < scatter->n ? scatter->dst[i] : nullptr;
+    sp.ld = scatter->ld; sp.off = scatter->off;
+    return launch_simt<double, false, false, MODE_FMA, EPI_NONE, true>(p, s, sp);        // same route guda_dgemm takes when DMMA declines
+  }
+  if ((alpha == 0.0 || k == 0) && beta == 1.0) return GUDA_OK;            // compute/dgemm.go:99
   // AxpyUnitary (fp64) is all-FMA only when every C row is 32-byte aligned and n % 4 == 0
   const bool rows_aligned = ((uintptr_t)c % 32 == 0) && (m == 1 || ((long long)ldc * 8) % 32 == 0) && (n % 4 == 0);
   if (!ta && !tb) {
@@ -296,6 +313,23 @@ int guda_dgemm(int ta, int tb, int m, int n, int k, double alpha, const double* 
 
 // SGEMM whose epilogue also stores the finished block at (row0, col0) of `ndest` larger row-major matrices (leading
 // dimension ld_dest) -- the building block of the fused GEMM + all-gather (sharded.cu), exact-order route only.
+// DGEMM twin of guda_sgemm_scatter (NN, m and n multiples of 4, 32-byte aligned rows): the DMMA kernel's epilogue stores
+// the finished block at (row0, col0) of every destination matrix
+int guda_dgemm_scatter(int ta, int tb, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb, double beta,
+                       double* c, int ldc, double* const* host_dests, int ndest, int ld_dest, int row0, int col0, guda_stream_t stream) {
+  if (ndest < 0 || ndest > GUDA_MAX_SCATTER || (ndest > 0 && !host_dests)) return set_error(GUDA_ERR_INVALID_ARG, "dgemm_scatter: bad destination list");
+  if (ndest == 0) return dgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream);
+  if (row0 < 0 || col0 < 0 || ld_dest < col0 + n) GUDA_PANIC("blas: bad leading dimension of C");
+  ScatterArgsT<double> sc{};
+  sc.n = ndest;
+  for (int i = 0; i < ndest; i++) {
+    if (!host_dests[i]) return set_error(GUDA_ERR_INVALID_ARG, "dgemm_scatter: null destination");
+    sc.dst[i] = host_dests[i];
+  }
+  sc.ld = ld_dest; sc.off = (long long)row0 * ld_dest + col0;
+  return dgemm_impl(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, stream, &sc);
+}
+
 int guda_sgemm_scatter(int ta, int tb, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb, float beta,
                        float* c, int ldc, float* const* host_dests, int ndest, int ld_dest, int row0, int col0, guda_stream_t stream) {
   if (ndest < 0 || ndest > GUDA_MAX_SCATTER || (ndest > 0 && !host_dests)) return set_error(GUDA_ERR_INVALID_ARG, "sgemm_scatter: bad destination list");

@@ -128,7 +128,8 @@ template <typename T> struct ScatterParams<T, true> {
   long long ld, off;
 };
 
-struct ScatterArgs { int n; float* dst[GUDA_MAX_SCATTER]; long long ld, off; };
+template <typename T> struct ScatterArgsT { int n; T* dst[GUDA_MAX_SCATTER]; long long ld, off; };
+using ScatterArgs = ScatterArgsT<float>;
 
 template <typename T, int BM, int BN, int BK>
 struct GemmSmem {

@@ -85,10 +85,12 @@ __global__ void __launch_bounds__(256) lds_pattern_kernel(const int* __restrict_
   for (int it = 0; it < iters; it++) {
 #pragma unroll
     for (int u = 0; u < 8; u++) {
-      const unsigned addr = base + u * 4096;
-      if (W == 16) asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r[u][0]), "=r"(r[u][1]), "=r"(r[u][2]), "=r"(r[u][3]) : "r"(addr));
-      else if (W == 8) asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r[u][0]), "=r"(r[u][1]) : "r"(addr));
-      else asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r[u][0]) : "r"(addr));
+      // the row moves with the iteration (whole 128-byte rows: the lane -> bank pattern is unchanged) so that the loads
+      // are not loop-invariant
+      const unsigned addr = base + u * 4096 + (it & 7) * 128;
+      if (W == 16) asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r[u][0]), "=r"(r[u][1]), "=r"(r[u][2]), "=r"(r[u][3]) : "r"(addr) : "memory");
+      else if (W == 8) asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r[u][0]), "=r"(r[u][1]) : "r"(addr) : "memory");
+      else asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r[u][0]) : "r"(addr) : "memory");
     }
   }
   __syncthreads();
@@ -213,7 +215,7 @@ int guda_microbench_peak(int kind, int reps, double* value) {
 int guda_microbench_lds(int width, const int* host_lane_idx, int iters, double* cycles_per_instr) {
   if (!host_lane_idx || !cycles_per_instr || iters <= 0) return set_error(GUDA_ERR_INVALID_ARG, "bad argument");
   if (width != 4 && width != 8 && width != 16) return set_error(GUDA_ERR_INVALID_ARG, "width must be 4, 8 or 16");
-  for (int i = 0; i < 32; i++) if (host_lane_idx[i] < 0 || host_lane_idx[i] * width + width > 4096) return set_error(GUDA_ERR_INVALID_ARG, "chunk index out of range");
+  for (int i = 0; i < 32; i++) if (host_lane_idx[i] < 0 || host_lane_idx[i] * width + width > 3072) return set_error(GUDA_ERR_INVALID_ARG, "chunk index out of range");
   int rc = bind_device();
   if (rc) return rc;
   int* idx; unsigned long long* out;

@@ -169,37 +169,51 @@ sgemm_pipe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   }
 
   const int a_off = wm * (TM * LY) + ly * 4, b_off = wn * (TN * LX) + lx * 4;
+  // one k step of the fast path: fragment loads (128-bit, conflict-free) + TM*TN/2 packed FMAs
+  auto kstep = [&](const float* As, const float* Bs, int kk) {
+    float af[TM], bf[TN];
+#pragma unroll
+    for (int cm = 0; cm < TM / 4; cm++) *reinterpret_cast<float4*>(af + cm * 4) = *reinterpret_cast<const float4*>(As + kk * BM + cm * (LY * 4));
+#pragma unroll
+    for (int cn = 0; cn < TN / 4; cn++) *reinterpret_cast<float4*>(bf + cn * 4) = *reinterpret_cast<const float4*>(Bs + kk * BN + cn * (LX * 4));
+    if constexpr (PAIR_M) {
+#pragma unroll
+      for (int j = 0; j < TN; j++) {
+        const unsigned long long bb = dup_f32(bf[j]);
+#pragma unroll
+        for (int i = 0; i < TM; i += 2) fma2_f32(acc[j][i], acc[j][i + 1], bb, af[i], af[i + 1]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < TM; i++) {
+        const unsigned long long aa = dup_f32(af[i]);
+#pragma unroll
+        for (int j = 0; j < TN; j += 2) fma2_f32(acc[i][j], acc[i][j + 1], aa, bf[j], bf[j + 1]);
+      }
+    }
+  };
   unsigned char zcur = KT > 0 ? zf[0] : 0;
+  // s / phase: ring slot and mbarrier parity of the current k-tile, carried in registers (no division in the loop).
+  // `ready`: the full barrier of the NEXT k-tile is tested (non-blocking mbarrier.test_wait) in the middle of the current
+  // stage's arithmetic, so at the stage boundary a warp normally falls straight through instead of paying the
+  // try_wait round trip (ncu: 4.6 % of all warp samples sat on that branch in the first version of this kernel).
+  int s = 0;
+  uint32_t phase = 0, ready = 0;
+  const bool dry = lag >= 100;      // timing experiment only (guda_set_sgemm_pipe lag >= 100): no waits, no refills, results are garbage
+  if (dry) lag -= 100;
   for (int kt = 0; kt < KT; kt++) {
-    const int s = kt % STAGES;
     const float* As = reinterpret_cast<const float*>(smem_raw + s * Cfg::STAGE_BYTES) + a_off;
     const float* Bs = reinterpret_cast<const float*>(smem_raw + s * Cfg::STAGE_BYTES) + BK * BM + b_off;
-    mbar_wait(&full[s], (kt / STAGES) & 1);
-    const unsigned char znext = kt + 1 < KT ? zf[kt + 1] : 0;      // read a stage ahead: the branch below never waits on shared memory
+    if (!ready && !dry) mbar_wait(&full[s], phase);
+    const int s1 = (s + 1 == STAGES) ? 0 : s + 1;
+    const uint32_t phase1 = (s + 1 == STAGES) ? phase ^ 1u : phase;
+    unsigned char znext = 0;
     if (!zcur) {
 #pragma unroll
-      for (int kk = 0; kk < BK; kk++) {
-        float af[TM], bf[TN];
+      for (int kk = 0; kk < BK / 2; kk++) kstep(As, Bs, kk);
+      if (kt + 1 < KT) { ready = dry ? 1u : mbar_test_wait_nb(&full[s1], phase1); znext = zf[kt + 1]; }
 #pragma unroll
-        for (int cm = 0; cm < TM / 4; cm++) *reinterpret_cast<float4*>(af + cm * 4) = *reinterpret_cast<const float4*>(As + kk * BM + cm * (LY * 4));
-#pragma unroll
-        for (int cn = 0; cn < TN / 4; cn++) *reinterpret_cast<float4*>(bf + cn * 4) = *reinterpret_cast<const float4*>(Bs + kk * BN + cn * (LX * 4));
-        if constexpr (PAIR_M) {
-#pragma unroll
-          for (int j = 0; j < TN; j++) {
-            const unsigned long long bb = dup_f32(bf[j]);
-#pragma unroll
-            for (int i = 0; i < TM; i += 2) fma2_f32(acc[j][i], acc[j][i + 1], bb, af[i], af[i + 1]);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < TM; i++) {
-            const unsigned long long aa = dup_f32(af[i]);
-#pragma unroll
-            for (int j = 0; j < TN; j += 2) fma2_f32(acc[i][j], acc[i][j + 1], aa, bf[j], bf[j + 1]);
-          }
-        }
-      }
+      for (int kk = BK / 2; kk < BK; kk++) kstep(As, Bs, kk);
     } else {
 #pragma unroll 2
       for (int kk = 0; kk < BK; kk++) {
@@ -216,22 +230,27 @@ sgemm_pipe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           }
         }
       }
+      ready = 0;
+      if (kt + 1 < KT) znext = zf[kt + 1];
     }
     zcur = znext;
     __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[s]);
-    if (tid == 0) {
-      // refill the stage every warp released `lag` iterations ago with k-tile kr + STAGES
+    if (lane == 0 && !dry) {
+      mbar_arrive(&empty[s]);
+      // the refill of the slot every warp released `lag` iterations ago (k-tile kr + STAGES) rotates over the warps, so no
+      // single warp carries the producer's instructions on its critical path
       const int kr = kt - lag;
-      if (kr >= 0 && kr + STAGES < KT) {
-        const int sr = kr % STAGES;
-        mbar_wait(&empty[sr], (kr / STAGES) & 1);
+      if (kr >= 0 && kr + STAGES < KT && (kt % Cfg::WARPS) == warp) {
+        int sr = s - lag; if (sr < 0) sr += STAGES;
+        const uint32_t pr = (s - lag < 0) ? phase ^ 1u : phase;
+        mbar_wait(&empty[sr], pr);
         float* sa = reinterpret_cast<float*>(smem_raw + sr * Cfg::STAGE_BYTES);
         mbar_arrive_expect_tx(&full[sr], Cfg::STAGE_BYTES);
         tma_load_2d(sa, &map_a, &full[sr], m0, (kr + STAGES) * BK);
         tma_load_2d(sa + BK * BM, &map_b, &full[sr], n0, (kr + STAGES) * BK);
       }
     }
+    s = s1; phase = phase1;
   }
   // (every refill is issued inside the loop: k-tile kr + STAGES < KT is requested at iteration kr + lag <= KT - 1 for lag < STAGES)
 
@@ -271,8 +290,8 @@ using Pipe7  = PipeCfg< 8,  8,  2, 16,  4, 1, 16, 4, 2>;    //  64 x 128, 128 th
 using Pipe8  = PipeCfg< 8,  8,  2, 16,  8, 1, 32, 3, 2>;    // Pipe1 with 32-deep stages
 using Pipe9  = PipeCfg<16,  8,  1, 32,  4, 1, 16, 4, 2>;    //  64 x 256, 128 threads, 16 x 8 micro-tile on one lane row
 using Pipe10 = PipeCfg< 8,  8,  2, 16,  4, 1, 32, 3, 2>;    // Pipe7 with 32-deep stages
-using Pipe11 = PipeCfg<16,  8,  2, 16,  4, 1, 16, 4, 3>;    // Pipe4 squeezed to 3 CTAs/SM (<= 170 registers)
-using Pipe12 = PipeCfg<16,  8,  2, 16,  4, 1, 32, 2, 3>;    // Pipe11 with 32-deep stages, 2-deep ring
+using Pipe11 = PipeCfg<16,  8,  1, 32,  4, 1, 16, 5, 2>;    // Pipe9 with a 5-deep ring
+using Pipe12 = PipeCfg<16,  8,  2, 16,  4, 1, 16, 6, 2>;    // Pipe4 with a 6-deep ring
 using Pipe13 = PipeCfg<16,  8,  1, 32,  4, 1, 32, 2, 2>;    // Pipe9 with 32-deep stages, 2-deep ring
 using Pipe14 = PipeCfg< 8,  8,  2, 16,  4, 1, 64, 2, 2>;    // Pipe7 with 64-deep stages (1024^3: 16 stage boundaries)
 constexpr int PIPE_NCFG = 14;
@@ -293,7 +312,7 @@ static int launch_pipe_cfg(const GemmParams<float>& p, const float* at, long lon
   std::call_once(once, [&] { attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM); });
   if (attr_err != cudaSuccess) return set_error(GUDA_ERR_EXECUTION, "sgemm_pipe: cannot reserve %d bytes of shared memory", Cfg::SMEM);
   const long long tiles = (long long)(p.m / Cfg::BM) * (p.n / Cfg::BN);
-  int lag = g_pipe_lag < 0 ? 0 : (g_pipe_lag > Cfg::STAGES - 1 ? Cfg::STAGES - 1 : g_pipe_lag);
+  int lag = g_pipe_lag < 0 ? 0 : (g_pipe_lag >= 100 ? 101 : (g_pipe_lag > Cfg::STAGES - 1 ? Cfg::STAGES - 1 : g_pipe_lag));
   kern<<<(unsigned)tiles, Cfg::THREADS, Cfg::SMEM, s>>>(ma, mb, p, flags, flag_ld, lag, sp);
   return check_launch("sgemm_pipe");
 }

@@ -65,7 +65,7 @@ struct PeerMapping { cudaIpcMemHandle_t handle; void* base; };
 struct Comm {
   ncclComm_t comm;
   int nranks, rank;
-  float* staging = nullptr;      // all-gather landing zone (NCCL mode), grown on demand
+  void* staging = nullptr;       // all-gather landing zone (NCCL mode), grown on demand
   size_t staging_bytes = 0;
   float* dev_scalar = nullptr;
   int gather_mode = GUDA_GATHER_P2P;
@@ -73,12 +73,16 @@ struct Comm {
   PeerRecord* dev_records = nullptr;            // [nranks + 1]: slot nranks is this rank's send buffer
   PeerRecord* host_records = nullptr;           // pinned, [nranks + 1]
   std::vector<std::vector<PeerMapping>> opened; // per peer rank: allocations already mapped into this process
+  // steady state: the gathered-C buffers of the previous call, valid while no rank's (handle, offset) record changes
+  bool cache_valid = false;
+  PeerRecord cache_mine{};
+  void* cache_peers[GUDA_MAX_SCATTER_RANKS] = {};
 };
 
 // Collective: every rank publishes where its c_full lives; returns device-usable pointers to every rank's c_full.
 // The NCCL all-gather + stream synchronise also acts as the entry barrier: when it returns, every rank has finished
 // whatever preceded this call on its stream, so peers may overwrite its c_full.
-static int resolve_peers(Comm* c, float* c_full, cudaStream_t s, float** out, bool* all_ok) {
+static int resolve_peers(Comm* c, void* c_full, cudaStream_t s, void** out, bool* all_ok) {
   PeerRecord mine{};
   CUdeviceptr base = 0; size_t range = 0;
   // the driver entry point is resolved at run time so that the library has no link-time dependency on libcuda.so.1
@@ -94,6 +98,20 @@ static int resolve_peers(Comm* c, float* c_full, cudaStream_t s, float** out, bo
   cudaGetLastError();
   mine.offset = ok ? (unsigned long long)((CUdeviceptr)c_full - base) : 0;
   mine.ok = ok ? 1 : 0;
+  // Steady state (every step of a loop gathers into the same buffers): one all-reduce asks "did any rank's record change?".
+  // It is also the entry barrier -- it completes on this stream only after every rank has reached it on theirs, i.e. after
+  // whatever they queued before this call, so peers may now overwrite this rank's c_full.  Only a change pays the full exchange.
+  float changed = (!c->cache_valid || memcmp(&mine, &c->cache_mine, sizeof(mine)) != 0) ? 1.0f : 0.0f;
+  GUDA_CUDA(cudaMemcpyAsync(c->dev_scalar, &changed, sizeof(float), cudaMemcpyHostToDevice, s));
+  GUDA_NCCL(g_nccl.AllReduce(c->dev_scalar, c->dev_scalar, 1, ncclFloat, ncclMax, c->comm, s));
+  GUDA_CUDA(cudaMemcpyAsync(&changed, c->dev_scalar, sizeof(float), cudaMemcpyDeviceToHost, s));
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  if (changed < 0.5f) {
+    for (int r = 0; r < c->nranks; r++) out[r] = c->cache_peers[r];
+    *all_ok = true;
+    return GUDA_OK;
+  }
+  c->cache_valid = false;
   c->host_records[c->nranks] = mine;
   GUDA_CUDA(cudaMemcpyAsync(c->dev_records + c->nranks, c->host_records + c->nranks, sizeof(PeerRecord), cudaMemcpyHostToDevice, s));
   GUDA_NCCL(g_nccl.AllGather(c->dev_records + c->nranks, c->dev_records, sizeof(PeerRecord), ncclChar, c->comm, s));
@@ -111,7 +129,7 @@ static int resolve_peers(Comm* c, float* c_full, cudaStream_t s, float** out, bo
       if (cudaIpcOpenMemHandle(&mapped, rec.handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); good = false; break; }
       c->opened[r].push_back(PeerMapping{rec.handle, mapped});
     }
-    out[r] = reinterpret_cast<float*>(static_cast<char*>(mapped) + rec.offset);
+    out[r] = static_cast<char*>(mapped) + rec.offset;
   }
   // every rank must take the same route: agree on the outcome (a rank that could not map a peer vetoes P2P for all)
   float flag = good ? 1.0f : 0.0f;
@@ -120,24 +138,31 @@ static int resolve_peers(Comm* c, float* c_full, cudaStream_t s, float** out, bo
   GUDA_CUDA(cudaMemcpyAsync(&flag, c->dev_scalar, sizeof(float), cudaMemcpyDeviceToHost, s));
   GUDA_CUDA(cudaStreamSynchronize(s));
   *all_ok = flag > 0.5f;
+  if (*all_ok) {
+    c->cache_valid = true;
+    c->cache_mine = mine;
+    for (int r = 0; r < c->nranks; r++) c->cache_peers[r] = out[r];
+  }
   return GUDA_OK;
 }
 
 // gathered [rank][m_loc][n_loc] blocks -> row-major c_full; 128-bit copies when the geometry allows
-__global__ void unpack_blocks_kernel(const float* __restrict__ staging, float* __restrict__ c_full, long long ldc_full, int pr, int pc,
+template <typename T, typename V>
+__global__ void unpack_blocks_kernel(const T* __restrict__ staging, T* __restrict__ c_full, long long ldc_full, int pr, int pc,
                                      int m_loc, int n_loc) {
+  constexpr int VN = sizeof(V) / sizeof(T);
   const long long per_block = (long long)m_loc * n_loc;
   const long long total = per_block * pr * pc;
-  if ((n_loc & 3) == 0 && (ldc_full & 3) == 0 && ((uintptr_t)c_full & 15) == 0 && ((uintptr_t)staging & 15) == 0) {
-    const long long nv = total / 4;
+  if ((n_loc % VN) == 0 && (ldc_full % VN) == 0 && ((uintptr_t)c_full & 15) == 0 && ((uintptr_t)staging & 15) == 0) {
+    const long long nv = total / VN;
     for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += (long long)gridDim.x * blockDim.x) {
-      long long e = v * 4;
+      long long e = v * VN;
       int q = (int)(e / per_block);
       long long w = e % per_block;
       int i = (int)(w / n_loc), j = (int)(w % n_loc);
       int r = q / pc, c = q % pc;
-      float4 val = *reinterpret_cast<const float4*>(staging + e);
-      *reinterpret_cast<float4*>(c_full + ((long long)r * m_loc + i) * ldc_full + (long long)c * n_loc + j) = val;
+      V val = *reinterpret_cast<const V*>(staging + e);
+      *reinterpret_cast<V*>(c_full + ((long long)r * m_loc + i) * ldc_full + (long long)c * n_loc + j) = val;
     }
   } else {
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
@@ -148,6 +173,29 @@ __global__ void unpack_blocks_kernel(const float* __restrict__ staging, float* _
       c_full[((long long)r * m_loc + i) * ldc_full + (long long)c * n_loc + j] = staging[e];
     }
   }
+}
+
+// local block -> every rank's c_full through NCCL (the route beside the fused epilogue)
+template <typename T, typename V>
+static int gather_blocks_nccl(Comm* c, int pr, int pc, int m_loc, int n_loc, int n_total, const T* c_block, T* c_full, int ldc_full,
+                              ncclDataType_t dt, cudaStream_t s) {
+  const size_t per_block = (size_t)m_loc * n_loc;
+  if (pc == 1 && ldc_full == n_total) {
+    // row panels are contiguous in c_full: gather straight into place
+    GUDA_NCCL(g_nccl.AllGather(c_block, c_full, per_block, dt, c->comm, s));
+    return GUDA_OK;
+  }
+  size_t need = per_block * c->nranks * sizeof(T);
+  if (need > c->staging_bytes) {
+    GUDA_CUDA(cudaStreamSynchronize(s));
+    if (c->staging) GUDA_CUDA(cudaFree(c->staging));
+    c->staging = nullptr; c->staging_bytes = 0;
+    GUDA_CUDA(cudaMalloc(&c->staging, need));
+    c->staging_bytes = need;
+  }
+  GUDA_NCCL(g_nccl.AllGather(c_block, c->staging, per_block, dt, c->comm, s));
+  unpack_blocks_kernel<T, V><<<sm_count() * 8, 256, 0, s>>>(static_cast<const T*>(c->staging), c_full, ldc_full, pr, pc, m_loc, n_loc);
+  return check_launch("unpack_blocks");
 }
 
 }  // namespace guda
@@ -224,10 +272,12 @@ static int sgemm_sharded_impl(guda_comm_t comm, int pr, int pc, int m_total, int
   // ---- fused route: ONE kernel computes the block (full K locally: the same per-element k-order as on one GPU, so the
   // bits are identical) and its epilogue stores every finished tile into every rank's c_full over NVLink ----
   if (c_full && c->gather_mode == GUDA_GATHER_P2P && !c->p2p_failed && sgemm_mode() == GUDA_SGEMM_EXACT) {
-    float* peers[GUDA_MAX_SCATTER_RANKS];
+    void* peers_v[GUDA_MAX_SCATTER_RANKS];
     bool ok = false;
-    if ((rc = resolve_peers(c, c_full, s, peers, &ok))) return rc;
+    if ((rc = resolve_peers(c, c_full, s, peers_v, &ok))) return rc;
     if (ok) {
+      float* peers[GUDA_MAX_SCATTER_RANKS];
+      for (int i = 0; i < c->nranks; i++) peers[i] = static_cast<float*>(peers_v[i]);
       const int r = c->rank / pc, q = c->rank % pc;
       rc = guda_sgemm_scatter(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, beta, c_block, ldc_block, peers, c->nranks,
                               ldc_full, r * m_loc, q * n_loc, stream);
@@ -243,28 +293,58 @@ static int sgemm_sharded_impl(guda_comm_t comm, int pr, int pc, int m_total, int
   rc = guda_sgemm(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, beta, c_block, ldc_block, stream);
   if (rc) return rc;
   if (!c_full) return GUDA_OK;             // caller only wants its block
-  const size_t per_block = (size_t)m_loc * n_loc;
-  if (pc == 1 && ldc_full == n_total) {
-    // row panels are contiguous in c_full: gather straight into place
-    GUDA_NCCL(g_nccl.AllGather(c_block, c_full, per_block, ncclFloat, c->comm, s));
-    return GUDA_OK;
+  return gather_blocks_nccl<float, float4>(c, pr, pc, m_loc, n_loc, n_total, c_block, c_full, ldc_full, ncclFloat, s);
+}
+
+// DGEMM twin (row j1 of the scope table: "SGEMM/DGEMM ... @1/2/4/8 B200").  The reference's Dgemm is single-threaded
+// (compute/dgemm.go:122); the 2-D partition with full K per rank keeps every element's chain, so the gathered matrix is
+// bit-identical to the one-GPU product.  Fused route: the DMMA kernel's epilogue stores into every rank's c_full.
+static int dgemm_sharded_impl(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, double alpha, const double* a_panel, int lda,
+                              const double* b_panel, int ldb, double beta, double* c_block, int ldc_block, double* c_full, int ldc_full,
+                              guda_stream_t stream) {
+  if (!comm) return set_error(GUDA_ERR_INVALID_ARG, "null communicator");
+  Comm* c = reinterpret_cast<Comm*>(comm);
+  if (pr < 1 || pc < 1 || pr * pc != c->nranks) return set_error(GUDA_ERR_INVALID_ARG, "process grid %dx%d does not match %d ranks", pr, pc, c->nranks);
+  if (m_total < 0) GUDA_PANIC("blas: m < 0");
+  if (n_total < 0) GUDA_PANIC("blas: n < 0");
+  if (m_total % pr || n_total % pc) return set_error(GUDA_ERR_INVALID_ARG, "m (n) must divide evenly over the process grid");
+  const int m_loc = m_total / pr, n_loc = n_total / pc;
+  if (ldc_block != n_loc) return set_error(GUDA_ERR_INVALID_ARG, "c_block must be packed (ldc_block == n/pc) for the all-gather");
+  int rc = bind_device();
+  if (rc) return rc;
+  cudaStream_t s = native(stream);
+  if (c_full && ldc_full < n_total) GUDA_PANIC("blas: bad leading dimension of C");
+  const bool p2p_shape = m_loc % 4 == 0 && n_loc % 4 == 0 && ldc_full % 4 == 0 && ((uintptr_t)c_full % 32) == 0 && ((uintptr_t)c_block % 32) == 0;
+  if (c_full && c->gather_mode == GUDA_GATHER_P2P && !c->p2p_failed && p2p_shape) {
+    void* peers_v[GUDA_MAX_SCATTER_RANKS];
+    bool ok = false;
+    if ((rc = resolve_peers(c, c_full, s, peers_v, &ok))) return rc;
+    if (ok) {
+      double* peers[GUDA_MAX_SCATTER_RANKS];
+      for (int i = 0; i < c->nranks; i++) peers[i] = static_cast<double*>(peers_v[i]);
+      const int r = c->rank / pc, q = c->rank % pc;
+      rc = guda_dgemm_scatter(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, beta, c_block, ldc_block, peers, c->nranks,
+                              ldc_full, r * m_loc, q * n_loc, stream);
+      if (rc) return rc;
+      GUDA_NCCL(g_nccl.AllReduce(c->dev_scalar, c->dev_scalar, 1, ncclFloat, ncclSum, c->comm, s));     // exit barrier
+      return GUDA_OK;
+    }
+    c->p2p_failed = true;
   }
-  size_t need = per_block * c->nranks * sizeof(float);
-  if (need > c->staging_bytes) {
-    GUDA_CUDA(cudaStreamSynchronize(s));
-    if (c->staging) GUDA_CUDA(cudaFree(c->staging));
-    c->staging = nullptr; c->staging_bytes = 0;
-    GUDA_CUDA(cudaMalloc((void**)&c->staging, need));
-    c->staging_bytes = need;
-  }
-  GUDA_NCCL(g_nccl.AllGather(c_block, c->staging, per_block, ncclFloat, c->comm, s));
-  unpack_blocks_kernel<<<sm_count() * 8, 256, 0, s>>>(c->staging, c_full, ldc_full, pr, pc, m_loc, n_loc);
-  return check_launch("unpack_blocks");
+  rc = guda_dgemm(0, 0, m_loc, n_loc, k, alpha, a_panel, lda, b_panel, ldb, beta, c_block, ldc_block, stream);
+  if (rc) return rc;
+  if (!c_full) return GUDA_OK;
+  return gather_blocks_nccl<double, double2>(c, pr, pc, m_loc, n_loc, n_total, c_block, c_full, ldc_full, ncclDouble, s);
 }
 
 int guda_sgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, float alpha, const float* a_panel, int lda,
                        const float* b_panel, int ldb, float* c_block, int ldc_block, float* c_full, int ldc_full, guda_stream_t stream) {
   return sgemm_sharded_impl(comm, pr, pc, m_total, n_total, k, alpha, a_panel, lda, b_panel, ldb, 0.0f, c_block, ldc_block, c_full, ldc_full, stream);
+}
+
+int guda_dgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, double alpha, const double* a_panel, int lda,
+                       const double* b_panel, int ldb, double* c_block, int ldc_block, double* c_full, int ldc_full, guda_stream_t stream) {
+  return dgemm_sharded_impl(comm, pr, pc, m_total, n_total, k, alpha, a_panel, lda, b_panel, ldb, 0.0, c_block, ldc_block, c_full, ldc_full, stream);
 }
 
 // The same step from HOST panels (each rank's A row panel and B column panel in pinned host memory) to a HOST C block: the uploads
@@ -322,7 +402,9 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
       bool fused = false;
       float* peers[GUDA_MAX_SCATTER_RANKS];
       if (c_full && ldc_full >= n_total && c->gather_mode == GUDA_GATHER_P2P && !c->p2p_failed && sgemm_mode() == GUDA_SGEMM_EXACT) {
-        if ((rc = resolve_peers(c, c_full, s, peers, &fused))) break;
+        void* peers_v[GUDA_MAX_SCATTER_RANKS];
+        if ((rc = resolve_peers(c, c_full, s, peers_v, &fused))) break;
+        for (int i = 0; i < c->nranks; i++) peers[i] = static_cast<float*>(peers_v[i]);
         if (!fused) c->p2p_failed = true;
       }
       if (!fused) {
@@ -379,6 +461,13 @@ int guda_comm_get_gather_mode(guda_comm_t comm, int* mode_in_effect) {
   Comm* c = reinterpret_cast<Comm*>(comm);
   *mode_in_effect = (c->gather_mode == GUDA_GATHER_P2P && !c->p2p_failed) ? GUDA_GATHER_P2P : GUDA_GATHER_NCCL;
   return GUDA_OK;
+}
+
+// AXPY over a vector split into contiguous chunks, one per rank (math.go:39): elementwise, so no collective at all; the
+// entry point exists so that the sharded Level-1 pair has the same shape (and the same argument checks) as the DOT below.
+int guda_saxpy_sharded(guda_comm_t comm, int n_local, float alpha, const float* x, float* y, guda_stream_t stream) {
+  if (!comm) return set_error(GUDA_ERR_INVALID_ARG, "saxpy_sharded: null communicator");
+  return guda_saxpy(n_local, alpha, x, 1, y, 1, stream);
 }
 
 int guda_sdot_sharded(guda_comm_t comm, int n_local, const float* x, const float* y, float* host_result, guda_stream_t stream) {

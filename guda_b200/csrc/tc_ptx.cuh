@@ -42,6 +42,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// non-blocking test of a phase parity.  No "memory" clobber on purpose: it is issued in the middle of a stage's arithmetic and must
+// not pin the surrounding shared-memory loads; a caller that sees 0 must still go through mbar_wait (which has the clobber)
+// and a caller that sees 1 reads the protected data only after a branch on this result.
+__device__ __forceinline__ uint32_t mbar_test_wait_nb(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, P1;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity));
+  return ok;
+}
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

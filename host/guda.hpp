@@ -295,4 +295,72 @@ inline void Conv2DDirect(const DevicePtr& input, const DevicePtr& kernel, const 
   check(guda_conv2d_direct(f32(input), f32(kernel), f32(bias), f32(output), &cp, nullptr), "Conv2DDirect");
 }
 
+// ---- tolerance framework (tolerance.go:10-191, tolerance_arch.go:8-127, numerical_parity.go:124-141) + the sm_100a entry ----
+struct ToleranceConfig {                                       // tolerance.go:10-26; the last four fields belong to the sm_100a entry
+  float AbsTol = 0, RelTol = 0; int ULPTol = 0; bool CheckNaN = false, CheckInf = false;
+  float KScale = 0; int HalfULPTol = 0; double Abs64 = 0, Rel64 = 0;
+  guda_tolerance_t c() const { return guda_tolerance_t{AbsTol, RelTol, ULPTol, CheckNaN, CheckInf, KScale, HalfULPTol, Abs64, Rel64}; }
+  static ToleranceConfig from(const guda_tolerance_t& t) {
+    ToleranceConfig r; r.AbsTol = t.abs_tol; r.RelTol = t.rel_tol; r.ULPTol = t.ulp_tol; r.CheckNaN = t.check_nan != 0; r.CheckInf = t.check_inf != 0;
+    r.KScale = t.k_scale; r.HalfULPTol = t.half_ulp_tol; r.Abs64 = t.abs64; r.Rel64 = t.rel64; return r;
+  }
+};
+inline ToleranceConfig tolerance_preset(int which) { guda_tolerance_t t; check(guda_tolerance_preset(which, &t), "TolerancePreset"); return ToleranceConfig::from(t); }
+inline ToleranceConfig DefaultTolerance() { return tolerance_preset(0); }      // tolerance.go:28-36
+inline ToleranceConfig StrictTolerance() { return tolerance_preset(1); }       // tolerance.go:39-45
+inline ToleranceConfig RelaxedTolerance() { return tolerance_preset(2); }      // tolerance.go:48-54
+inline ToleranceConfig mergeTolerances(const ToleranceConfig& base, const ToleranceConfig& over) {                  // tolerance_arch.go:41-57
+  guda_tolerance_t b = base.c(), o = over.c(), out; check(guda_merge_tolerances(&b, &o, &out), "mergeTolerances"); return ToleranceConfig::from(out);
+}
+// tolerance_arch.go:116-127; arch "" = the device that computed the results (sm_100a), or "amd64" / "arm64" / "generic"
+inline ToleranceConfig GetOperationTolerance(const std::string& operation, const std::string& arch = "") {
+  guda_tolerance_t t; check(guda_get_operation_tolerance(operation.c_str(), arch.empty() ? nullptr : arch.c_str(), &t), "GetOperationTolerance");
+  return ToleranceConfig::from(t);
+}
+inline int Float32ULPDiff(float a, float b) {                                  // tolerance.go:100-118
+  uint32_t x, y; std::memcpy(&x, &a, 4); std::memcpy(&y, &b, 4);
+  if ((x ^ y) >> 31) return 0x7FFFFFFF;
+  return static_cast<int>(x > y ? x - y : y - x);
+}
+inline bool Float32NearEqual(float a, float b, const ToleranceConfig& tol) {   // tolerance.go:57-97
+  if (tol.CheckNaN && a != a && b != b) return true;
+  const bool ia = a > 3.4028234e38f || a < -3.4028234e38f, ib = b > 3.4028234e38f || b < -3.4028234e38f;
+  if (tol.CheckInf && ia && ib && ((a > 0) == (b > 0))) return true;
+  if (a == b) return true;
+  const float d32 = a - b;
+  const double gap = d32 < 0 ? -(double)d32 : (double)d32;
+  const double aa = a < 0 ? -(double)a : (double)a, bb = b < 0 ? -(double)b : (double)b;
+  if (gap <= (double)tol.AbsTol || gap <= (aa > bb ? aa : bb) * (double)tol.RelTol) return true;
+  return tol.ULPTol > 0 && Float32ULPDiff(a, b) <= tol.ULPTol;
+}
+struct VerificationResult {                                                    // tolerance.go:121-128
+  float MaxAbsError = 0, MaxRelError = 0; int MaxULPError = 0; long long NumErrors = 0, TotalItems = 0, FirstError = -1;
+  bool IsAcceptable(const ToleranceConfig& tol) const {                        // tolerance.go:177-182
+    return NumErrors == 0 || (MaxAbsError <= tol.AbsTol && MaxRelError <= tol.RelTol && MaxULPError <= tol.ULPTol);
+  }
+};
+// tolerance.go:131-174 over two device buffers of n floats (one streaming pass on the GPU)
+inline VerificationResult VerifyFloat32Array(const DevicePtr& expected, const DevicePtr& actual, long long n, const ToleranceConfig& tol) {
+  guda_tolerance_t t = tol.c(); guda_verify_result_t r;
+  check(guda_verify_f32(static_cast<const float*>(expected.ptr), static_cast<const float*>(actual.ptr), n, &t, &r, nullptr), "VerifyFloat32Array");
+  VerificationResult v; v.MaxAbsError = r.max_abs_error; v.MaxRelError = r.max_rel_error; v.MaxULPError = r.max_ulp_error;
+  v.NumErrors = r.num_errors; v.TotalItems = r.total_items; v.FirstError = r.first_error; return v;
+}
+
+// ---- kernel-launch surface (guda.go:66-89,184-196,310-339): host closures cannot run on the device; the entry points exist and refuse ----
+struct Dim3 { int X = 1, Y = 1, Z = 1; int Size() const { return X * Y * Z; } };
+struct ThreadID {
+  Dim3 BlockIdx, ThreadIdx, BlockDim, GridDim;
+  int Global() const { return BlockIdx.X * BlockDim.X + ThreadIdx.X; }
+  int GlobalX() const { return Global(); }
+  int GlobalY() const { return BlockIdx.Y * BlockDim.Y + ThreadIdx.Y; }
+  int GlobalZ() const { return BlockIdx.Z * BlockDim.Z + ThreadIdx.Z; }
+};
+template <typename Kernel, typename... Args>
+inline void Launch(Kernel&&, const Dim3& grid, const Dim3& block, Args&&...) {
+  if (grid.Size() <= 0 || block.Size() <= 0) throw GUDAError(ErrorType::InvalidArg, "Launch", "grid and block dimensions must be positive");
+  throw GUDAError(ErrorType::NotImplemented, "Launch", "host closures cannot run on the device: use the device-kernel entry points "
+                  "(Add/Multiply/ReLU/Sigmoid, FusedKernel, LinearReLU, GELU, GEMMBFloat16/GEMMFloat16, the reductions)");
+}
+
 }  // namespace guda

@@ -148,6 +148,37 @@ int main() {
     EXPECT(ArgMax(d, 0) == -1 && Max(d, 0) == -INFINITY && Min(d, 0) == INFINITY && Sum(d, 0) == 0.0f, "empty reductions");
     Free(d);
   }
+  // ---- tolerance framework (tolerance_test.go:8-240, tolerance_arch_test.go:27-57) through the C++ mirror, device verification vs the oracle
+  {
+    ToleranceConfig d = DefaultTolerance(), g = GetOperationTolerance("gemm"), ga = GetOperationTolerance("gemm", "arm64");
+    EXPECT(d.AbsTol == 1e-7f && d.RelTol == 1e-5f && d.ULPTol == 4 && d.CheckNaN && d.CheckInf, "DefaultTolerance");
+    EXPECT(g.AbsTol == 1e-6f && g.ULPTol == 4 && g.KScale == 2.0f && ga.ULPTol == 16 && ga.KScale == 0.0f, "GetOperationTolerance(gemm) sm_100a / arm64");
+    ToleranceConfig base; base.AbsTol = 1e-7f; base.RelTol = 1e-6f; base.ULPTol = 2; base.CheckNaN = true;
+    ToleranceConfig over; over.RelTol = 1e-4f; over.ULPTol = 16;
+    ToleranceConfig m = mergeTolerances(base, over);
+    EXPECT(m.AbsTol == 1e-7f && m.RelTol == 1e-4f && m.ULPTol == 16 && m.CheckNaN && !m.CheckInf, "merge keeps non-overridden fields");
+    EXPECT(Float32NearEqual(1e-8f, 2e-8f, d) && !Float32NearEqual(1e-6f, 2e-6f, d) && Float32NearEqual(0.0f, -0.0f, d), "Float32NearEqual");
+    EXPECT(Float32ULPDiff(1.0f, -1.0f) == 0x7FFFFFFF && Float32ULPDiff(1.0f, std::nextafterf(1.0f, 2.0f)) == 1, "Float32ULPDiff");
+    const size_t n = 100003;
+    auto e = uniform(n, 77), a = e;
+    for (size_t i = 0; i < n; i += 97) a[i] *= 1.0f + 3e-4f;
+    a[5] = -a[5]; e[9] = std::nanf(""); a[9] = std::nanf("");
+    DevicePtr de = Malloc(n * 4), da = Malloc(n * 4);
+    de.CopyFrom(e); da.CopyFrom(a);
+    VerificationResult v = VerifyFloat32Array(de, da, (long long)n, g);
+    orc_tol_t ot{g.AbsTol, g.RelTol, g.ULPTol, 1, 1};
+    orc_verify_t ov;
+    orc_verify_f32(e.data(), a.data(), n, &ot, &ov);
+    EXPECT(v.NumErrors == ov.num_errors && v.FirstError == ov.first_error && v.MaxULPError == ov.max_ulp && v.TotalItems == (long long)n &&
+           std::memcmp(&v.MaxAbsError, &ov.max_abs, 4) == 0 && std::memcmp(&v.MaxRelError, &ov.max_rel, 4) == 0 && v.NumErrors > 0,
+           "VerifyFloat32Array on the device == oracle: %lld errors", v.NumErrors);
+    EXPECT(!v.IsAcceptable(g), "IsAcceptable");
+    Free(de); Free(da);
+    bool refused = false;
+    try { Launch([](ThreadID) {}, Dim3{4, 1, 1}, Dim3{64, 1, 1}); } catch (const GUDAError& err) { refused = err.type == ErrorType::NotImplemented; }
+    ThreadID t{Dim3{3, 2, 1}, Dim3{5, 1, 0}, Dim3{64, 4, 1}, Dim3{8, 8, 1}};
+    EXPECT(refused && t.Global() == 197 && t.GlobalY() == 9 && (Dim3{4, 2, 3}).Size() == 24, "Launch surface");
+  }
   std::printf(failures ? "host_test: %d FAILED\n" : "host_test: all checks passed\n", failures);
   return failures ? 1 : 0;
 }

@@ -130,6 +130,11 @@ int guda_get_dgemm_mode(int* mode);
 int guda_sgemm_scatter(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* a, int lda, const float* b, int ldb,
                        float beta, float* c, int ldc, float* const* host_dests, int ndest, int ld_dest, int row0, int col0,
                        guda_stream_t stream);
+/* DGEMM twin (NN form, m and n multiples of 4, 32-byte aligned C rows and destinations): the FP64 tensor-pipe kernel's epilogue
+ * performs the same peer stores; the kernel behind guda_dgemm_sharded. */
+int guda_dgemm_scatter(int trans_a, int trans_b, int m, int n, int k, double alpha, const double* a, int lda, const double* b, int ldb,
+                       double beta, double* c, int ldc, double* const* host_dests, int ndest, int ld_dest, int row0, int col0,
+                       guda_stream_t stream);
 /* bfloat16.go:104 GEMMBFloat16 (trans flags ignored by the reference -> must be 0 here), float16.go:201 GEMMFloat16.
  * 16-bit storage, fp32 accumulation; a/b/c are uint16 bit patterns. */
 int guda_gemm_bf16(int trans_a, int trans_b, int m, int n, int k, float alpha, const uint16_t* a, int lda,
@@ -274,6 +279,39 @@ int guda_fill_uniform_f64(double* dst, size_t rows, size_t cols, size_t ld, uint
 /* ---- measured denominators for rooflines (bench.py): kind 0 = FP32 FFMA TFLOP/s, 1 = FP64 DFMA TFLOP/s,
  * 2 = 128-bit streaming copy GB/s (read+write bytes), 3 = FP64 tensor pipe (DMMA m8n8k4) TFLOP/s,
  * 4 = packed fp32 FMA (fma.rn.f32x2 / FFMA2) TFLOP/s ---- */
+/* ---- tolerance framework (tolerance.go:10-191, tolerance_arch.go:8-127, numerical_parity.go:103-141) ------------------------------
+ * ToleranceConfig with the additions the "sm_100a" architecture entry needs (zero = not applicable / keep the base value):
+ *   k_scale       an element also passes if |delta| <= k_scale * K * u * sum_l |a_il||b_lj| (u = unit roundoff of the accumulation type)
+ *   half_ulp_tol  bf16 / fp16 outputs: distance in ULPs of the 16-bit format
+ *   abs64, rel64  fp64 results (blas/testblas/common.go:22-38 dTolEqual) */
+typedef struct guda_tolerance {
+  float abs_tol, rel_tol;
+  int ulp_tol;
+  int check_nan, check_inf;
+  float k_scale;
+  int half_ulp_tol;
+  double abs64, rel64;
+} guda_tolerance_t;
+/* tolerance.go:121-128 VerificationResult */
+typedef struct guda_verify_result {
+  float max_abs_error, max_rel_error;
+  int max_ulp_error;
+  long long num_errors, total_items, first_error;      /* first_error = -1 if none */
+} guda_verify_result_t;
+/* 0 DefaultTolerance, 1 StrictTolerance, 2 RelaxedTolerance (tolerance.go:28-54) */
+int guda_tolerance_preset(int preset, guda_tolerance_t* out);
+/* tolerance_arch.go:41-57 mergeTolerances: non-zero override fields replace the base */
+int guda_merge_tolerances(const guda_tolerance_t* base, const guda_tolerance_t* override_, guda_tolerance_t* out);
+/* tolerance_arch.go:116-127 GetOperationTolerance.  operation: "gemm", "conv2d", "reduce_sum", "softmax" as in the reference, plus
+ * "dot", "dgemm", "gemm_3xtf32", "gemm_bf16", "gemm_f16", "gemm_bf16_fused"; anything else -> DefaultTolerance.
+ * arch: NULL or "sm_100a" (the device that produced the results), "amd64", "arm64", "generic" (the reference's GOARCH cases). */
+int guda_get_operation_tolerance(const char* operation, const char* arch, guda_tolerance_t* out);
+/* numerical_parity.go:132-141 StandardTolerances[operation]; NotImplemented for a name the map does not hold */
+int guda_standard_tolerance(const char* operation, float* abs_tol, float* rel_tol, int* ulp_tol);
+/* tolerance.go:131-174 VerifyFloat32Array on two DEVICE arrays (one HBM-streaming pass); blocks, result in host memory */
+int guda_verify_f32(const float* expected, const float* actual, long long n, const guda_tolerance_t* tol,
+                    guda_verify_result_t* host_result, guda_stream_t stream);
+
 int guda_microbench_peak(int kind, int reps, double* value);
 /* SM cycles per warp-level shared-memory load instruction for a lane -> chunk-index pattern (width 4 / 8 / 16 bytes):
  * the wavefront cost model behind the lane layouts of the SIMT GEMM kernels. */
@@ -307,6 +345,13 @@ enum { GUDA_GATHER_P2P = 0, GUDA_GATHER_NCCL = 1 };
 int guda_comm_set_gather_mode(guda_comm_t comm, int mode);
 int guda_comm_get_gather_mode(guda_comm_t comm, int* mode_in_effect);
 int guda_sdot_sharded(guda_comm_t comm, int n_local, const float* x, const float* y, float* host_result, guda_stream_t stream);
+/* AXPY on this rank's contiguous chunk of a sharded vector (math.go:39): elementwise, no collective. */
+int guda_saxpy_sharded(guda_comm_t comm, int n_local, float alpha, const float* x, float* y, guda_stream_t stream);
+/* DGEMM twin of guda_sgemm_sharded (compute/dgemm.go:25): 2-D block partition, full K per rank (bit-identical to one GPU),
+ * C gathered on every rank -- by the DMMA kernel's peer-store epilogue (default) or ncclAllGather. */
+int guda_dgemm_sharded(guda_comm_t comm, int pr, int pc, int m_total, int n_total, int k, double alpha,
+                       const double* a_panel, int lda, const double* b_panel, int ldb,
+                       double* c_block, int ldc_block, double* c_full, int ldc_full, guda_stream_t stream);
 
 #ifdef __cplusplus
 }

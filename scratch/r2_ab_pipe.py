@@ -26,7 +26,7 @@ if what in ("all", "lds"):
             g.capi.check(L.guda_microbench_lds(w, idx, 2000, C.byref(v)), "lds")
             print("LDS.%d pattern %-22s %.2f cycles per warp instruction" % (w * 8, name, v.value), flush=True)
 
-CFGS = list(range(0, 15))
+CFGS = [int(v) for v in os.environ.get("PIPE_CFGS", ",".join(str(i) for i in range(15))).split(",")]
 
 if what in ("all", "check"):
     # bit-equality against the register-staged kernel (cfg 0), incl. alpha != 1, beta != 0, zeros in A, TN form

@@ -152,8 +152,10 @@ def test_dot_within_reduce_tolerance(g, O, n):
     got = g.DOT(dx, dy, n)
     want = O.sdot(n, x, 1, y, 1)
     exact = float(np.dot(x.astype(np.float64), y.astype(np.float64)))
-    bound = 2.0 * n * 2.0 ** -24 * float(np.dot(np.abs(x).astype(np.float64), np.abs(y).astype(np.float64)))
-    assert O.near_equal(float(want), float(got), TOL_REDUCE) or abs(float(got) - float(want)) <= bound
+    # ReduceArchTolerance, or -- when the reference's own order is the less accurate one and sits near that bound (n = 2^22: its
+    # error against fp64 is 0.76 of the bound) -- no further from the oracle than twice the oracle's own distance to the fp64 value
+    assert O.near_equal(float(want), float(got), TOL_REDUCE) or \
+        abs(float(got) - float(want)) <= 2.0 * abs(float(want) - exact) + 4.0 * 2.0 ** -24 * abs(exact)
     assert abs(float(got) - exact) <= abs(float(want) - exact) + 1e-6 * max(1.0, abs(exact))   # at least as accurate as the reference order
     # deterministic
     assert g.DOT(dx, dy, n) == got

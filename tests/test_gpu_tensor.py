@@ -30,17 +30,25 @@ def _bf16_vals(O, n, seed, lo=-1.0, hi=1.0):
     return O.to_bf16_fast(O.uniform_f32(n, seed, lo, hi))
 
 
-def _ulp16_check(got_f, want_f, mant_bits, order_bound=0.0):
-    """1 ULP of the 16-bit format, plus the fp32 summation-order bound (matters only for sums that cancel to ~0)."""
-    ulp = np.maximum(np.abs(want_f), 2.0 ** -14) * 2.0 ** -mant_bits
+def _tol(op):
+    """The sm_100a entry of the tolerance framework (guda.GetOperationTolerance(op)): HalfULPTol / KScale are the stated bounds."""
+    from guda_b200 import tolerance as T
+    return T.GetOperationTolerance(op)
+
+
+def _ulp16_check(got_f, want_f, mant_bits, order_bound=0.0, op="gemm_bf16"):
+    """HalfULPTol ULPs of the 16-bit format, plus the fp32 summation-order bound (matters only for sums that cancel to ~0)."""
+    from guda_b200 import tolerance as T
+    ulp = T.half_ulp_bound(_tol(op), want_f, mant_bits, -14)
     bad = np.abs(got_f.astype(np.float64) - want_f.astype(np.float64)) > ulp * 1.001 + order_bound
     return int(bad.sum()), float(np.mean(got_f == want_f))
 
 
-def _order_bound(O, a16, lda, b16, ldb, m, n, k, alpha, beta, c16, conv):
+def _order_bound(O, a16, lda, b16, ldb, m, n, k, alpha, beta, c16, conv, op="gemm_bf16"):
+    from guda_b200 import tolerance as T
     A = np.abs(conv(a16).reshape(-1)[:m * lda].reshape(m, lda)[:, :k].astype(np.float64))
     B = np.abs(conv(b16).reshape(-1)[:k * ldb].reshape(k, ldb)[:, :n].astype(np.float64))
-    return (2.0 * k * 2.0 ** -24 * (abs(alpha) * (A @ B) + abs(beta) * np.abs(conv(c16).reshape(m, n).astype(np.float64)))).reshape(-1)
+    return T.k_scaled_bound(_tol(op), k, abs(alpha) * (A @ B), 2.0 ** -24, abs(beta) * np.abs(conv(c16).reshape(m, n).astype(np.float64))).reshape(-1)
 
 
 @pytest.mark.parametrize("m,n,k,lda_pad,ldb_pad", [(128, 256, 64, 0, 0), (128, 256, 256, 0, 0), (256, 512, 192, 0, 0),
@@ -69,7 +77,7 @@ def test_gemm_f16_tensor_route(g, O):
     got = dc.UInt16().view(np.float16).astype(np.float32)
     want = O.gemm_f16(0, 0, m, n, k, 1.5, a, k, b, n, 0.5, c0.copy(), n, threads=8).view(np.float16).astype(np.float32)
     f16 = lambda h: np.ascontiguousarray(h).view(np.float16).astype(np.float32)
-    nbad, frac_equal = _ulp16_check(got, want, 10, _order_bound(O, a, k, b, n, m, n, k, 1.5, 0.5, c0, f16))
+    nbad, frac_equal = _ulp16_check(got, want, 10, _order_bound(O, a, k, b, n, m, n, k, 1.5, 0.5, c0, f16, "gemm_f16"), "gemm_f16")
     assert nbad == 0, (nbad, frac_equal)
     assert frac_equal > 0.9
     g.Free(da); g.Free(db); g.Free(dc)
@@ -91,8 +99,8 @@ def test_fused_bf16_bias_act_tensor_route(g, O, act):
     v = (pre + bias).astype(np.float32)
     want = np.maximum(v, 0) if act == "relu" else O.gelu(v)
     want = O.bf16_to_f32(O.to_bf16_fast(want)).reshape(-1)
-    ulp = np.maximum(np.abs(want), 2.0 ** -6) * 2.0 ** -7
-    assert np.all(np.abs(got - want) <= 2.0 * ulp)
+    from guda_b200 import tolerance as T
+    assert np.all(np.abs(got - want) <= T.half_ulp_bound(_tol("gemm_bf16_fused"), want, 7, -6))
     for p in (da, db, dbias, dc):
         g.Free(p)
 
@@ -131,7 +139,8 @@ def test_sgemm_3xtf32_within_stated_bound(g, O, m, n, k):
     want = O.sgemm(0, 0, m, n, k, 1.5, a, k, b, n, 0.5, c0.copy(), n, threads=8).astype(np.float64)
     A, B = a.reshape(m, k).astype(np.float64), b.reshape(k, n).astype(np.float64)
     truth = 1.5 * (A @ B) + 0.5 * c0.reshape(m, n)
-    bound = 8.0 * k * 2.0 ** -24 * (1.5 * (np.abs(A) @ np.abs(B)) + 0.5 * np.abs(c0.reshape(m, n)))
+    from guda_b200 import tolerance as T
+    bound = T.k_scaled_bound(_tol("gemm_3xtf32"), k, 1.5 * (np.abs(A) @ np.abs(B)), 2.0 ** -24, 0.5 * np.abs(c0.reshape(m, n)))
     assert np.all(np.abs(got.reshape(m, n) - want.reshape(m, n)) <= bound)
     err_tc = np.max(np.abs(got.reshape(m, n) - truth)); err_ref = np.max(np.abs(want.reshape(m, n) - truth))
     print("3xTF32 max abs err vs fp64: %.3e   reference FMA chain: %.3e" % (err_tc, err_ref))

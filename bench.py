@@ -120,6 +120,55 @@ def cpu_sgemm_sample(steps, warmup, threads):
     return 2.0 * n ** 3 / dt / 1e12, dt
 
 
+def _timed(fn, reps=2):
+    fn()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    return (time.perf_counter() - t0) / reps
+
+
+def cpu_suite_baselines(cores):
+    """The reference's CPU path (oracle port) beside each suite config, threaded the way the reference threads it
+    (BASELINE.md section 3): SGEMM over all cores (compute/sgemm.go:165-264), AXPY / DOT / DGEMM on ONE thread
+    (compute/level1float32.go:247-249, compute/dgemm.go:122).  Bounded: about 10 s in total."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle as O
+    out = {}
+    n = 1024
+    a, b, c = O.uniform_f32(n * n, 1), O.uniform_f32(n * n, 2), np.zeros(n * n, np.float32)
+    dt = _timed(lambda: O.sgemm(0, 0, n, n, n, 1.0, a, n, b, n, 0.0, c, n, threads=cores), 3)
+    out["sgemm_1024"] = {"value": 2.0 * n ** 3 / dt / 1e12, "unit": "TFLOP/s", "cores": cores, "kind": "port",
+                         "sample": "SGEMM 1024^3 fp32 alpha=1 beta=0, full size, one task per 64x64 C block over all cores, %.1f ms" % (dt * 1e3)}
+    nv = 1 << 24
+    x, y = O.uniform_f32(nv, 3), O.uniform_f32(nv, 4)
+    dt = _timed(lambda: O.saxpy(nv, 2.5, x, 1, y, 1), 3)
+    chunks = [(i * (nv // cores), (i + 1) * (nv // cores) if i < cores - 1 else nv) for i in range(cores)]
+    with ThreadPoolExecutor(cores) as ex:
+        dta = _timed(lambda: list(ex.map(lambda ch: O.saxpy(ch[1] - ch[0], 2.5, x[ch[0]:ch[1]], 1, y[ch[0]:ch[1]], 1), chunks)), 3)
+        dtd_all = _timed(lambda: sum(ex.map(lambda ch: float(O.sdot(ch[1] - ch[0], x[ch[0]:ch[1]], 1, y[ch[0]:ch[1]], 1)), chunks)), 3)
+    out["saxpy_16M"] = {"value": 12.0 * nv / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                        "sample": "SAXPY n=2^24 alpha=2.5 full size, ONE thread as the reference (compute/level1float32.go:247-249), %.1f ms" % (dt * 1e3),
+                        "all_cores_not_the_reference": {"value": 12.0 * nv / dta / 1e9, "unit": "GB/s", "cores": cores}}
+    dt = _timed(lambda: O.sdot(nv, x, 1, y, 1), 3)
+    out["sdot_16M"] = {"value": 8.0 * nv / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                       "sample": "SDOT n=2^24 full size, ONE thread as the reference (compute/level1float32_sdot.go:18), %.1f ms" % (dt * 1e3),
+                       "all_cores_not_the_reference": {"value": 8.0 * nv / dtd_all / 1e9, "unit": "GB/s", "cores": cores}}
+    M, K, N = 1024, 4096, 16384
+    a, b, bias, c = O.uniform_f32(M * K, 5), O.uniform_f32(K * N, 6, -0.05, 0.05), O.uniform_f32(N, 7), np.zeros(M * N, np.float32)
+    dt = _timed(lambda: O.fused_gemm_bias_gelu(0, 0, M, N, K, 1.0, a, K, b, N, 0.0, c, N, bias, threads=cores), 1)
+    out["fused_gemm_bias_gelu_f32_8192x4096x16384"] = {
+        "value": 2.0 * M * N * K / dt / 1e12, "unit": "TFLOP/s", "cores": cores, "kind": "port",
+        "sample": "M reduced 8192 -> 1024 (K=4096, N=16384 kept): GEMM over all cores, then the reference's second bias+GELU pass "
+                  "(fused_gelu.go:96-137), %.2f s" % dt}
+    n = 2048
+    ad, bd, cd = O.uniform_f64(n * n, 8), O.uniform_f64(n * n, 9), np.zeros(n * n)
+    dt = _timed(lambda: O.dgemm(0, 0, n, n, n, 1.0, ad, n, bd, n, 0.0, cd, n), 1)
+    out["dgemm_16384"] = {"value": 2.0 * n ** 3 / dt / 1e12, "unit": "TFLOP/s", "cores": 1, "kind": "port",
+                          "sample": "N reduced 16384 -> 2048, ONE thread as the reference (compute/dgemm.go:122 -> dgemm_fix.go:7-11), %.2f s" % dt}
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -441,6 +490,180 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
 from guda_b200.sharding import grid_for, block_extents  # noqa: E402  (integer geometry only; no device code)
 
 
+def _panel_host(g, rows, cols, seed, row0, col0, full_cols, dtype=np.float32):
+    """rows x cols window at (row0, col0) of the seeded full matrix: regenerated on the device (counter-based RNG) and copied down."""
+    it = np.dtype(dtype).itemsize
+    p = g.Malloc(rows * cols * it)
+    g.FillUniform(p, rows, cols, cols, seed, row0=row0, col0=col0, full_cols=full_cols, dtype=dtype)
+    g.Synchronize()
+    h = (p.Float32() if dtype == np.float32 else p.Float64())[:rows * cols].copy()
+    g.Free(p)
+    return h
+
+
+def parity_blocks(g, read_block, n, blocks, seed_a, seed_b, dtype=np.float32):
+    """SURVEY.md 8(d) parity at scale: a C element is ONE sequential-k chain over a row of A and a column of B, and the inputs come
+    from a counter-based generator, so the 4 x n / n x 4 panels behind any 4 x 4 block of C can be regenerated and handed to the
+    oracle (outside every timed region).  Returns the number of blocks that are bit-identical to the oracle's chains."""
+    from oracle import oracle as O
+    good = 0
+    for i0, j0 in blocks:
+        ar = _panel_host(g, 4, n, seed_a, i0, 0, n, dtype)
+        bc = _panel_host(g, n, 4, seed_b, 0, j0, n, dtype)
+        if dtype == np.float32:
+            want = O.sgemm(0, 0, 4, 4, n, 1.0, ar, n, bc, 4, 0.0, np.zeros(16, np.float32), 4).reshape(4, 4)
+        else:
+            want = O.dgemm(0, 0, 4, 4, n, 1.0, ar, n, bc, 4, 0.0, np.zeros(16), 4).reshape(4, 4)
+        got = read_block(i0, j0)
+        good += int(np.array_equal(got.view(np.uint32 if dtype == np.float32 else np.uint64), want.view(np.uint32 if dtype == np.float32 else np.uint64))
+                    and bool(np.all(np.isfinite(got))))
+    return good
+
+
+def _device_block_reader(g, c, ldc, row_off, col_off, dtype=np.float32):
+    it = np.dtype(dtype).itemsize
+
+    def read(i0, j0):
+        out = np.empty((4, 4), dtype)
+        for i in range(4):
+            row = g.DevicePtr(c.ptr + ((i0 - row_off + i) * ldc + (j0 - col_off)) * it, 4 * it)
+            out[i] = (row.Float32() if dtype == np.float32 else row.Float64())[:4]
+        return out
+    return read
+
+
+def sample_blocks(n, pr, pc, rank, world):
+    """>= 6 blocks of the gathered C: the two far corners, a block owned by ANOTHER rank, one straddling the seam of four ranks'
+    blocks (or the centre), one straddling a 64 x 128 tile corner, one at an unaligned position."""
+    m_loc, n_loc = n // pr, n // pc
+    other = (rank + 1) % world
+    orow, ocol = (other // pc) * m_loc, (other % pc) * n_loc
+    return [(0, 0), (n - 4, n - 4), (orow + m_loc // 2 + 1, ocol + n_loc // 2 + 3), (m_loc - 2, n_loc - 2) if world > 1 else (n // 2 - 2, n // 2 - 2),
+            (62, 126), ((40001 * 7) % (n - 4), (50003 * 3) % (n - 4))]
+
+
+def sharded_secondary(dev, comm, dist, world, rank, pr, pc, peaks, dmma_peak, barrier, max_over_ranks, min_over_ranks):
+    """N > 1 only: the other sharded forms of SURVEY.md 8(e), each timed on the device (max over ranks) and checked.
+      dgemm_16384     DGEMM 16384^3 (BASELINE configs[3]) 2-D partitioned, C gathered by the DMMA kernel's peer-store epilogue
+      sdot_sharded    per-rank DOT over 2^24 resident elements + one-float all-reduce (weak scaling: n = 2^24 * N)
+      saxpy_sharded   per-rank AXPY over 2^24 resident elements, no collective"""
+    import torch
+    from oracle import oracle as O
+    from guda_b200 import tolerance as T
+    g, L = dev.g, dev.L
+    out = {}
+    ok = True
+    # ---- DGEMM 16384^3
+    n = 16384
+    row0, m_loc, col0, n_loc = block_extents(rank, pr, pc, n, n)
+    a_p, b_p, c_b, c_f = g.Malloc(m_loc * n * 8), g.Malloc(n * n_loc * 8), g.Malloc(m_loc * n_loc * 8), g.Malloc(n * n * 8)
+    g.FillUniform(a_p, m_loc, n, n, seed=21, row0=row0, col0=0, full_cols=n, dtype=np.float64)
+    g.FillUniform(b_p, n, n_loc, n_loc, seed=22, row0=0, col0=col0, full_cols=n, dtype=np.float64)
+    g.Memset(c_f, 0xFF, n * n * 8)
+
+    def dstep():
+        g.capi.check(L.guda_dgemm_sharded(comm, pr, pc, n, n, n, 1.0, a_p.ptr, n, b_p.ptr, n_loc, c_b.ptr, n_loc, c_f.ptr, n, None), "DgemmSharded")
+    dstep(); dstep()
+    barrier()
+    ms = max_over_ranks(dev.time_ms(dstep, 3))
+    barrier()
+    good = parity_blocks(g, _device_block_reader(g, c_f, n, 0, 0, np.float64), n, sample_blocks(n, pr, pc, rank, world), 21, 22, np.float64)
+    good = min_over_ranks(good)
+    kms = dev.time_ms(lambda: L.guda_dgemm(0, 0, m_loc, n_loc, n, 1.0, a_p.ptr, n, b_p.ptr, n_loc, 0.0, c_b.ptr, n_loc, None), 2)
+    ktf = 2.0 * m_loc * n_loc * n / (kms * 1e-3) / 1e12
+    out["dgemm_16384"] = {"value": 2.0 * n ** 3 / (ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": ms, "scaling": "strong",
+                          "workload": "DGEMM 16384^3 fp64 NN alpha=1 beta=0 (BASELINE configs[3]), %dx%d block partition, C gathered on every rank "
+                                      "by the FP64 tensor-pipe kernel's peer-store epilogue" % (pr, pc),
+                          "roofline": {"bound": "tensor", "pipe": "fp64 tensor (DMMA)", "achieved": ktf, "peak": dmma_peak, "unit": "TFLOP/s",
+                                       "frac": ktf / dmma_peak if dmma_peak else None, "what": "this rank's block GEMM alone, per GPU"},
+                          "parity": {"blocks": 6, "bit_identical": bool(good == 6), "where": "gathered C on every rank vs the oracle's chains"}}
+    ok = ok and good == 6
+    for p in (a_p, b_p, c_b, c_f):
+        g.Free(p)
+    L.guda_pool_trim()
+    # ---- sharded Level-1: n_local = 2^24 per rank, 4 rotating pairs (512 MiB > L2)
+    nl = 1 << 24
+    pairs = []
+    for i in range(4):
+        x, y = g.Malloc(nl * 4), g.Malloc(nl * 4)
+        g.FillUniform(x, 1, nl, nl, 300 + i, row0=0, col0=rank * nl, full_cols=nl * world)
+        g.FillUniform(y, 1, nl, nl, 400 + i, row0=0, col0=rank * nl, full_cols=nl * world)
+        pairs.append((x, y))
+    it = [0]
+    res = C.c_float(0)
+
+    def sdot():
+        x, y = pairs[it[0] % 4]; it[0] += 1
+        g.capi.check(L.guda_sdot_sharded(comm, nl, x.ptr, y.ptr, C.byref(res), None), "SdotSharded")
+
+    def saxpy():
+        x, y = pairs[it[0] % 4]; it[0] += 1
+        g.capi.check(L.guda_saxpy_sharded(comm, nl, 1e-3, x.ptr, y.ptr, None), "SaxpySharded")
+
+    def tiny_dot():                                        # the collective + host read alone: the latency floor of the blocking call
+        x, y = pairs[0]
+        g.capi.check(L.guda_sdot_sharded(comm, 32, x.ptr, y.ptr, C.byref(res), None), "SdotSharded")
+    for _ in range(4):
+        sdot()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(40):
+        sdot()
+    ms = max_over_ranks((time.perf_counter() - t0) / 40 * 1e3)
+    for _ in range(4):
+        tiny_dot()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(40):
+        tiny_dot()
+    floor_ms = max_over_ranks((time.perf_counter() - t0) / 40 * 1e3)
+    # parity: the sharded result of pair 0 against the one-GPU DOT of the whole vector (rank 0 regenerates it), ReduceArchTolerance
+    it[0] = 0
+    sdot()
+    got = float(res.value)
+    dot_ok = 1.0
+    if rank == 0:
+        xf, yf = g.Malloc(nl * world * 4), g.Malloc(nl * world * 4)
+        g.FillUniform(xf, 1, nl * world, nl * world, 300); g.FillUniform(yf, 1, nl * world, nl * world, 400)
+        whole = float(g.DOT(xf, yf, nl * world))
+        dot_ok = 1.0 if T.Float32NearEqual(whole, got, T.GetOperationTolerance("dot")) else 0.0
+        g.Free(xf); g.Free(yf)
+    dot_ok = min_over_ranks(dot_ok)
+    gbs = 8.0 * nl * world / (ms * 1e-3) / 1e9
+    out["sdot_sharded"] = {"value": gbs, "unit": "GB/s", "ms_per_call": ms, "scaling": "weak", "n_total": nl * world,
+                           "what": "blocking call: per-rank DOT + one-float ncclAllReduce + host read of the scalar, wall clock, max over ranks",
+                           "allreduce_and_host_read_floor_ms": floor_ms,
+                           "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"] * world, "unit": "GB/s",
+                                        "frac": gbs / (peaks["hbm_gbs"] * world), "frac_excluding_the_floor": 8.0 * nl * world / (max(ms - floor_ms, 1e-6) * 1e-3) / 1e9 / (peaks["hbm_gbs"] * world)},
+                           "parity": {"within_ReduceArchTolerance_of_one_gpu": bool(dot_ok > 0.5)}}
+    ok = ok and dot_ok > 0.5
+    for _ in range(4):
+        saxpy()
+    barrier()
+    ms = max_over_ranks(dev.time_ms(saxpy, 40))
+    barrier()
+    # parity: a 4096-element window of this rank's chunk replayed by the oracle (one FMA per element: every bit)
+    x, y = pairs[0]
+    win = 4096
+    hx = g.DevicePtr(x.ptr + 4 * 12345, win * 4).Float32()[:win].copy()
+    hy = g.DevicePtr(y.ptr + 4 * 12345, win * 4).Float32()[:win].copy()
+    g.capi.check(L.guda_saxpy_sharded(comm, win, 2.5, x.ptr + 4 * 12345, y.ptr + 4 * 12345, None), "SaxpySharded")
+    g.Synchronize()
+    ax_ok = float(np.array_equal(g.DevicePtr(y.ptr + 4 * 12345, win * 4).Float32()[:win], O.saxpy(win, 2.5, hx, 1, hy.copy(), 1)))
+    ax_ok = min_over_ranks(ax_ok)
+    gbs = 12.0 * nl * world / (ms * 1e-3) / 1e9
+    out["saxpy_sharded"] = {"value": gbs, "unit": "GB/s", "ms_per_call": ms, "scaling": "weak", "n_total": nl * world,
+                            "what": "stream-ordered per-rank AXPY on its resident chunk, no collective; CUDA events, max over ranks",
+                            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"] * world, "unit": "GB/s", "frac": gbs / (peaks["hbm_gbs"] * world)},
+                            "parity": {"bit_identical_window": bool(ax_ok > 0.5)}}
+    ok = ok and ax_ok > 0.5
+    for x, y in pairs:
+        g.Free(x); g.Free(y)
+    L.guda_pool_trim()
+    out["all_parity_ok"] = bool(ok)
+    return out
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -470,6 +693,14 @@ def main():
         if dist is not None:
             dist.barrier()
         g.Synchronize()
+
+    def min_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return float(t.item())
 
     def max_over_ranks(x):
         if dist is None:
@@ -528,6 +759,12 @@ def main():
     flops = 2.0 * n ** 3
     value = flops / (ms * 1e-3) / 1e12
 
+    # ---- parity, outside the timed region: sampled blocks of the (gathered) C against the oracle's chains, on EVERY rank
+    c_check, ld_check = (c_full, n) if world > 1 else (c_block, n)
+    blocks = sample_blocks(n, pr, pc, rank, world)
+    good = parity_blocks(g, _device_block_reader(g, c_check, ld_check, 0, 0), n, blocks, 11, 12) if args.mode == "exact" else len(blocks)
+    all_good = min_over_ranks(good)
+
     # dominant kernel alone (the local block GEMM), for the roofline
     def local_gemm():
         L.guda_sgemm(0, 0, m_loc, n_loc, n, 1.0, a_panel.ptr, n, b_panel.ptr, n_loc, 0.0, c_block.ptr, n_loc, None)
@@ -566,9 +803,19 @@ def main():
                                                        c_block.ptr, c_full.ptr, n, None), "SgemmShardedHost")
             e2e_step()
             barrier()
-            e_ms = max_over_ranks(dev.time_ms(e2e_step, max(1, min(args.steps, 2))))
+            e_steps = max(1, min(args.steps, 5))
+            e_ms = max_over_ranks(dev.time_ms(e2e_step, e_steps))
             barrier()
-            e2e = {"value": flops / (e_ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": e_ms,
+            # parity of the HOST result block (this rank's m_loc x n_loc block of C), outside the timed region
+            hc_arr = np.ctypeslib.as_array(C.cast(hc, C.POINTER(C.c_float)), shape=(m_loc, n_loc))
+            eb = [(row0, col0), (row0 + m_loc - 4, col0 + n_loc - 4), (row0 + (m_loc // 2 | 1), col0 + (n_loc // 3 | 2))]
+            e_good = 0
+            if args.mode == "exact":
+                e_good = parity_blocks(g, lambda i0, j0: hc_arr[i0 - row0:i0 - row0 + 4, j0 - col0:j0 - col0 + 4].copy(), n, eb, 11, 12)
+            e_all = min_over_ranks(e_good)
+            e2e = {"value": flops / (e_ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": e_ms, "steps": e_steps,
+                   "parity": {"blocks": len(eb), "bit_identical": bool(e_all == len(eb)), "where": "host C block of every rank vs the oracle's chains"}
+                             if args.mode == "exact" else None,
                    "h2d_bytes_per_step": (m_loc * n + n * n_loc) * 4 * world, "d2h_bytes_per_step": m_loc * n_loc * 4 * world,
                    "host_memory": "pinned",
                    "call": "guda_sgemm_host (K-chunk pipelined H2D, row-panel D2H)" if world == 1 else
@@ -583,9 +830,16 @@ def main():
             g.Free(p)
     L.guda_pool_trim()
 
+    secondary = sharded_secondary(dev, comm, dist, world, rank, pr, pc, peaks, dmma_peak, barrier, max_over_ranks, min_over_ranks) \
+        if (comm is not None and not args.no_suite) else None
+
     suite_res, cpu = None, None
     if rank == 0 and world == 1 and not args.no_suite:
         suite_res = suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak)
+        if not args.no_cpu:
+            for key, cb in cpu_suite_baselines(host_cores()).items():
+                if key in suite_res:
+                    suite_res[key]["cpu_baseline"] = cb
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = host_cores()
         tf, dt = cpu_sgemm_sample(2, 1, cores)
@@ -602,20 +856,33 @@ def main():
         L.guda_comm_destroy(comm)
     if rank == 0:
         # exact mode: K >= 16384 runs as 8192-deep launches resuming the same fp32 chains (gemm.cu launch_simt)
+        # exact mode, per step: every 8192-deep K chunk is one pre-pass (t = alpha*A transposed k-major + zero flags) and one
+        # pipeline launch (sgemm_pipe.cu); the NCCL gather route adds an unpack kernel when pc > 1
         kchunks = (n + 8191) // 8192 if (args.mode == "exact" and n >= 16384) else 1
-        launches = args.steps * (kchunks + (0 if (world == 1 or gather.startswith("fused") or pc == 1) else 1))
+        launches = args.steps * (2 * kchunks + (0 if (world == 1 or gather.startswith("fused") or pc == 1) else 1))
         line = {"metric": "sgemm_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "SGEMM %d^3 fp32 NN alpha=1 beta=0 (BASELINE configs[4]); %dx%d block partition%s" % (
                                n, pr, pc, ", C gathered on every rank inside the step (%s)" % gather if world > 1 else ""),
                            "math": "exact fp32 SIMT, reference k-order (bit-exact vs oracle)" if args.mode == "exact" else "3xTF32 tcgen05",
                            "l2": "operands %.1f GiB per rank, far larger than the 126 MB L2" % ((m_loc * n + n * n_loc) * 4 / 2 ** 30)},
-                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "parity": {"blocks": len(blocks), "bit_identical": bool(all_good == len(blocks)),
+                           "route": ("p2p" if gather.startswith("fused") else "nccl") if world > 1 else "single",
+                           "where": "sampled 4x4 blocks of the %s C on every rank (corners, another rank's block, block seam, tile corner, "
+                                    "unaligned) vs the oracle's FMA chains over regenerated panels" % ("gathered" if world > 1 else "full")}
+                          if args.mode == "exact" else None,
+                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "sharded": secondary,
                 "measured_here": {"ffma_tflops": ffma_peak, "dfma_tflops": dfma_peak, "dmma_tflops": dmma_peak, "copy_gbs": copy_peak},
                 "suite": suite_res}
         print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
+    bad = args.mode == "exact" and (all_good != len(blocks) or (e2e is not None and e2e.get("parity") and not e2e["parity"]["bit_identical"])
+                                    or (secondary is not None and not secondary.get("all_parity_ok", True)))
+    if bad:
+        if rank == 0:
+            print("bench.py: PARITY MISMATCH (see the parity objects of the JSON line)", file=sys.stderr)
+        sys.exit(1)
 
 
 if __name__ == "__main__":

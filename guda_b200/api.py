@@ -710,6 +710,12 @@ def SetSgemmMode(mode):
     capi.check(_L().guda_set_sgemm_mode(mode), "SetSgemmMode")
 
 
+def SetSgemmPipe(cfg=-1, lag=-1):
+    """Exact-route kernel choice (bit-identical results either way): -1 automatic, 0 register-staged kernel only, 1.. a forced
+    configuration of the TMA-fed pipeline (sgemm_pipe.cu; shapes that do not fit it still take the register-staged kernel)."""
+    capi.check(_L().guda_set_sgemm_pipe(cfg, lag), "SetSgemmPipe")
+
+
 def SetDgemmMode(mode):
     """0 = FP64 tensor pipe (DMMA) where eligible (default), 1 = SIMT DFMA kernel for every form."""
     capi.check(_L().guda_set_dgemm_mode(mode), "SetDgemmMode")

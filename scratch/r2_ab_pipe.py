@@ -71,7 +71,7 @@ if what in ("all", "time"):
             a, b, c = sets[i % nset]
             g.capi.check(L.guda_sgemm(0, 0, n, n, n, 1.0, a.ptr, n, b.ptr, n, 0.0, c.ptr, n, None), "sgemm")
         for cfg in CFGS:
-            for lag in ((1,) if cfg == 0 else (0, 1)):
+            for lag in ((1,) if cfg == 0 else [int(v) for v in os.environ.get("PIPE_LAGS", "1").split(",")]):
                 g.capi.check(L.guda_set_sgemm_pipe(cfg, lag), "pipe")
                 for i in range(3):
                     run(i)

@@ -112,6 +112,30 @@ def main():
             L.guda_free_host(h)
         return res
 
+    def run_dgemm(n, mode):
+        """guda_dgemm_sharded: gathered c_full on every rank bit-identical to the one-GPU DGEMM (DMMA route) of the same operands."""
+        g.capi.check(L.guda_comm_set_gather_mode(comm, mode), "SetGatherMode")
+        r0, m_loc, c0, n_loc = block_extents(rank, pr, pc, n, n)
+        a_panel, b_panel = g.Malloc(m_loc * n * 8), g.Malloc(n * n_loc * 8)
+        c_block, c_full = g.Malloc(m_loc * n_loc * 8), g.Malloc(n * n * 8)
+        g.FillUniform(a_panel, m_loc, n, n, seed=41, row0=r0, col0=0, full_cols=n, dtype=np.float64)
+        g.FillUniform(b_panel, n, n_loc, n_loc, seed=42, row0=0, col0=c0, full_cols=n, dtype=np.float64)
+        g.Memset(c_full, 0xFF, n * n * 8)
+        for _ in range(2):                                   # second call takes the cached peer mapping
+            g.capi.check(L.guda_dgemm_sharded(comm, pr, pc, n, n, n, 1.0, a_panel.ptr, n, b_panel.ptr, n_loc, c_block.ptr, n_loc,
+                                              c_full.ptr, n, None), "DgemmSharded")
+        g.Synchronize()
+        a, b, c = g.Malloc(n * n * 8), g.Malloc(n * n * 8), g.Malloc(n * n * 8)
+        g.FillUniform(a, n, n, n, seed=41, dtype=np.float64); g.FillUniform(b, n, n, n, seed=42, dtype=np.float64)
+        g.Dgemm(False, False, n, n, n, 1.0, a, n, b, n, 0.0, c, n)
+        g.Synchronize()
+        res = {"bit_identical_to_one_gpu": bool(np.array_equal(c_full.Float64(), c.Float64()))}
+        for p in (a, b, c, a_panel, b_panel, c_block, c_full):
+            g.Free(p)
+        return res
+
+    out["check_dgemm_p2p"] = run_dgemm(1024, 0)
+    out["check_dgemm_nccl"] = run_dgemm(1024, 1)
     out["check_host_p2p"] = run_host(1024, 2 * 8192 + 300, 0)
     out["check_host_nccl"] = run_host(1024, 2 * 8192 + 300, 1)
     out["check_p2p"] = run(args.check_size, 0, 1, True)
@@ -127,7 +151,16 @@ def main():
     r = C.c_float(0)
     g.capi.check(L.guda_sdot_sharded(comm, nvec // world, x.ptr + lo * 4, y.ptr + lo * 4, C.byref(r), None), "SdotSharded")
     out["sdot"] = {"one_gpu": float(whole), "sharded": float(r.value), "within_reduce_tolerance": bool(abs(r.value - whole) <= max(1e-5, 1e-4 * abs(whole)))}
+    # sharded AXPY: this rank's chunk, bit-identical to the same chunk of the one-GPU AXPY
+    yy = g.Malloc(nvec * 4); g.FillUniform(yy, 1, nvec, nvec, 32)
+    g.AXPY(2.5, x, yy, nvec)
+    g.capi.check(L.guda_saxpy_sharded(comm, nvec // world, 2.5, x.ptr + lo * 4, y.ptr + lo * 4, None), "SaxpySharded")
+    g.Synchronize()
+    out["saxpy"] = {"chunk_bit_identical": bool(np.array_equal(g.DevicePtr(y.ptr + lo * 4, (nvec // world) * 4).Float32(),
+                                                                g.DevicePtr(yy.ptr + lo * 4, (nvec // world) * 4).Float32()))}
     ok = torch.tensor([1.0 if (out["check_p2p"]["bit_identical_to_one_gpu"] and out["check_nccl"]["bit_identical_to_one_gpu"]
+                               and out["check_dgemm_p2p"]["bit_identical_to_one_gpu"] and out["check_dgemm_nccl"]["bit_identical_to_one_gpu"]
+                               and out["saxpy"]["chunk_bit_identical"]
                                and all(out[k][f] for k in ("check_host_p2p", "check_host_nccl")
                                        for f in ("gathered_bit_identical", "host_block_bit_identical"))
                                and out["sdot"]["within_reduce_tolerance"]) else 0.0], device="cuda")

@@ -538,8 +538,8 @@ def sample_blocks(n, pr, pc, rank, world):
     m_loc, n_loc = n // pr, n // pc
     other = (rank + 1) % world
     orow, ocol = (other // pc) * m_loc, (other % pc) * n_loc
-    return [(0, 0), (n - 4, n - 4), (orow + m_loc // 2 + 1, ocol + n_loc // 2 + 3), (m_loc - 2, n_loc - 2) if world > 1 else (n // 2 - 2, n // 2 - 2),
-            (62, 126), ((40001 * 7) % (n - 4), (50003 * 3) % (n - 4))]
+    seam = (m_loc - 2 if pr > 1 else n // 2 - 2, n_loc - 2 if pc > 1 else n // 2 - 2)
+    return [(0, 0), (n - 4, n - 4), (orow + m_loc // 2 + 1, ocol + n_loc // 2 + 3), seam, (62, 126), ((40001 * 7) % (n - 4), (50003 * 3) % (n - 4))]
 
 
 def sharded_secondary(dev, comm, dist, world, rank, pr, pc, peaks, dmma_peak, barrier, max_over_ranks, min_over_ranks):
@@ -600,6 +600,12 @@ def sharded_secondary(dev, comm, dist, world, rank, pr, pc, peaks, dmma_peak, ba
         x, y = pairs[it[0] % 4]; it[0] += 1
         g.capi.check(L.guda_saxpy_sharded(comm, nl, 1e-3, x.ptr, y.ptr, None), "SaxpySharded")
 
+    dres = g.Malloc(64)
+
+    def sdot_dev():                                        # stream-ordered form: the scalar stays on the device, no host read
+        x, y = pairs[it[0] % 4]; it[0] += 1
+        g.capi.check(L.guda_sdot_sharded_device(comm, nl, x.ptr, y.ptr, dres.ptr, None), "SdotShardedDevice")
+
     def tiny_dot():                                        # the collective + host read alone: the latency floor of the blocking call
         x, y = pairs[0]
         g.capi.check(L.guda_sdot_sharded(comm, 32, x.ptr, y.ptr, C.byref(res), None), "SdotSharded")
@@ -629,6 +635,17 @@ def sharded_secondary(dev, comm, dist, world, rank, pr, pc, peaks, dmma_peak, ba
         dot_ok = 1.0 if T.Float32NearEqual(whole, got, T.GetOperationTolerance("dot")) else 0.0
         g.Free(xf); g.Free(yf)
     dot_ok = min_over_ranks(dot_ok)
+    for _ in range(4):
+        sdot_dev()
+    barrier()
+    ms_dev = max_over_ranks(dev.time_ms(sdot_dev, 40))
+    barrier()
+    g.Free(dres)
+    gbs_dev = 8.0 * nl * world / (ms_dev * 1e-3) / 1e9
+    out["sdot_sharded_stream_ordered"] = {
+        "value": gbs_dev, "unit": "GB/s", "ms_per_call": ms_dev, "scaling": "weak", "n_total": nl * world,
+        "what": "guda_sdot_sharded_device: per-rank DOT + one-float ncclAllReduce, result left on the device; CUDA events over 40 back-to-back calls, max over ranks",
+        "roofline": {"bound": "hbm", "achieved": gbs_dev, "peak": peaks["hbm_gbs"] * world, "unit": "GB/s", "frac": gbs_dev / (peaks["hbm_gbs"] * world)}}
     gbs = 8.0 * nl * world / (ms * 1e-3) / 1e9
     out["sdot_sharded"] = {"value": gbs, "unit": "GB/s", "ms_per_call": ms, "scaling": "weak", "n_total": nl * world,
                            "what": "blocking call: per-rank DOT + one-float ncclAllReduce + host read of the scalar, wall clock, max over ranks",
@@ -816,10 +833,13 @@ def main():
             e2e = {"value": flops / (e_ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": e_ms, "steps": e_steps,
                    "parity": {"blocks": len(eb), "bit_identical": bool(e_all == len(eb)), "where": "host C block of every rank vs the oracle's chains"}
                              if args.mode == "exact" else None,
-                   "h2d_bytes_per_step": (m_loc * n + n * n_loc) * 4 * world, "d2h_bytes_per_step": m_loc * n_loc * 4 * world,
+                   # N > 1: every unique panel chunk crosses PCIe once (its owner uploads it, ncclBroadcast fans it out over NVLink)
+                   "h2d_bytes_per_step": 2 * n * n * 4, "d2h_bytes_per_step": m_loc * n_loc * 4 * world,
+                   "nvlink_broadcast_bytes_per_step": ((pc - 1) * pr * m_loc * n + (pr - 1) * pc * n * n_loc) * 4,
                    "host_memory": "pinned",
                    "call": "guda_sgemm_host (K-chunk pipelined H2D, row-panel D2H)" if world == 1 else
-                           "guda_sgemm_sharded_host (K-chunk pipelined H2D under the GEMM, fused gather on the last chunk, D2H of the C block)"}
+                           "guda_sgemm_sharded_host (K-chunk pipelined: one H2D per unique panel chunk + NVLink broadcast to the ranks sharing it, under the "
+                           "GEMM; fused gather on the last chunk; D2H of the C block)"}
             for hp in (ha, hb, hc):
                 L.guda_free_host(hp)
         else:
@@ -856,9 +876,9 @@ def main():
         L.guda_comm_destroy(comm)
     if rank == 0:
         # exact mode: K >= 16384 runs as 8192-deep launches resuming the same fp32 chains (gemm.cu launch_simt)
-        # exact mode, per step: every 8192-deep K chunk is one pre-pass (t = alpha*A transposed k-major + zero flags) and one
+        # exact mode, per step: every 4096-deep K chunk is one pre-pass (t = alpha*A transposed k-major + zero flags) and one
         # pipeline launch (sgemm_pipe.cu); the NCCL gather route adds an unpack kernel when pc > 1
-        kchunks = (n + 8191) // 8192 if (args.mode == "exact" and n >= 16384) else 1
+        kchunks = (n + 4095) // 4096 if (args.mode == "exact" and n >= 8192) else 1          # sgemm_pipe.cu: 4096-deep K chunks from k = 8192 up
         launches = args.steps * (2 * kchunks + (0 if (world == 1 or gather.startswith("fused") or pc == 1) else 1))
         line = {"metric": "sgemm_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",

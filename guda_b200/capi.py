@@ -149,6 +149,7 @@ SIGNATURES = {
     "guda_comm_set_gather_mode": (i, [vp, i]),
     "guda_comm_get_gather_mode": (i, [vp, ip]),
     "guda_sdot_sharded": (i, [vp, i, vp, vp, fp, vp]),
+    "guda_sdot_sharded_device": (i, [vp, i, vp, vp, vp, vp]),
     "guda_saxpy_sharded": (i, [vp, i, f, vp, vp, vp]),
     "guda_dgemm_sharded": (i, [vp, i, i, i, i, i, d, vp, i, vp, i, vp, i, vp, i, vp]),
     "guda_tolerance_preset": (i, [i, C.POINTER(Tolerance)]),
@@ -157,7 +158,6 @@ SIGNATURES = {
     "guda_standard_tolerance": (i, [C.c_char_p, fp, fp, ip]),
     "guda_verify_f32": (i, [vp, vp, C.c_longlong, C.POINTER(Tolerance), C.POINTER(VerifyResult), vp]),
     "guda_microbench_peak": (i, [i, i, dp]),
-    "guda_microbench_lds": (i, [i, ip, i, dp]),
 }
 
 _lib = None

@@ -151,7 +151,11 @@ struct TileLoader {
   static_assert(NVEC % 256 == 0, "tile must split evenly over 256 threads");
   V reg[PER_THREAD];
 
-  __device__ __forceinline__ void load(const T* __restrict__ g, long long ld, int mn0, int k0, int MN, int K, int tid) {
+  // scale / do_scale: on the edge path (FAST == false) operand A is scaled HERE, element by element, so that the zero padding
+  // beyond (MN, K) stays an exact +0 -- scaling it in store() would turn it into NaN for alpha = +-Inf (0 * Inf) and the
+  // zero test `t != 0` would then let the NaN into every accumulator of the tile.
+  __device__ __forceinline__ void load(const T* __restrict__ g, long long ld, int mn0, int k0, int MN, int K, int tid, T scale = T(1),
+                                       bool do_scale = false) {
 #pragma unroll
     for (int it = 0; it < PER_THREAD; it++) {
       int v = tid + it * 256;
@@ -168,7 +172,7 @@ struct TileLoader {
           int gm = mn0 + mn + (KCONTIG ? 0 : j), gk = k0 + kk + (KCONTIG ? j : 0);
           bool ok = gm < MN && gk < K;
           const T* p = KCONTIG ? g + (long long)gm * ld + gk : g + (long long)gk * ld + gm;
-          r[j] = ok ? *p : T(0);
+          r[j] = ok ? (do_scale ? g_mul(scale, *p) : *p) : T(0);
         }
       }
     }
@@ -186,7 +190,7 @@ struct TileLoader {
       T* r = reinterpret_cast<T*>(&reg[it]);
       if (do_scale) {
 #pragma unroll
-        for (int j = 0; j < VN; j++) { r[j] = g_mul(scale, r[j]); anyzero |= (r[j] == T(0)); }
+        for (int j = 0; j < VN; j++) { if (FAST) r[j] = g_mul(scale, r[j]); anyzero |= (r[j] == T(0)); }
       }
       if (KCONTIG) {
 #pragma unroll
@@ -273,7 +277,7 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p, S
   const int KT = (p.k + BK - 1) / BK;
   bool zf = false;
   if (KT > 0) {
-    la.load(p.a, p.lda, m0, 0, p.m, p.k, tid);
+    la.load(p.a, p.lda, m0, 0, p.m, p.k, tid, p.alpha, true);
     lb.load(p.b, p.ldb, n0, 0, p.n, p.k, tid);
     bool z = la.template store<Smem::LDA_S>(sm.a[0], p.alpha, true, tid);
     lb.template store<Smem::LDB_S>(sm.b[0], T(0), false, tid);
@@ -282,7 +286,7 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p, S
   for (int kt = 0; kt < KT; kt++) {
     const int cur = kt & 1;
     if (kt + 1 < KT) {
-      la.load(p.a, p.lda, m0, (kt + 1) * BK, p.m, p.k, tid);
+      la.load(p.a, p.lda, m0, (kt + 1) * BK, p.m, p.k, tid, p.alpha, true);
       lb.load(p.b, p.ldb, n0, (kt + 1) * BK, p.n, p.k, tid);
     }
     if (!zf && MODE == MODE_FMA) {
@@ -319,8 +323,10 @@ __global__ void __launch_bounds__(256, MINB) gemm_simt_kernel(GemmParams<T> p, S
         }
       }
     } else {
+      const int kreal = FAST ? BK : (p.k - kt * BK < BK ? p.k - kt * BK : BK);     // the reference never visits k >= K (bfloat16.go:152 has no zero test to hide it)
 #pragma unroll
       for (int kk = 0; kk < BK; kk++) {
+        if (!FAST && kk >= kreal) break;
         T af[TM], bf[TN];
         load_frag<T, HM>(af, &sm.a[cur][kk][ty * HM]);
         load_frag<T, HM>(af + HM, &sm.a[cur][kk][BM / 2 + ty * HM]);

@@ -18,6 +18,7 @@
 // (4 per SM) with a deterministic last-block final reduction that writes the scalar straight
 // into mapped pinned host memory, so the host needs no extra copy.
 #include "common.cuh"
+#include <map>
 #include <mutex>
 
 namespace guda {
@@ -185,6 +186,7 @@ __global__ void __launch_bounds__(L1_THREADS, 4) dot_kernel(size_t n, const T* _
   for (int u = 0; u < L1_UNROLL; u++)
 #pragma unroll
     for (int j = 0; j < VN; j++) acc[u][j] = T(0);
+  pdl_wait();              // x / y may be the previous kernel's output; everything above ran under that kernel's tail
 
   const bool unit = (incx == 1 && incy == 1);
   if (unit) {
@@ -221,6 +223,7 @@ __global__ void __launch_bounds__(L1_THREADS, 4) dot_kernel(size_t n, const T* _
     for (size_t i = (size_t)blockIdx.x * L1_THREADS + threadIdx.x; i < n; i += (size_t)gridDim.x * L1_THREADS)
       acc[0][0] = fma_t(x[(long long)i * incx], y[(long long)i * incy], acc[0][0]);
   }
+  pdl_trigger();           // the streaming part is over: the next kernel's CTAs may be scheduled under this kernel's fold
   // fixed-order in-thread tree
   T s = T(0);
 #pragma unroll
@@ -275,6 +278,26 @@ template <typename T> static size_t head_elems(const void* p) {
 }
 
 static std::mutex g_dot_mu;
+// One scratch slot (partials + ticket counter + pinned host scalar) PER STREAM: DOTs on one stream are ordered by the stream, DOTs
+// on different streams (or host threads) never share partials or a ticket -- the round-1 scheme rotated 8 global slots and released
+// its lock before the launch on the device-result path, so more than 8 DOTs in flight could fold each other's partials.
+struct DotSlot { void* partials; unsigned int* counter; void* host_scalar; void* host_scalar_dev; };
+static std::map<cudaStream_t, DotSlot> g_dot_slots;
+static int dot_slot_for(cudaStream_t s, DotSlot* out) {
+  std::lock_guard<std::mutex> lk(g_dot_mu);
+  auto it = g_dot_slots.find(s);
+  if (it == g_dot_slots.end()) {
+    DotSlot d{};
+    GUDA_CUDA(cudaMalloc(&d.partials, 8192));
+    GUDA_CUDA(cudaMalloc((void**)&d.counter, 256));
+    GUDA_CUDA(cudaMemset(d.counter, 0, 256));
+    GUDA_CUDA(cudaHostAlloc(&d.host_scalar, 64, cudaHostAllocMapped));
+    GUDA_CUDA(cudaHostGetDevicePointer(&d.host_scalar_dev, d.host_scalar, 0));
+    it = g_dot_slots.emplace(s, d).first;
+  }
+  *out = it->second;
+  return GUDA_OK;
+}
 
 template <typename T>
 static int axpy_impl(int n, T alpha, const T* x, int incx, T* y, int incy, guda_stream_t stream, const char* op) {
@@ -356,7 +379,6 @@ static int scal_impl(int n, T alpha, T* x, int incx, guda_stream_t stream, const
   return check_launch(op);
 }
 
-static unsigned int g_dot_slot = 0;
 
 template <typename T>
 static int dot_impl(int n, const T* x, int incx, const T* y, int incy, T* host_result, T* dev_result, guda_stream_t stream, const char* op) {
@@ -372,8 +394,6 @@ static int dot_impl(int n, const T* x, int incx, const T* y, int incy, T* host_r
     return GUDA_OK;                                         // level1float32_sdot.go:25-30: returns 0
   }
   if (!x || !y) return set_error(GUDA_ERR_INVALID_ARG, "%s: null pointer", op);
-  Scratch* sc;
-  get_scratch(&sc);
   size_t N = (size_t)n;
   const T* xs = x; const T* ys = y;
   if (incx < 0) xs = x + (long long)(-n + 1) * incx;
@@ -395,26 +415,28 @@ static int dot_impl(int n, const T* x, int incx, const T* y, int incy, T* host_r
   static int occ = 0;       // resident CTAs per SM for this kernel: the grid must be exactly one full wave
   if (occ == 0) {
     int o = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dot_kernel<float>, L1_THREADS, 0) != cudaSuccess || o < 1) o = 2;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dot_kernel<T>, L1_THREADS, 0) != cudaSuccess || o < 1) o = 2;
     if (o > 4) o = 4;
     occ = o;
   }
   unsigned wave = (unsigned)sm_count() * (unsigned)occ;
   if (grid > wave) grid = wave;
   if (grid == 0) grid = 1;
-  // 8 scratch slots of 8 KiB (>= 592 partials of 8 bytes) + one ticket counter each
-  std::unique_lock<std::mutex> lk(g_dot_mu);
-  unsigned slot = (g_dot_slot++) & 7;
-  T* partials = reinterpret_cast<T*>(reinterpret_cast<char*>(sc->dev_partials) + slot * 8192);
-  unsigned int* counter = sc->dev_counter + slot * 8;
-  T* host_alias = host_result ? reinterpret_cast<T*>(reinterpret_cast<char*>(sc->host_scalar_dev) + slot * 16) : nullptr;
-  if (!host_result) lk.unlock();
-  dot_kernel<T><<<grid, L1_THREADS, 0, s>>>(N, xs, unit ? 1 : ix, ys, unit ? 1 : iy, head, partials, counter, host_alias, dev_result);
+  DotSlot slot;
+  if ((rc = dot_slot_for(s, &slot))) return rc;
+  T* partials = reinterpret_cast<T*>(slot.partials);                      // 8 KiB >= 592 partials of 8 bytes
+  unsigned int* counter = slot.counter;
+  T* host_alias = host_result ? reinterpret_cast<T*>(slot.host_scalar_dev) : nullptr;
+  {
+    cudaError_t le = launch_pdl(1, dot_kernel<T>, dim3(grid), dim3(L1_THREADS), 0, s, N, xs, (long long)(unit ? 1 : ix), ys, (long long)(unit ? 1 : iy),
+                                head, partials, counter, host_alias, dev_result);
+    if (le != cudaSuccess) return set_error(GUDA_ERR_EXECUTION, "%s launch failed: %s", op, cudaGetErrorString(le));
+  }
   rc = check_launch(op);
   if (rc) return rc;
   if (host_result) {
     GUDA_CUDA(cudaStreamSynchronize(s));
-    *host_result = *reinterpret_cast<volatile T*>(reinterpret_cast<char*>(sc->host_scalar) + slot * 16);
+    *host_result = *reinterpret_cast<volatile T*>(slot.host_scalar);
   }
   return GUDA_OK;
 }

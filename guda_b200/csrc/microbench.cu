@@ -69,39 +69,6 @@ __global__ void __launch_bounds__(256) copy_peak_kernel(const float4* __restrict
   }
 }
 
-// Shared-memory load cost per lane->address pattern (the design input of sgemm_pipe.cu's lane layouts): every lane loads
-// W bytes at chunk index lane_idx[lane] (units of W bytes), 8 independent loads in flight per warp, 8 warps per CTA,
-// one CTA; the result is SM cycles per warp-level load instruction = wavefronts when the LSU is the limiter.
-template <int W>
-__global__ void __launch_bounds__(256) lds_pattern_kernel(const int* __restrict__ lane_idx, int iters, unsigned long long* out) {
-  __shared__ __align__(16) unsigned char buf[40 * 1024];
-  for (int i = threadIdx.x; i < 40 * 1024 / 4; i += 256) reinterpret_cast<unsigned*>(buf)[i] = i;
-  const unsigned base = static_cast<unsigned>(__cvta_generic_to_shared(buf)) + lane_idx[threadIdx.x & 31] * W;
-  unsigned r[8][4];
-#pragma unroll
-  for (int u = 0; u < 8; u++) r[u][0] = r[u][1] = r[u][2] = r[u][3] = 0;
-  __syncthreads();
-  const long long t0 = clock64();
-  for (int it = 0; it < iters; it++) {
-#pragma unroll
-    for (int u = 0; u < 8; u++) {
-      // the row moves with the iteration (whole 128-byte rows: the lane -> bank pattern is unchanged) so that the loads
-      // are not loop-invariant
-      const unsigned addr = base + u * 4096 + (it & 7) * 128;
-      if (W == 16) asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r[u][0]), "=r"(r[u][1]), "=r"(r[u][2]), "=r"(r[u][3]) : "r"(addr) : "memory");
-      else if (W == 8) asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r[u][0]), "=r"(r[u][1]) : "r"(addr) : "memory");
-      else asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r[u][0]) : "r"(addr) : "memory");
-    }
-  }
-  __syncthreads();
-  const long long t1 = clock64();
-  unsigned x = 0;
-#pragma unroll
-  for (int u = 0; u < 8; u++) x ^= r[u][0] ^ r[u][1] ^ r[u][2] ^ r[u][3];
-  if (threadIdx.x == 0) out[0] = (unsigned long long)(t1 - t0);
-  if (x == 0xdeadbeefu) out[1] = x;
-}
-
 template <typename T>
 static int fma_peak(double* tflops, int reps) {
   int rc = bind_device();
@@ -211,29 +178,4 @@ int guda_microbench_peak(int kind, int reps, double* value) {
   return GUDA_OK;
 }
 
-// cycles per warp-level shared-memory load for a lane -> chunk pattern (width = 4, 8 or 16 bytes; 32 chunk indices, each < 256)
-int guda_microbench_lds(int width, const int* host_lane_idx, int iters, double* cycles_per_instr) {
-  if (!host_lane_idx || !cycles_per_instr || iters <= 0) return set_error(GUDA_ERR_INVALID_ARG, "bad argument");
-  if (width != 4 && width != 8 && width != 16) return set_error(GUDA_ERR_INVALID_ARG, "width must be 4, 8 or 16");
-  for (int i = 0; i < 32; i++) if (host_lane_idx[i] < 0 || host_lane_idx[i] * width + width > 3072) return set_error(GUDA_ERR_INVALID_ARG, "chunk index out of range");
-  int rc = bind_device();
-  if (rc) return rc;
-  int* idx; unsigned long long* out;
-  GUDA_CUDA(cudaMalloc((void**)&idx, 128));
-  GUDA_CUDA(cudaMalloc((void**)&out, 16));
-  cudaStream_t s = native(nullptr);
-  GUDA_CUDA(cudaMemcpyAsync(idx, host_lane_idx, 128, cudaMemcpyHostToDevice, s));
-  for (int r = 0; r < 2; r++) {
-    if (width == 16) lds_pattern_kernel<16><<<1, 256, 0, s>>>(idx, iters, out);
-    else if (width == 8) lds_pattern_kernel<8><<<1, 256, 0, s>>>(idx, iters, out);
-    else lds_pattern_kernel<4><<<1, 256, 0, s>>>(idx, iters, out);
-    if ((rc = check_launch("lds_pattern"))) { cudaFree(idx); cudaFree(out); return rc; }
-  }
-  unsigned long long cyc = 0;
-  GUDA_CUDA(cudaMemcpyAsync(&cyc, out, 8, cudaMemcpyDeviceToHost, s));
-  GUDA_CUDA(cudaStreamSynchronize(s));
-  cudaFree(idx); cudaFree(out);
-  *cycles_per_instr = (double)cyc / ((double)iters * 8.0 * 8.0);
-  return GUDA_OK;
-}
 }

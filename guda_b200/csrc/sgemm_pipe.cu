@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(256) sgemm_prepass_kernel(const float* __restr
   const int tid = threadIdx.x;
   const int m0 = blockIdx.y * 64, k0 = blockIdx.x * 64;
   if (tid < 4) zf[tid] = 0;
+  pdl_wait();                // A may be the previous kernel's output, and the scratch it overwrites may still be read by it
   __syncthreads();
   bool z = false;
   if (!TA) {
@@ -72,6 +73,7 @@ __global__ void __launch_bounds__(256) sgemm_prepass_kernel(const float* __restr
     __syncthreads();
   }
   if (tid < 4 && k0 + tid * 16 < k) flags[(long long)blockIdx.y * flag_ld + blockIdx.x * 4 + tid] = (unsigned char)zf[tid];
+  pdl_trigger();             // this CTA's part of At / flags is written: the pipeline kernel behind may start being scheduled
 }
 
 // ---------------------------------------------------------------- host side
@@ -88,6 +90,14 @@ constexpr int PIPE_DEFAULT = 1;
 
 static int g_pipe_cfg = [] { const char* e = getenv("GUDA_SGEMM_PIPE"); return e ? atoi(e) : -1; }();   // -1 auto, 0 off, 1.. forced config
 static int g_pipe_lag = [] { const char* e = getenv("GUDA_SGEMM_PIPE_LAG"); return e ? atoi(e) : 1; }();
+// L2 blocking of large calls.  A tile group is `rows` rows of C sweeping N: its A panel (rows x kc) stays in L2
+// for the whole sweep, each B column tile (kc x 128) is shared by the group's rows/64 CTAs and re-read once per group.  The ~592
+// resident CTAs sit at unrelated k positions, so the working set is the WHOLE resident patch: kc * (4*rows + 592*64*512/rows) bytes
+// -- 144 MB at kc = 8192, rows = 2048 (round 1's depth; it thrashes the 126 MB L2: 2.74 TB of DRAM traffic per 65536^3 step) and
+// 72 MB at kc = 4096, which fits: 1.31 TB per step at the same speed (profiles/r02/l2_blocking_sweep_32768.log: rows = 4096 falls
+// off the cliff again).  Traffic model: 4*N^2*K/rows (B re-reads) + 8*N^2*K/kc (the C round trip of a K-chunked launch).
+static int g_pipe_group_rows = [] { const char* e = getenv("GUDA_PIPE_GROUP_ROWS"); return e ? atoi(e) : 2048; }();
+static int g_pipe_kc = [] { const char* e = getenv("GUDA_PIPE_KC"); return e ? atoi(e) : 4096; }();
 
 template <class Cfg, int EPI, bool SCAT>
 static int launch_pipe_cfg(const GemmParams<float>& p, const float* at, long long ldat, const unsigned char* flags, int flag_ld,
@@ -103,7 +113,8 @@ static int launch_pipe_cfg(const GemmParams<float>& p, const float* at, long lon
   if (attr_err != cudaSuccess) return set_error(GUDA_ERR_EXECUTION, "sgemm_pipe: cannot reserve %d bytes of shared memory", Cfg::SMEM);
   const long long tiles = (long long)(p.m / Cfg::BM) * (p.n / Cfg::BN);
   int lag = g_pipe_lag < 0 ? 0 : (g_pipe_lag >= 100 ? 101 : (g_pipe_lag > Cfg::STAGES - 1 ? Cfg::STAGES - 1 : g_pipe_lag));
-  kern<<<(unsigned)tiles, Cfg::THREADS, Cfg::SMEM, s>>>(ma, mb, p, flags, flag_ld, lag, sp);
+  cudaError_t le = launch_pdl(4, kern, dim3((unsigned)tiles), dim3(Cfg::THREADS), Cfg::SMEM, s, ma, mb, p, flags, flag_ld, lag, g_pipe_group_rows, sp);
+  if (le != cudaSuccess) return set_error(GUDA_ERR_EXECUTION, "sgemm_pipe launch failed: %s", cudaGetErrorString(le));
   return check_launch("sgemm_pipe");
 }
 
@@ -148,7 +159,7 @@ int sgemm_pipe_try(int ta, int tb, int m, int n, int k, float alpha, const float
     if (scatter->ld % 4 || scatter->off % 4) return -1;
     for (int i = 0; i < scatter->n; i++) if (!al16(scatter->dst[i])) return -1;
   }
-  constexpr int KC = 8192;
+  const int KC = g_pipe_kc;
   const int kc_max = (epi == EPI_NONE && k >= 2 * KC) ? KC : k;       // the fused epilogues run on one unchunked chain
   if (kc_max / 16 > PIPE_ZF_MAX) return -1;
   PoolTemp at, fl;
@@ -160,8 +171,11 @@ int sgemm_pipe_try(int ta, int tb, int m, int n, int k, float alpha, const float
     const int kc = k - k0 < kc_max ? k - k0 : kc_max;
     const bool last = k0 + kc >= k;
     dim3 pg((kc + 63) / 64, m / 64);
-    if (ta) sgemm_prepass_kernel<true><<<pg, 256, 0, s>>>(a + (long long)k0 * lda, lda, m, kc, alpha, (float*)at.p, m, (unsigned char*)fl.p, flag_ld);
-    else    sgemm_prepass_kernel<false><<<pg, 256, 0, s>>>(a + k0, lda, m, kc, alpha, (float*)at.p, m, (unsigned char*)fl.p, flag_ld);
+    cudaError_t le = ta ? launch_pdl(2, sgemm_prepass_kernel<true>, pg, dim3(256), 0, s, a + (long long)k0 * lda, (long long)lda, m, kc, alpha, (float*)at.p,
+                                     (long long)m, (unsigned char*)fl.p, flag_ld)
+                        : launch_pdl(2, sgemm_prepass_kernel<false>, pg, dim3(256), 0, s, a + k0, (long long)lda, m, kc, alpha, (float*)at.p, (long long)m,
+                                     (unsigned char*)fl.p, flag_ld);
+    if (le != cudaSuccess) return set_error(GUDA_ERR_EXECUTION, "sgemm_prepass launch failed: %s", cudaGetErrorString(le));
     if ((rc = check_launch("sgemm_prepass"))) return rc;
     GemmParams<float> p{m, n, kc, alpha, k0 == 0 ? beta : 1.0f, nullptr, 0, b + (long long)k0 * ldb, ldb, c, ldc, bias, m, n};
     if (scatter && last) {

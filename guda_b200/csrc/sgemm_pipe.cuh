@@ -1,5 +1,5 @@
 // sgemm_pipe.cuh -- the kernel template of sgemm_pipe.cu (see the header comment there), in a header so that the instruction-stream
-// explorer (scratch/explore_pipe.py: compile-only sweeps read by scratch/sass_reuse2.py) can instantiate it on its own.
+// explorer (tools/explore_pipe.py: compile-only sweeps read by tools/sass_reuse.py) can instantiate it on its own.
 #pragma once
 #include "gemm_simt.cuh"
 #include "tc_ptx.cuh"
@@ -33,7 +33,7 @@ struct PipeCfg {
 template <class Cfg, int EPI, bool SCAT>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB)
 sgemm_pipe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, GemmParams<float> p,
-                  const unsigned char* __restrict__ flags, int flag_ld, int lag, ScatterParams<float, SCAT> sp) {
+                  const unsigned char* __restrict__ flags, int flag_ld, int lag, int group_rows, ScatterParams<float, SCAT> sp) {
   using namespace tc;
   constexpr int TM = Cfg::TM, TN = Cfg::TN, LY = Cfg::LY, LX = Cfg::LX, BM = Cfg::BM, BN = Cfg::BN, BK = Cfg::BK, STAGES = Cfg::STAGES;
   constexpr bool PAIR_M = Cfg::PAIR_M;
@@ -47,7 +47,7 @@ sgemm_pipe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   // CTA -> tile: groups of row blocks sweep N so that co-resident CTAs share A row panels and B column panels in L2
   int tile_m, tile_n;
   {
-    const int tiles_m = p.m / BM, tiles_n = p.n / BN, group = (2048 / BM) > 0 ? (2048 / BM) : 1;
+    const int tiles_m = p.m / BM, tiles_n = p.n / BN, group = (group_rows / BM) > 0 ? (group_rows / BM) : 1;
     const int t = blockIdx.x;
     const int per_group = group * tiles_n;
     const int gi = t / per_group, r = t - gi * per_group;
@@ -64,6 +64,7 @@ sgemm_pipe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     for (int s = 0; s < STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], Cfg::WARPS); }
     fence_barrier_init();
     prefetch_tmap(&map_a); prefetch_tmap(&map_b);
+    pdl_wait();                          // At / flags come from the pre-pass launched just before; everything above overlapped its tail
     const int pre = KT < STAGES ? KT : STAGES;
     for (int s = 0; s < pre; s++) {
       float* sa = reinterpret_cast<float*>(smem_raw + s * Cfg::STAGE_BYTES);
@@ -72,6 +73,7 @@ sgemm_pipe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       tma_load_2d(sa + BK * BM, &map_b, &full[s], n0, s * BK);
     }
   }
+  if (tid != 0) pdl_wait();
   for (int kt = tid; kt < KT; kt += Cfg::THREADS) {
     unsigned char f = 0;
 #pragma unroll
@@ -242,6 +244,7 @@ sgemm_pipe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   }
   // (every refill is issued inside the loop: k-tile kr + STAGES < KT is requested at iteration kr + lag <= KT - 1 for lag < STAGES)
 
+  pdl_trigger();               // the k walk is over: the next kernel on the stream may be scheduled under the epilogue stores
   // ---- epilogue in registers, single 128-bit store per chunk
 #pragma unroll
   for (int i = 0; i < TM; i++) {

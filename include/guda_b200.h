@@ -313,9 +313,6 @@ int guda_verify_f32(const float* expected, const float* actual, long long n, con
                     guda_verify_result_t* host_result, guda_stream_t stream);
 
 int guda_microbench_peak(int kind, int reps, double* value);
-/* SM cycles per warp-level shared-memory load instruction for a lane -> chunk-index pattern (width 4 / 8 / 16 bytes):
- * the wavefront cost model behind the lane layouts of the SIMT GEMM kernels. */
-int guda_microbench_lds(int width, const int* host_lane_idx, int iters, double* cycles_per_instr);
 
 /* ---- multi-GPU (new, additive: GetDeviceCount()==1 stays pinned for the single-device API, guda_test.go:332) ----
  * One process per GPU.  The communicator wraps NCCL (loaded at run time); id bytes come from
@@ -345,6 +342,8 @@ enum { GUDA_GATHER_P2P = 0, GUDA_GATHER_NCCL = 1 };
 int guda_comm_set_gather_mode(guda_comm_t comm, int mode);
 int guda_comm_get_gather_mode(guda_comm_t comm, int* mode_in_effect);
 int guda_sdot_sharded(guda_comm_t comm, int n_local, const float* x, const float* y, float* host_result, guda_stream_t stream);
+/* the same, stream-ordered: the sum lands in dev_result (device memory) on every rank and the call does not block */
+int guda_sdot_sharded_device(guda_comm_t comm, int n_local, const float* x, const float* y, float* dev_result, guda_stream_t stream);
 /* AXPY on this rank's contiguous chunk of a sharded vector (math.go:39): elementwise, no collective. */
 int guda_saxpy_sharded(guda_comm_t comm, int n_local, float alpha, const float* x, float* y, guda_stream_t stream);
 /* DGEMM twin of guda_sgemm_sharded (compute/dgemm.go:25): 2-D block partition, full K per rank (bit-identical to one GPU),

@@ -2,6 +2,9 @@
 """Turn ncu output brought back in gpurun_out/ into the tracked summaries under profiles/.
 
   python profiles/summarize.py launches <launches.csv> <out.md>       per-kernel launch list (gpu__time_duration.sum)
+  python profiles/summarize.py raw <raw.csv> <out.md> [key=regex ...]   the same from `ncu -i rep --page raw --csv` exported on the GPU box
+  python profiles/summarize.py stalls <source.csv> <out.md>             warp-state samples by reason / by opcode + the hottest non-FFMA2
+                                                                        instructions, from `ncu -i rep --page source --csv`
   python profiles/summarize.py full <report.ncu-rep> <out.md> [key=regex ...]
         one block of headline metrics per profiled launch; `key=regex` pairs also record
         dram read+write bytes per launch of the first kernel matching regex into profiles/traffic.json
@@ -65,8 +68,45 @@ def launches(csv_path, out_path):
             sum(v[0] for v in agg.values()), total / 1e6))
 
 
-def full(rep_path, out_path, pairs):
-    raw = subprocess.run(["ncu", "-i", rep_path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+def stalls(src_csv, out_path):
+    rows = list(csv.reader(open(src_csv)))
+    kernel = rows[0][1] if len(rows[0]) > 1 else ""
+    hdr, data = rows[1], rows[2:]
+    ix = {h: i for i, h in enumerate(hdr)}
+    cols = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
+    by_reason, by_op, lds = collections.Counter(), collections.Counter(), collections.Counter()
+    total, lines = 0, []
+    for r in data:
+        n = int(r[ix["# Samples"]] or 0)
+        total += n
+        src = r[ix["Source"]].strip()
+        op = (src.split()[1] if src.startswith("@") else src.split()[0]) if src else ""
+        by_op[op.split(".")[0]] += n
+        st = {c[6:]: int(r[ix[c]] or 0) for c in cols if int(r[ix[c]] or 0)}
+        for k, v in st.items():
+            by_reason[k] += v
+        if op.startswith("LDS"):
+            lds[op + " wavefronts"] += int(r[ix["L1 Wavefronts Shared"]] or 0)
+            lds[op + " instructions"] += int(r[ix["Instructions Executed"]] or 0)
+        lines.append((n, src[:70], st))
+    with open(out_path, "w") as f:
+        f.write("Source: `%s` (ncu --set full --import-source on, source page)\n\nKernel: `%s`\n\n" % (os.path.basename(src_csv), kernel[:200]))
+        f.write("%d warp-state samples.\n\n| stall reason | samples | share |\n|---|---:|---:|\n" % total)
+        for k, v in by_reason.most_common(10):
+            f.write("| %s | %d | %.1f%% |\n" % (k, v, 100.0 * v / max(total, 1)))
+        f.write("\n| opcode | samples | share |\n|---|---:|---:|\n")
+        for k, v in by_op.most_common(8):
+            f.write("| %s | %d | %.1f%% |\n" % (k, v, 100.0 * v / max(total, 1)))
+        for op in sorted({k.rsplit(" ", 1)[0] for k in lds}):
+            if lds[op + " instructions"]:
+                f.write("\n`%s`: %.2f shared-memory wavefronts per instruction (%d instructions)\n" % (op, lds[op + " wavefronts"] / lds[op + " instructions"], lds[op + " instructions"]))
+        f.write("\nHottest instructions that are not FFMA2:\n\n| samples | instruction | stall reasons |\n|---:|---|---|\n")
+        for n, src, st in sorted([l for l in lines if not l[1].startswith("FFMA2")], key=lambda l: -l[0])[:12]:
+            f.write("| %d | `%s` | %s |\n" % (n, src, ", ".join("%s %d" % kv for kv in sorted(st.items(), key=lambda kv: -kv[1])[:3])))
+
+
+def full(rep_path, out_path, pairs, raw_csv=None):
+    raw = open(raw_csv).read() if raw_csv else subprocess.run(["ncu", "-i", rep_path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
     col = {h: i for i, h in enumerate(hdr)}
@@ -118,5 +158,9 @@ if __name__ == "__main__":
         traffic(sys.argv[2], sys.argv[3], int(sys.argv[4]) if len(sys.argv) > 4 else 1)
     elif sys.argv[1] == "launches":
         launches(sys.argv[2], sys.argv[3])
+    elif sys.argv[1] == "raw":
+        full(sys.argv[2], sys.argv[3], sys.argv[4:], raw_csv=sys.argv[2])
+    elif sys.argv[1] == "stalls":
+        stalls(sys.argv[2], sys.argv[3])
     else:
         full(sys.argv[2], sys.argv[3], sys.argv[4:])

@@ -48,6 +48,40 @@ def test_sgemm_bit_exact_nn_tn_tt(g, O, m, n, k, ta, tb):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("alpha", [np.inf, -np.inf])
+@pytest.mark.parametrize("m,n,k", [(65, 67, 1), (130, 40, 2), (7, 5, 3), (65, 67, 19)])
+def test_sgemm_infinite_alpha_on_ragged_shapes(g, O, m, n, k, alpha):
+    """alpha = +-Inf on shapes that take the edge path (zero padding beyond m / n / k): the padding must stay an exact zero --
+    0 * Inf = NaN would pass the `tmp != 0` test and poison whole tiles; the reference never visits those indices."""
+    a = O.uniform_f32(m * k, 5); b = O.uniform_f32(k * n, 6); c0 = O.uniform_f32(m * n, 7)
+    got = _run_sgemm(g, 0, 0, m, n, k, float(alpha), a, k, b, n, 0.5, c0, n)
+    want = O.sgemm(0, 0, m, n, k, float(alpha), a, k, b, n, 0.5, c0.copy(), n)
+    assert np.array_equal(got, want, equal_nan=True)
+    assert not np.isfinite(want).any()
+    if k == 1:
+        assert not np.isnan(want).any()          # one term per element: +-Inf everywhere, a NaN could only come from the padding
+
+
+def test_gemm_bf16_exact_route_keeps_negative_zero_on_ragged_k(g, O):
+    """bfloat16.go:136-157 has no zero test: sum = beta*c; sum += (alpha*a)*b for the REAL k only.  With a = 0, b < 0 every product
+    is -0 and a -0 start stays -0; one extra padded step (+0 * +0) would flip it to +0."""
+    m, n, k = 5, 9, 3
+    a = O.to_bf16_fast(np.zeros(m * k, np.float32))
+    b = O.to_bf16_fast(-np.abs(O.uniform_f32(k * n, 8)) - np.float32(0.5))
+    c0 = O.to_bf16_fast(np.full(m * n, -0.0, np.float32))
+    da, db, dc = g.to_device(a), g.to_device(b), g.to_device(c0)
+    g.SetGemm16Mode(1)
+    try:
+        g.GEMMBFloat16(False, False, m, n, k, 1.0, da, k, db, n, 1.0, dc, n)
+        g.Synchronize()
+    finally:
+        g.SetGemm16Mode(0)
+    want = O.gemm_bf16(m, n, k, 1.0, a, k, b, n, 1.0, c0.copy(), n)
+    assert np.array_equal(dc.UInt16(), want) and np.all(want == 0x8000)
+    for p in (da, db, dc):
+        g.Free(p)
+
+
 @pytest.mark.parametrize("m,n,k", [(9, 7, 8), (63, 65, 64), (128, 128, 128), (257, 129, 77), (512, 512, 300)])
 def test_sgemm_nt_within_tolerance(g, O, m, n, k):
     """NotTrans x Trans is the DotUnitary form (32-lane blocked order): compared under the K-scaled GEMM tolerance.

@@ -109,6 +109,58 @@ def test_streams_and_events(g):
     g.Synchronize()
 
 
+def test_pool_reuse_is_ordered_after_work_queued_on_another_stream(g, O):
+    """Free while a kernel on stream A still writes the block, Malloc again (first fit hands the same block back), use it on
+    stream B: the pool must order the new owner after stream A's queued work (runtime.cu: an event recorded at Free, waited for
+    at reuse).  The reference's synchronous BLAS never had this window (memory.go:207-227); an asynchronous drop-in does."""
+    n = 4096
+    sa, sb = g.CreateStream(), g.CreateStream()
+    a, b = g.Malloc(n * n * 4), g.Malloc(n * n * 4)
+    g.FillUniform(a, n, n, n, 1); g.FillUniform(b, n, n, n, 2)
+    g.Synchronize()
+    for _ in range(3):
+        c = g.Malloc(n * n * 4 + 64)
+        for _ in range(4):
+            g.GEMM(False, False, n, n, n, 1.0, a, n, b, n, 0.0, c, n, stream=sa)      # ~9 ms of work writing c, queued on stream A
+        g.Free(c)                                                                   # ... and freed under it
+        q = g.Malloc(n * n * 4 + 64)
+        assert q.ptr == c.ptr                                                       # first-fit reuse, as memory.go:160-180
+        g.Memset(q, 0x5A, n * n * 4, stream=sb)                                     # the new owner runs on stream B
+        sb.Synchronize(); sa.Synchronize()
+        assert np.all(q.Byte()[:n * n * 4] == 0x5A)                                 # stream A's late writes did not land on top
+        g.Free(q)
+    for p in (a, b):
+        g.Free(p)
+    sa.Destroy(); sb.Destroy()
+    g.PoolTrim()
+
+
+def test_dot_device_results_on_many_streams_do_not_share_scratch(g, O):
+    """12 streams x 6 device-result DOTs in flight at once: each stream owns its partials and ticket counter (level1.cu), so every
+    result equals the deterministic single-stream value bit for bit."""
+    n = (1 << 20) + 77
+    L = g.load()
+    xs = [g.to_device(O.uniform_f32(n, 300 + i)) for i in range(3)]
+    ys = [g.to_device(O.uniform_f32(n, 400 + i)) for i in range(3)]
+    want = [np.float32(g.DOT(xs[i], ys[i], n)) for i in range(3)]
+    streams = [g.CreateStream() for _ in range(12)]
+    outs = g.Malloc(12 * 6 * 4)
+    for rep in range(6):
+        for si, st in enumerate(streams):
+            i = (si + rep) % 3
+            g.capi.check(L.guda_sdot_device(n, xs[i].ptr, 1, ys[i].ptr, 1, outs.ptr + 4 * (si * 6 + rep), st.handle), "SdotDevice")
+    for st in streams:
+        st.Synchronize()
+    got = outs.Float32()[:72].reshape(12, 6)
+    for si in range(12):
+        for rep in range(6):
+            assert got[si, rep].view(np.uint32) == want[(si + rep) % 3].view(np.uint32), (si, rep)
+    for st in streams:
+        st.Destroy()
+    for p in xs + ys + [outs]:
+        g.Free(p)
+
+
 # ------------------------------------------------------------------ Level 1 fp32
 @pytest.mark.parametrize("n", [1, 3, 31, 32, 33, 1000, 1024, 4097, 1 << 20, (1 << 20) + 5])
 def test_axpy_bit_exact(g, O, n):

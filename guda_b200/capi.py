@@ -85,6 +85,7 @@ SIGNATURES = {
     "guda_sscal": (i, [i, f, vp, i, vp]),
     "guda_sdot": (i, [i, vp, i, vp, i, fp, vp]),
     "guda_sdot_device": (i, [i, vp, i, vp, i, vp, vp]),
+    "guda_sdot_device_static": (i, [i, vp, i, vp, i, vp, vp]),     # no allocation on the call path (no reference counterpart)
     "guda_daxpy": (i, [i, d, vp, i, vp, i, vp]),
     "guda_dscal": (i, [i, d, vp, i, vp]),
     "guda_ddot": (i, [i, vp, i, vp, i, dp, vp]),

@@ -31,6 +31,7 @@ int map_cuda_error(cudaError_t e);
 int bind_device();
 int current_device();
 int sm_count();
+bool runtime_inited();       // true once guda_init (or the first ordinary call) has set the library up; never initialises
 
 struct Stream { cudaStream_t s; };
 struct Event { cudaEvent_t e; };

@@ -441,6 +441,94 @@ static int dot_impl(int n, const T* x, int incx, const T* y, int incy, T* host_r
   return GUDA_OK;
 }
 
+// ---------------------------------------------------------------- DOT with no allocation anywhere on the call path
+// No counterpart in the reference: added for callers that cannot allocate (CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  Same kernel as guda_sdot_device; its scratch -- one fp32
+// partial per CTA and the ticket counter -- lives in a file-scope __device__ array instead of the per-stream DotSlot that
+// dot_slot_for() cudaMallocs on first use.  Every GPU that loads the library holds these 4352 bytes until exit.  In host code
+// the array's NAME is a host-side stand-in, not a device address: the device address is resolved with cudaGetSymbolAddress, once
+// per device, with that device current, and that pointer is what the kernel gets.  All calls on a device share the array: the
+// ticket is cleared (stream-ordered) before every launch, partials are fully rewritten by every launch, and calls that OVERLAP on
+// the GPU (different streams, or several host threads on different streams) race on it -- callers serialise them on one stream.
+constexpr int DOT_STATIC_MAX_PARTIALS = 1024;                                        // grid is min(one wave, this)
+constexpr size_t DOT_STATIC_COUNTER_OFF = DOT_STATIC_MAX_PARTIALS * sizeof(float);     // the ticket gets a 256-byte line of its own
+constexpr size_t DOT_STATIC_BYTES = DOT_STATIC_COUNTER_OFF + 256;
+static __device__ __align__(256) unsigned char g_dot_static_scratch[DOT_STATIC_BYTES];
+constexpr int DOT_STATIC_MAX_DEVICES = 64;
+static std::mutex g_dot_static_mu;
+static unsigned char* g_dot_static_ptr[DOT_STATIC_MAX_DEVICES];                        // device address of the array, per device ordinal
+
+static int dot_static_scratch(unsigned char** out) {
+  int dev = -1;
+  GUDA_CUDA(cudaGetDevice(&dev));                           // bind_device() has made the library's device current on this thread
+  if (dev < 0 || dev >= DOT_STATIC_MAX_DEVICES) return set_error(GUDA_ERR_DEVICE, "Sdot (static scratch): device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_dot_static_mu);
+  if (!g_dot_static_ptr[dev]) {
+    unsigned char* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_dot_static_scratch);
+    if (e != cudaSuccess || !ptr)
+      return set_error(GUDA_ERR_DEVICE, "Sdot (static scratch): cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    g_dot_static_ptr[dev] = ptr;
+  }
+  *out = g_dot_static_ptr[dev];
+  return GUDA_OK;
+}
+
+static int sdot_static_impl(int n, const float* x, int incx, const float* y, int incy, float* dev_result, guda_stream_t stream) {
+  const char* op = "Sdot (static scratch)";
+  if (incx == 0) GUDA_PANIC("blas: zero x index increment");
+  if (incy == 0) GUDA_PANIC("blas: zero y index increment");
+  if (n < 0) GUDA_PANIC("blas: n < 0");
+  if (n > GUDA_SDOT_STATIC_MAX_N)
+    return set_error(GUDA_ERR_INVALID_ARG, "%s: n = %d exceeds the maximum of %d elements this entry point accepts", op, n, GUDA_SDOT_STATIC_MAX_N);
+  if (!runtime_inited())                                    // initialising allocates (runtime.cu init_locked); this call must not
+    return set_error(GUDA_ERR_INVALID_ARG, "%s: library not initialised -- call guda_init first (this entry point allocates nothing, "
+                                           "so it cannot set the library up itself)", op);
+  int rc = bind_device();
+  if (rc) return rc;
+  cudaStream_t s = native(stream);
+  if (n == 0) {
+    GUDA_CUDA(cudaMemsetAsync(dev_result, 0, sizeof(float), s));          // level1float32_sdot.go:25-30: returns 0
+    return GUDA_OK;
+  }
+  if (!x || !y) return set_error(GUDA_ERR_INVALID_ARG, "%s: null pointer", op);
+  const size_t N = (size_t)n;
+  const float* xs = x; const float* ys = y;
+  if (incx < 0) xs = x + (long long)(-n + 1) * incx;
+  if (incy < 0) ys = y + (long long)(-n + 1) * incy;
+  bool unit = (incx == 1 && incy == 1);
+  size_t head = 0;
+  if (unit) {
+    if ((((uintptr_t)x ^ (uintptr_t)y) & 15) == 0 && ((uintptr_t)x % sizeof(float)) == 0) {
+      head = head_elems<float>(x);
+      if (head > N) head = N;
+    } else {
+      unit = false;
+    }
+  }
+  const size_t work = unit ? (N / Vec<float>::N + (size_t)L1_THREADS * L1_UNROLL - 1) / ((size_t)L1_THREADS * L1_UNROLL)
+                           : (N + L1_THREADS - 1) / L1_THREADS;
+  static int occ = 0;
+  if (occ == 0) {
+    int o = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dot_kernel<float>, L1_THREADS, 0) != cudaSuccess || o < 1) o = 2;
+    occ = o > 4 ? 4 : o;
+  }
+  size_t grid = work;
+  const size_t wave = (size_t)sm_count() * (size_t)occ;
+  if (grid > wave) grid = wave;
+  if (grid > (size_t)DOT_STATIC_MAX_PARTIALS) grid = DOT_STATIC_MAX_PARTIALS;
+  if (grid == 0) grid = 1;
+  unsigned char* scratch = nullptr;
+  if ((rc = dot_static_scratch(&scratch))) return rc;
+  float* partials = reinterpret_cast<float*>(scratch);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(scratch + DOT_STATIC_COUNTER_OFF);
+  GUDA_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), s));        // the array keeps the last call's contents: the ticket must start at 0
+  dot_kernel<float><<<(unsigned)grid, L1_THREADS, 0, s>>>(N, xs, (long long)(unit ? 1 : incx), ys, (long long)(unit ? 1 : incy), head, partials,
+                                                           counter, (float*)nullptr, dev_result);
+  return check_launch(op);
+}
+
 }  // namespace guda
 
 using namespace guda;
@@ -468,5 +556,9 @@ int guda_ddot(int n, const double* x, int incx, const double* y, int incy, doubl
 int guda_ddot_device(int n, const double* x, int incx, const double* y, int incy, double* dev_result, guda_stream_t stream) {
   if (!dev_result) return set_error(GUDA_ERR_INVALID_ARG, "Ddot: null result pointer");
   return dot_impl<double>(n, x, incx, y, incy, nullptr, dev_result, stream, "Ddot");
+}
+int guda_sdot_device_static(int n, const float* x, int incx, const float* y, int incy, float* dev_result, guda_stream_t stream) {
+  if (!dev_result) return set_error(GUDA_ERR_INVALID_ARG, "Sdot (static scratch): null result pointer");
+  return sdot_static_impl(n, x, incx, y, incy, dev_result, stream);
 }
 }

@@ -101,6 +101,7 @@ int bind_device() {
   return GUDA_OK;
 }
 int current_device() { return st().device; }
+bool runtime_inited() { return st().inited; }
 int sm_count() { return st().sms; }
 cudaStream_t native(guda_stream_t h) { return h ? reinterpret_cast<Stream*>(h)->s : st().default_stream.s; }
 int get_scratch(Scratch** out) { *out = &st().scratch; return GUDA_OK; }

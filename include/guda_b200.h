@@ -98,6 +98,18 @@ int guda_saxpy(int n, float alpha, const float* x, int incx, float* y, int incy,
 int guda_sscal(int n, float alpha, float* x, int incx, guda_stream_t stream);
 int guda_sdot(int n, const float* x, int incx, const float* y, int incy, float* host_result, guda_stream_t stream);
 int guda_sdot_device(int n, const float* x, int incx, const float* y, int incy, float* dev_result, guda_stream_t stream);
+/* guda_sdot_device with NO allocation anywhere on the call path.  It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernel and arithmetic as guda_sdot_device; the kernel's scratch (one fp32 partial per
+ * CTA + the ticket counter, 4352 bytes) is a file-scope __device__ array that every GPU loading the library holds until exit,
+ * instead of the per-stream buffers the ordinary entry points cudaMalloc on first use.  Limits and rules:
+ *   - n <= GUDA_SDOT_STATIC_MAX_N, otherwise GUDA_ERR_INVALID_ARG ("... exceeds the maximum ...") and nothing is launched;
+ *   - the library must already be initialised (guda_init allocates; this call will not): GUDA_ERR_INVALID_ARG otherwise;
+ *   - x, y and dev_result are the caller's device buffers; the result is stream-ordered on `stream`, never copied to the host;
+ *   - all calls on a device share the one scratch array (the ticket is cleared before every launch): calls that overlap on the
+ *     GPU -- different streams -- race on it and return garbage.  Serialise them on one stream. */
+#define GUDA_SDOT_STATIC_MAX_N (1 << 28)   /* elements per operand = the reference's own cap on an fp32 DevicePtr view (memory.go:250) */
+int guda_sdot_device_static(int n, const float* x, int incx, const float* y, int incy, float* dev_result, guda_stream_t stream);
 /* ---- Level 1, fp64: compute/level1float64.go:211,595, level1float64_ddot.go:14 ---- */
 int guda_daxpy(int n, double alpha, const double* x, int incx, double* y, int incy, guda_stream_t stream);
 int guda_dscal(int n, double alpha, double* x, int incx, guda_stream_t stream);

@@ -360,6 +360,20 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     tf = 2.0 * n ** 3 / (ms * 1e-3) / 1e12
     out["sgemm_1024"] = {"value": tf, "unit": "TFLOP/s", "ms": ms, "roofline": {"bound": "fp32_simt", "achieved": tf, "peak": ffma_peak,
                          "unit": "TFLOP/s", "frac": tf / ffma_peak, "peak_source": "FFMA microbenchmark, this run"}}
+    # the same call in the opt-in 3xTF32 math mode (stated tolerance, not the reference's bits: tests/test_gpu_tensor.py), for scale
+    g.SetSgemmMode(1)
+    try:
+        for _ in range(5):
+            sg()
+        ms3 = dev.time_ms(sg, 50)
+    finally:
+        g.SetSgemmMode(0)
+    tf3 = 2.0 * n ** 3 / (ms3 * 1e-3) / 1e12
+    tpeak3 = peaks["bf16_tflops"] / 2.0 / 3.0
+    out["sgemm_1024_3xtf32"] = {"value": tf3, "unit": "TFLOP/s", "ms": ms3, "includes": "hi/lo split pre-pass + pool traffic",
+                                "math": "3xTF32 split on tcgen05 (opt-in, abs(delta) <= 8*K*u*sum|a||b|); NOT bit-identical to the reference",
+                                "roofline": {"bound": "tensor", "achieved": tf3, "peak": tpeak3, "unit": "TFLOP/s", "frac": tf3 / tpeak3,
+                                             "peak_source": "MEASURED_PEAKS.json bf16 burst / 2 (tf32 rate) / 3 (three MMAs per product)"}}
     for a, b, c in sets:
         g.Free(a); g.Free(b); g.Free(c)
 

@@ -253,8 +253,18 @@ __global__ void __launch_bounds__(L1_THREADS, 4) dot_kernel(size_t n, const T* _
   __syncthreads();
   if (is_last) {
     // deterministic final pass: thread t sums partials t, t+256, ... then the same block tree
+    // (up to four partials per thread are requested before the first add: one L2 round trip on the tail instead of one per partial)
     T v = T(0);
-    for (unsigned int i = threadIdx.x; i < gridDim.x; i += L1_THREADS) v = add_t(v, __ldcg(partials + i));
+    for (unsigned int base = threadIdx.x; base < gridDim.x; base += 4 * L1_THREADS) {
+      T p[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const unsigned int i = base + j * L1_THREADS;
+        p[j] = i < gridDim.x ? __ldcg(partials + i) : T(0);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) v = add_t(v, p[j]);
+    }
     v = warp_sum(v);
     if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = v;
     __syncthreads();
@@ -272,6 +282,15 @@ __global__ void __launch_bounds__(L1_THREADS, 4) dot_kernel(size_t n, const T* _
 }
 
 // ---------------------------------------------------------------- host side
+// Grid of the persistent DOT wave: at most `wave` CTAs, and as few idle chunk slots in the last round as possible -- with
+// `rounds` = ceil(work / wave) every CTA walks `rounds` chunks except for a remainder smaller than `rounds` (2^24 floats: 4096
+// chunks on a 592-CTA wave = 7 rounds; 586 CTAs x 7 = 4102 slots instead of 592 x 7 = 4144).
+static inline size_t dot_grid(size_t work, size_t wave) {
+  if (work <= wave) return work ? work : 1;
+  const size_t rounds = (work + wave - 1) / wave;
+  return (work + rounds - 1) / rounds;
+}
+
 template <typename T> static size_t head_elems(const void* p) {
   uintptr_t mis = (uintptr_t)p & 15;
   return mis ? (16 - mis) / sizeof(T) : 0;
@@ -420,8 +439,7 @@ static int dot_impl(int n, const T* x, int incx, const T* y, int incy, T* host_r
     occ = o;
   }
   unsigned wave = (unsigned)sm_count() * (unsigned)occ;
-  if (grid > wave) grid = wave;
-  if (grid == 0) grid = 1;
+  grid = (unsigned)dot_grid(work, wave);
   DotSlot slot;
   if ((rc = dot_slot_for(s, &slot))) return rc;
   T* partials = reinterpret_cast<T*>(slot.partials);                      // 8 KiB >= 592 partials of 8 bytes
@@ -514,11 +532,9 @@ static int sdot_static_impl(int n, const float* x, int incx, const float* y, int
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dot_kernel<float>, L1_THREADS, 0) != cudaSuccess || o < 1) o = 2;
     occ = o > 4 ? 4 : o;
   }
-  size_t grid = work;
-  const size_t wave = (size_t)sm_count() * (size_t)occ;
-  if (grid > wave) grid = wave;
-  if (grid > (size_t)DOT_STATIC_MAX_PARTIALS) grid = DOT_STATIC_MAX_PARTIALS;
-  if (grid == 0) grid = 1;
+  size_t wave = (size_t)sm_count() * (size_t)occ;
+  if (wave > (size_t)DOT_STATIC_MAX_PARTIALS) wave = DOT_STATIC_MAX_PARTIALS;
+  const size_t grid = dot_grid(work, wave);
   unsigned char* scratch = nullptr;
   if ((rc = dot_static_scratch(&scratch))) return rc;
   float* partials = reinterpret_cast<float*>(scratch);

@@ -10,7 +10,7 @@
 //   Max / Min                : bit-exact, including NaN and signed-zero behaviour.  VMAXPS/VMINPS return the SECOND operand unless
 //       the first is strictly greater (smaller), so a NaN is forgotten by the next number in its AVX lane and +-0 ties go to the
 //       later element -- order-dependent, but only then.  One streaming pass computes the plain extreme plus a saw-a-NaN flag; when
-//       there was no NaN and the extreme is not zero the plain extreme IS the reference's result (a unique bit pattern).  Otherwise
+//       there was no NaN and the extreme is not a zero tie (+0 and -0 both present) the plain extreme IS the reference's result.  Otherwise
 //       (rare) an exact kernel replays the 8-lane fold with an ordered, associative segment summary
 //       {EMPTY | NONAN v | HASNAN v} (v = fold of the elements after the segment's last NaN).
 //   Sum / SumSquares         : fp32 pairwise tree (more accurate than the reference's 16 / 8 sequential lanes), deterministic for a
@@ -29,7 +29,7 @@ enum RedOp { RED_SUM = 0, RED_SUMSQ, RED_MAX, RED_MIN, RED_ARGMAX, RED_ARGMIN, R
 
 struct __align__(16) RedResult {
   float v;              // value (sum, extreme, or the extreme's value for arg ops)
-  unsigned flags;       // bit 0: a NaN was seen (Max / Min)
+  unsigned flags;       // Max / Min: bit 0 a NaN was seen, bit 1 a +0 was seen, bit 2 a -0 was seen
   long long idx;        // index (arg ops)
 };
 
@@ -70,9 +70,11 @@ __device__ __forceinline__ void red_elem(RedState<OP>& s, float e, long long i) 
   if constexpr (OP == RED_MAX) {
     if (e != e) s.flags |= 1u;
     else if (e > s.v) s.v = e;
+    if (e == 0.0f) s.flags |= 2u << (__float_as_uint(e) >> 31);       // bit 1: saw +0, bit 2: saw -0
   } else if constexpr (OP == RED_MIN) {
     if (e != e) s.flags |= 1u;
     else if (e < s.v) s.v = e;
+    if (e == 0.0f) s.flags |= 2u << (__float_as_uint(e) >> 31);
   } else if constexpr (OP == RED_ARGMAX) {
     if (e > s.v) { s.v = e; s.idx = i; }
   } else if constexpr (OP == RED_ARGMIN) {
@@ -366,7 +368,9 @@ static int launch_reduce(size_t n, const float* x, long long incx, RedResult* ho
   GUDA_CUDA(cudaStreamSynchronize(s));
   host_out->v = host_alias->v; host_out->flags = host_alias->flags; host_out->idx = host_alias->idx;
   if (OP == RED_MAX || OP == RED_MIN) {
-    if ((host_out->flags & 1u) || host_out->v == 0.0f) {          // NaN seen or a possible +-0 tie: replay the reference's order
+    // replay the reference's order only when it can matter: a NaN was seen, or the extreme is a zero AND both signs of zero occur
+    // (a vector holding only +0 -- any post-ReLU tensor's Min -- or only -0 has one possible answer, the streaming pass's)
+    if ((host_out->flags & 1u) || (host_out->v == 0.0f && (host_out->flags & 6u) == 6u)) {
       if (OP == RED_MAX) minmax_exact_kernel<true><<<1, MM_THREADS, 0, s>>>(n, x, dev_alias);
       else minmax_exact_kernel<false><<<1, MM_THREADS, 0, s>>>(n, x, dev_alias);
       rc = check_launch(what);

@@ -73,7 +73,7 @@ def test_ties_pick_the_first_index(g, O, n):
 @pytest.mark.parametrize("n", [1, 7, 8, 9, 17, 100, 1001, 70001, 1 << 20])
 def test_nan_and_signed_zero_follow_the_avx2_kernels(g, O, n):
     rng = np.random.default_rng(7 * n + 1)
-    for trial in range(6):
+    for trial in range(8):
         x = rng.standard_normal(n).astype(np.float32)
         if trial in (0, 1, 2):
             x[rng.integers(0, n, max(1, n // 7))] = np.nan
@@ -87,6 +87,10 @@ def test_nan_and_signed_zero_follow_the_avx2_kernels(g, O, n):
             x[:] = np.nan
         if trial == 5:
             x = -np.abs(x); x[rng.integers(0, n, max(1, n // 3))] = np.where(rng.random(max(1, n // 3)) < 0.5, 0.0, -0.0)   # max is +-0
+        if trial == 6:
+            x = np.maximum(x, np.float32(0.0))               # post-ReLU: the Min is +0 and no -0 exists -> no replay needed, same bits
+        if trial == 7:
+            x = -np.abs(x); x[rng.integers(0, n, max(1, n // 3))] = np.float32(-0.0)          # the Max is -0 and no +0 exists
         d = g.to_device(x)
         assert same_bits(d.Max(n), O.smax(x)), (n, trial)
         assert same_bits(d.Min(n), O.smin(x)), (n, trial)

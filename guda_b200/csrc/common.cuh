@@ -93,8 +93,9 @@ struct PoolTemp {
 };
 
 // two library-lifetime non-blocking streams for copies pipelined under compute (host_gemm.cu)
-int aux_copy_streams(cudaStream_t* in, cudaStream_t* out);
+int aux_copy_streams(cudaStream_t* in, cudaStream_t* out, cudaStream_t* in2 = nullptr);
 // K boundaries of the host-operand pipeline (short first chunk, then 8192-deep)
 void host_k_chunks(int k, std::vector<int>& bounds);
+int host_c_panels(int m);
 
 }  // namespace guda

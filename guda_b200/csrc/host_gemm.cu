@@ -16,34 +16,50 @@ namespace guda {
 
 constexpr int HG_KC = 8192;          // = the device path's K block (gemm.cu KChunk<float>): each chunk is a single launch
 
-struct HgStreams { cudaStream_t in = nullptr, out = nullptr; };
+struct HgStreams { cudaStream_t in = nullptr, in2 = nullptr, out = nullptr; };
 static int hg_streams(HgStreams** o) {
   static HgStreams st;
   if (!st.in) {
-    GUDA_CUDA(cudaStreamCreateWithFlags(&st.in, cudaStreamNonBlocking));
-    GUDA_CUDA(cudaStreamCreateWithFlags(&st.out, cudaStreamNonBlocking));
+    // Highest priority: what runs on these streams besides copies is the NVLink broadcast of the sharded host step (an NCCL kernel).
+    // The GEMM launches fill every SM (4 CTAs x 126 registers x 128 threads), and at equal priority a waiting kernel only gets CTA
+    // slots when the running grid has none left to issue -- one broadcast per GEMM launch boundary, which starved the upload
+    // pipeline at 8 GPUs.  At higher priority its few CTAs take the first slots a retiring GEMM CTA frees (every ~0.1 ms).
+    int least = 0, greatest = 0;
+    GUDA_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    GUDA_CUDA(cudaStreamCreateWithPriority(&st.in, cudaStreamNonBlocking, greatest));
+    GUDA_CUDA(cudaStreamCreateWithPriority(&st.in2, cudaStreamNonBlocking, greatest));
+    GUDA_CUDA(cudaStreamCreateWithPriority(&st.out, cudaStreamNonBlocking, greatest));
   }
   *o = &st;
   return GUDA_OK;
 }
 
-// K-chunk schedule: a short first chunk (its upload is the only one nothing can hide), then up to the next multiple of HG_KC, then
-// HG_KC-deep chunks.  Any split keeps the bits: every chunk resumes the same FMA chains.
+// K-chunk schedule: a short first chunk (its upload is the only one nothing can hide), then doubling depths up to HG_KC, then
+// HG_KC-deep chunks: 0, 512, 1024, 2048, 4096, 8192, 16384, ...  Chunk j+1 uploads under chunk j's GEMM, so its depth may exceed
+// chunk j's only by the ratio of GEMM time to upload time per unit of k -- about 13 on one GPU, but only 2-3 at 8 GPUs, where a
+// rank's GEMM share is 1/8 while the rank that uploads a shared A row panel still moves half of A (round 2's 1024 -> 8192 jump left
+// the 8-GPU GEMM waiting ~40 ms for its second chunk).  Any split keeps the bits: every chunk resumes the same FMA chains.
 void host_k_chunks(int k, std::vector<int>& bounds) {
   bounds.clear();
   bounds.push_back(0);
-  if (k > 2 * HG_KC) { bounds.push_back(HG_KC / 8); bounds.push_back(HG_KC); }
-  else if (k > HG_KC) bounds.push_back(HG_KC / 8);
-  for (int b = bounds.back() + HG_KC; b < k; b += HG_KC) bounds.push_back(b);
+  if (k > HG_KC)
+    for (int b = HG_KC / 16; b < HG_KC && b < k; b *= 2) bounds.push_back(b);
+  for (int b = HG_KC; b < k; b += HG_KC) bounds.push_back(b);
   bounds.push_back(k);
+  // The LAST chunk is the only one whose results are final, so the download of C can only hide under it: make it two blocks deep
+  // (8 GPUs: each rank's 2 GiB block leaves at ~12 GB/s when all eight write host memory at once, 175 ms against 130 ms of GEMM per
+  // 8192-deep chunk -- the trace showed the step ending 40-75 ms after its last kernel).
+  if (bounds.size() >= 5 && bounds[bounds.size() - 2] >= 2 * HG_KC) bounds.erase(bounds.end() - 2);
 }
+int host_c_panels(int m) { return m >= 16384 ? 16 : (m >= 2048 ? 8 : 1); }   // row panels of the last chunk: the last panel's download is the exposed tail
 
-int aux_copy_streams(cudaStream_t* in, cudaStream_t* out) {
+int aux_copy_streams(cudaStream_t* in, cudaStream_t* out, cudaStream_t* in2) {
   HgStreams* st;
   int rc = hg_streams(&st);
   if (rc) return rc;
   *in = st->in;
   *out = st->out;
+  if (in2) *in2 = st->in2;
   return GUDA_OK;
 }
 
@@ -139,7 +155,7 @@ extern "C" int guda_sgemm_host(int ta, int tb, int m, int n, int k, float alpha,
       continue;
     }
     // last (or only) chunk: row panels, each copied out as soon as it is finished
-    int panels = m >= 2048 ? 8 : 1;
+    int panels = host_c_panels(m);
     int pm = ((m + panels - 1) / panels + 127) / 128 * 128;
     for (int r0 = 0; r0 < m; r0 += pm) {
       const int pr = m - r0 < pm ? m - r0 : pm;

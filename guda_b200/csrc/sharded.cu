@@ -3,6 +3,7 @@
 // (dlopen) so the library has no link-time NCCL dependency and single-GPU users never touch it.
 // The reference has no multi-device notion at all (guda.go:227-229 GetDeviceCount() == 1).
 #include "common.cuh"
+#include <string>
 #include <cuda.h>
 #include <dlfcn.h>
 #include <nccl.h>
@@ -378,18 +379,23 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
     return set_error(GUDA_ERR_INVALID_ARG, "sgemm_sharded_host: null pointer");
   int rc = bind_device();
   if (rc) return rc;
-  cudaStream_t s = native(stream), s_in, s_out;
-  if ((rc = aux_copy_streams(&s_in, &s_out))) return rc;
+  cudaStream_t s = native(stream), s_in, s_in2, s_out;             // s_in carries the A chunks, s_in2 the B chunks
+  if ((rc = aux_copy_streams(&s_in, &s_out, &s_in2))) return rc;
   std::vector<cudaEvent_t> evs;
+  // GUDA_HOST_STEP_TRACE=1: events carry timestamps and every rank prints, per K chunk, when its operands were on the device and when
+  // its GEMM finished (ms from the start of the step) -- the tool that shows whether the GEMM ever waits for the upload pipeline
+  static const bool trace = [] { const char* e = getenv("GUDA_HOST_STEP_TRACE"); return e && atoi(e) != 0; }();
   auto new_event = [&](cudaEvent_t* e) -> int {
-    GUDA_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    GUDA_CUDA(cudaEventCreateWithFlags(e, trace ? cudaEventDefault : cudaEventDisableTiming));
     evs.push_back(*e);
     return GUDA_OK;
   };
+  std::vector<cudaEvent_t> tr_in, tr_done;
   cudaEvent_t e0;
   if ((rc = new_event(&e0))) return rc;
   GUDA_CUDA(cudaEventRecord(e0, s));
   GUDA_CUDA(cudaStreamWaitEvent(s_in, e0, 0));
+  GUDA_CUDA(cudaStreamWaitEvent(s_in2, e0, 0));
   std::vector<int> kb;
   host_k_chunks(k, kb);
   const int nk = (int)kb.size() - 1;
@@ -403,8 +409,13 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
   if (c->nranks > 1 && (c->grid_pr != pr || c->grid_pc != pc)) {
     if (c->row_comm) { g_nccl.CommDestroy(c->row_comm); c->row_comm = nullptr; }
     if (c->col_comm) { g_nccl.CommDestroy(c->col_comm); c->col_comm = nullptr; }
-    if (pc > 1) GUDA_NCCL(g_nccl.CommSplit(c->comm, gr, gc, &c->row_comm, nullptr));
-    if (pr > 1) GUDA_NCCL(g_nccl.CommSplit(c->comm, pr + gc, gr, &c->col_comm, nullptr));
+    // The broadcasts run under a GEMM that owns every SM, and a rank that only receives sits in its broadcast kernel while the
+    // root is still uploading: keep those kernels to a few CTAs (they need ~10 GB/s, not the link rate).  GUDA_BCAST_CTAS overrides.
+    ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+    static const int bcast_ctas = [] { const char* e = getenv("GUDA_BCAST_CTAS"); return e ? atoi(e) : 4; }();
+    if (bcast_ctas > 0) { cfg.minCTAs = 1; cfg.maxCTAs = bcast_ctas; }
+    if (pc > 1) GUDA_NCCL(g_nccl.CommSplit(c->comm, gr, gc, &c->row_comm, &cfg));
+    if (pr > 1) GUDA_NCCL(g_nccl.CommSplit(c->comm, pr + gc, gr, &c->col_comm, &cfg));
     c->grid_pr = pr; c->grid_pc = pc;
   }
   const int a_root = gr % pc, b_root = (gc + 1) % pr;            // rank inside row_comm / col_comm that uploads the shared panel
@@ -420,16 +431,25 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
     if (c->row_comm) GUDA_NCCL(g_nccl.Broadcast(a_chunk, a_chunk, (size_t)m_loc * kc, ncclFloat, a_root, c->row_comm, s_in));
     if (b_owner)
       GUDA_CUDA(cudaMemcpy2DAsync(b_chunk, (size_t)n_loc * 4, host_b_panel + (size_t)k0 * ldb, (size_t)ldb * 4, (size_t)n_loc * 4, kc,
-                                  cudaMemcpyHostToDevice, s_in));
-    if (c->col_comm) GUDA_NCCL(g_nccl.Broadcast(b_chunk, b_chunk, (size_t)kc * n_loc, ncclFloat, b_root, c->col_comm, s_in));
-    cudaEvent_t e_in;
-    if ((rc = new_event(&e_in))) break;
+                                  cudaMemcpyHostToDevice, s_in2));
+    if (c->col_comm) GUDA_NCCL(g_nccl.Broadcast(b_chunk, b_chunk, (size_t)kc * n_loc, ncclFloat, b_root, c->col_comm, s_in2));
+    cudaEvent_t e_in, e_in_b;                                       // the two operand streams never wait for each other
+    if ((rc = new_event(&e_in)) || (rc = new_event(&e_in_b))) break;
     GUDA_CUDA(cudaEventRecord(e_in, s_in));
+    GUDA_CUDA(cudaEventRecord(e_in_b, s_in2));
     GUDA_CUDA(cudaStreamWaitEvent(s, e_in, 0));
+    GUDA_CUDA(cudaStreamWaitEvent(s, e_in_b, 0));
+    if (trace) { tr_in.push_back(e_in); tr_in.push_back(e_in_b); }
     const float bj = j == 0 ? 0.0f : 1.0f;
-    if (j + 1 < nk)
+    if (j + 1 < nk) {
       rc = guda_sgemm(0, 0, m_loc, n_loc, kc, alpha, a_chunk, kc, b_chunk, n_loc, bj, c_block_dev, n_loc, stream);
-    else {
+      if (trace && !rc) {
+        cudaEvent_t e_done;
+        if ((rc = new_event(&e_done))) break;
+        GUDA_CUDA(cudaEventRecord(e_done, s));
+        tr_done.push_back(e_done);
+      }
+    } else {
       // last chunk.  Fused route: the GEMM + all-gather launch is cut into row panels so that each finished panel of this rank's
       // block streams back to the host while the next one computes; otherwise the generic step, then one download.
       bool fused = false;
@@ -447,7 +467,7 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
       }
       GUDA_CUDA(cudaStreamWaitEvent(s_out, e0, 0));
       const int r = c->rank / pc, q = c->rank % pc;
-      const int panels = m_loc >= 2048 ? 8 : 1;
+      const int panels = host_c_panels(m_loc);
       const int pm = ((m_loc + panels - 1) / panels + 127) / 128 * 128;
       for (int p0 = 0; p0 < m_loc && !rc; p0 += pm) {
         const int ph = m_loc - p0 < pm ? m_loc - p0 : pm;
@@ -479,6 +499,24 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
                                        cudaMemcpyDeviceToHost, s);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
     if (ce != cudaSuccess) rc = set_error(map_cuda_error(ce), "sgemm_sharded_host: %s", cudaGetErrorString(ce));
+  }
+  if (trace && !rc) {
+    cudaEvent_t e_end;
+    if (!new_event(&e_end) && cudaEventRecord(e_end, s) == cudaSuccess && cudaEventSynchronize(e_end) == cudaSuccess) {
+      std::string line = "[guda host step] rank " + std::to_string(c->rank) + " k-bounds/in/done ms:";
+      for (size_t j = 0; 2 * j + 1 < tr_in.size(); j++) {
+        float t_a = 0, t_b = 0, t_done = 0;
+        cudaEventElapsedTime(&t_a, e0, tr_in[2 * j]);
+        cudaEventElapsedTime(&t_b, e0, tr_in[2 * j + 1]);
+        if (j < tr_done.size()) cudaEventElapsedTime(&t_done, e0, tr_done[j]);
+        char buf[96];
+        snprintf(buf, sizeof buf, " %d:A%.1f,B%.1f/%.1f", kb[j + 1], t_a, t_b, t_done);
+        line += buf;
+      }
+      float t_end = 0;
+      cudaEventElapsedTime(&t_end, e0, e_end);
+      fprintf(stderr, "%s end %.1f\n", line.c_str(), t_end);
+    }
   }
   for (cudaEvent_t e : evs) cudaEventDestroy(e);
   return rc;

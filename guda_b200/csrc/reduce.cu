@@ -145,6 +145,9 @@ __global__ void __launch_bounds__(RED_THREADS, 4) reduce_kernel(size_t n, const 
 #pragma unroll
     for (int j = 0; j < 4; j++) acc[u][j] = 0.0f;
 
+  // Max / Min, vector path: umin == 0 <=> a +0 occurred; smin == INT_MIN <=> a -0; smax > 0x7F800000 or umax > 0xFF800000 <=> a NaN
+  unsigned bits_umin = 0xFFFFFFFFu, bits_umax = 0u;
+  int bits_smin = 0x7FFFFFFF, bits_smax = (int)0x80000000;
   if (incx == 1) {
     const size_t nvec = (n - head) / 4;
     const float4* xv = reinterpret_cast<const float4*>(x + head);
@@ -167,6 +170,17 @@ __global__ void __launch_bounds__(RED_THREADS, 4) reduce_kernel(size_t n, const 
           } else if constexpr (OP == RED_SUMSQ) {
 #pragma unroll
             for (int j = 0; j < 4; j++) acc[u][j] = __fmaf_rn(e[j], e[j], acc[u][j]);
+          } else if constexpr (OP == RED_MAX || OP == RED_MIN) {
+            // branch-free: the extreme with NaN-ignoring max/min, and the three facts the host needs (a NaN, a +0, a -0 occurred)
+            // as four integer extremes of the bit patterns -- independent accumulators instead of one compare/select chain, so the
+            // arithmetic between two batches of loads stays short (this kernel is one load batch per iteration: latency-bound)
+            const unsigned* b = reinterpret_cast<const unsigned*>(&r[u]);
+            if constexpr (OP == RED_MAX) s.v = fmaxf(s.v, fmaxf(fmaxf(e[0], e[1]), fmaxf(e[2], e[3])));
+            else s.v = fminf(s.v, fminf(fminf(e[0], e[1]), fminf(e[2], e[3])));
+            bits_umin = min(bits_umin, min(min(b[0], b[1]), min(b[2], b[3])));
+            bits_umax = max(bits_umax, max(max(b[0], b[1]), max(b[2], b[3])));
+            bits_smin = min(bits_smin, min(min((int)b[0], (int)b[1]), min((int)b[2], (int)b[3])));
+            bits_smax = max(bits_smax, max(max((int)b[0], (int)b[1]), max((int)b[2], (int)b[3])));
           } else {
             const long long i0 = (long long)(head + 4 * i);
 #pragma unroll
@@ -197,6 +211,12 @@ __global__ void __launch_bounds__(RED_THREADS, 4) reduce_kernel(size_t n, const 
 #pragma unroll
     for (int u = 0; u < RED_UNROLL; u++) t = __fadd_rn(t, __fadd_rn(__fadd_rn(acc[u][0], acc[u][1]), __fadd_rn(acc[u][2], acc[u][3])));
     s.v = t;
+  }
+
+  if constexpr (OP == RED_MAX || OP == RED_MIN) {
+    if (bits_smax > 0x7F800000 || bits_umax > 0xFF800000u) s.flags |= 1u;
+    if (bits_umin == 0u) s.flags |= 2u;
+    if (bits_smin == (int)0x80000000) s.flags |= 4u;
   }
 
   __shared__ RedState<OP> smem[RED_THREADS / 32];

@@ -4,6 +4,7 @@
 // The reference has no multi-device notion at all (guda.go:227-229 GetDeviceCount() == 1).
 #include "common.cuh"
 #include <string>
+#include <chrono>
 #include <cuda.h>
 #include <dlfcn.h>
 #include <nccl.h>
@@ -391,6 +392,9 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
     return GUDA_OK;
   };
   std::vector<cudaEvent_t> tr_in, tr_done;
+  std::vector<double> tr_host;                                     // host clock (ms since entry) when chunk j's copies / GEMM were enqueued
+  const auto t_entry = std::chrono::steady_clock::now();
+  auto host_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_entry).count(); };
   cudaEvent_t e0;
   if ((rc = new_event(&e0))) return rc;
   GUDA_CUDA(cudaEventRecord(e0, s));
@@ -426,8 +430,17 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
     const int k0 = kb[j], kc = kb[j + 1] - kb[j];
     float* a_chunk = a_panel_dev + (size_t)m_loc * k0;
     float* b_chunk = b_panel_dev + (size_t)k0 * n_loc;
+    if (trace) tr_host.push_back(host_ms());
     if (a_owner)
       GUDA_CUDA(cudaMemcpy2DAsync(a_chunk, (size_t)kc * 4, host_a_panel + k0, (size_t)lda * 4, (size_t)kc * 4, m_loc, cudaMemcpyHostToDevice, s_in));
+    if (a_owner && b_owner) {
+      // one H2D engine serves both streams in submission order: without this edge every B chunk (no dependencies among them) is
+      // submitted at once and A chunk j+1, which becomes ready only after broadcast j, queues behind ALL of B (2 GPUs: 150 ms stall)
+      cudaEvent_t e_a_up;
+      if ((rc = new_event(&e_a_up))) break;
+      GUDA_CUDA(cudaEventRecord(e_a_up, s_in));
+      GUDA_CUDA(cudaStreamWaitEvent(s_in2, e_a_up, 0));
+    }
     if (c->row_comm) GUDA_NCCL(g_nccl.Broadcast(a_chunk, a_chunk, (size_t)m_loc * kc, ncclFloat, a_root, c->row_comm, s_in));
     if (b_owner)
       GUDA_CUDA(cudaMemcpy2DAsync(b_chunk, (size_t)n_loc * 4, host_b_panel + (size_t)k0 * ldb, (size_t)ldb * 4, (size_t)n_loc * 4, kc,
@@ -439,7 +452,7 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
     GUDA_CUDA(cudaEventRecord(e_in_b, s_in2));
     GUDA_CUDA(cudaStreamWaitEvent(s, e_in, 0));
     GUDA_CUDA(cudaStreamWaitEvent(s, e_in_b, 0));
-    if (trace) { tr_in.push_back(e_in); tr_in.push_back(e_in_b); }
+    if (trace) { tr_in.push_back(e_in); tr_in.push_back(e_in_b); tr_host.push_back(host_ms()); }
     const float bj = j == 0 ? 0.0f : 1.0f;
     if (j + 1 < nk) {
       rc = guda_sgemm(0, 0, m_loc, n_loc, kc, alpha, a_chunk, kc, b_chunk, n_loc, bj, c_block_dev, n_loc, stream);
@@ -509,8 +522,8 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
         cudaEventElapsedTime(&t_a, e0, tr_in[2 * j]);
         cudaEventElapsedTime(&t_b, e0, tr_in[2 * j + 1]);
         if (j < tr_done.size()) cudaEventElapsedTime(&t_done, e0, tr_done[j]);
-        char buf[96];
-        snprintf(buf, sizeof buf, " %d:A%.1f,B%.1f/%.1f", kb[j + 1], t_a, t_b, t_done);
+        char buf[160];
+        snprintf(buf, sizeof buf, " %d:A%.1f,B%.1f/%.1f[host %.1f-%.1f]", kb[j + 1], t_a, t_b, t_done, tr_host[2 * j], tr_host[2 * j + 1]);
         line += buf;
       }
       float t_end = 0;

@@ -18,7 +18,8 @@
 // (64 fp64 accumulators per thread).  Operands stream global -> shared with 16-byte cp.async (zero-fill at the edges)
 // through a 4-stage ring; shared rows are padded by 4 doubles, which makes every fragment load (LDS.64, quarter-warp
 // = 4 rows x 4 k) bank-conflict free.  The last K % 4 terms are applied with scalar FMAs on the accumulator fragments.
-#include "gemm_simt.cuh"      // ScatterParams / ScatterArgsT (the fused all-gather epilogue shared with the SGEMM kernels)
+#include "gemm_simt.cuh"
+#include <cstdlib>      // ScatterParams / ScatterArgsT (the fused all-gather epilogue shared with the SGEMM kernels)
 
 namespace guda {
 
@@ -33,13 +34,30 @@ struct DmmaParams {
 };
 
 namespace dmma {
-constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4, THREADS = 256;
-constexpr int LDK = BK + 4;        // A (not transposed) in shared: [BM][LDK]
-constexpr int LDT = 128 + 4;       // k-major operands in shared: [BK][LDT]
-constexpr int A_STAGE = (BM * LDK > BK * LDT) ? BM * LDK : BK * LDT;     // doubles
-constexpr int B_STAGE = BK * LDT;
-constexpr int STAGE = A_STAGE + B_STAGE;
-constexpr int SMEM_BYTES = STAGES * STAGE * 8;
+constexpr int BM = 128, BN = 128;
+// Variants of the 128 x 128 CTA tile (GUDA_DMMA_WARPS=0 selects round 1's kernel as the A/B arm; evidence in DESIGN.md section 4 and
+// profiles/r02/ncu_dgemm_dmma_4096_*.md).  8 warps as 2 x 4, warp tile 64 x 32 (8 x 4 DMMA tiles, 64 accumulators per thread):
+//   W = 0: the next stage's cp.async issued right after the barrier (generic, clamped addresses) -- tensor pipe 81.6 % busy, 30.0
+//          TFLOP/s at 8192^3: after every barrier all eight warps ran ~125 instructions of address code, then their fragment loads,
+//          before the first DMMA of the tile
+//   W = 2: the cp.async of the next stage is issued AFTER the first k4 step's DMMAs have been queued, interior tiles take a
+//          clamp-free address path (two pointers + constant steps), and the DMMA asm is not `volatile`, so ptxas may move
+//          fragment loads and address arithmetic across it -- tensor pipe 92.3 %, 33.9 TFLOP/s at 8192^3, 34.2 at 16384^3 (default)
+// Measured and dropped: 16 warps of 32 x 32 (28.1: more shared-memory traffic, spills at 128 registers); W = 2 with BK 32 / 3 stages
+// (32.0); W = 2 with 5 or 6 stages (33.8 / 33.7).  A register-only loop of the same DMMA pattern sustains 37.1 TFLOP/s with these
+// 8 warps per SM (tools/dmma_lab.cu), so occupancy is not the limit.
+template <int W> struct Warps;
+template <> struct Warps<0> { static constexpr int WM = 2, WN = 4, MF = 8, NF = 4, THREADS = 256, BK = 16, STAGES = 4; static constexpr bool LATE = false; };
+template <> struct Warps<2> { static constexpr int WM = 2, WN = 4, MF = 8, NF = 4, THREADS = 256, BK = 16, STAGES = 4; static constexpr bool LATE = true; };
+template <int W> struct Geo {
+  static constexpr int BK = Warps<W>::BK, STAGES = Warps<W>::STAGES;
+  static constexpr int LDK = BK + 4;        // A (not transposed) in shared: [BM][LDK]
+  static constexpr int LDT = 128 + 4;       // k-major operands in shared: [BK][LDT]
+  static constexpr int A_STAGE = (BM * LDK > BK * LDT) ? BM * LDK : BK * LDT;     // doubles
+  static constexpr int B_STAGE = BK * LDT;
+  static constexpr int STAGE = A_STAGE + B_STAGE;
+  static constexpr int SMEM_BYTES = STAGES * STAGE * 8;
+};
 
 __device__ __forceinline__ void cp_async16(double* smem, const double* g, int src_bytes) {
   unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -51,6 +69,10 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 __device__ __forceinline__ void dmma_8x8x4(double (&c)[2], double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
+// the same instruction without `volatile`: the compiler may move fragment loads and address arithmetic across it (variants 2, 3)
+__device__ __forceinline__ void dmma_8x8x4_free(double (&c)[2], double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
 __device__ __forceinline__ int clamp16(long long bytes) { return bytes >= 16 ? 16 : (bytes > 0 ? (int)bytes : 0); }
 }  // namespace dmma
 
@@ -58,12 +80,16 @@ __device__ __forceinline__ int clamp16(long long bytes) { return bytes >= 16 ? 1
 // SKIP: the reference route has the `tmp != 0` test.
 // SCAT: besides c (which may then be null) every finished element is stored at (row, col) + off of each matrix in sp.dst[] --
 // the gathered C of every rank, peers reached through NVLink-mapped pointers (sharded.cu, guda_dgemm_sharded).
-template <bool TA, bool SCALE, bool SKIP, bool SCAT = false>
-__global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams p, ScatterParams<double, SCAT> sp) {
+template <bool TA, bool SCALE, bool SKIP, bool SCAT = false, int W = 0>
+__global__ void __launch_bounds__(dmma::Warps<W>::THREADS, 1) dgemm_dmma_kernel(DmmaParams p, ScatterParams<double, SCAT> sp) {
   using namespace dmma;
+  constexpr int THREADS = Warps<W>::THREADS, MF = Warps<W>::MF, NF = Warps<W>::NF, WROWS = MF * 8, WCOLS = NF * 8;
+  constexpr int BK = Geo<W>::BK, STAGES = Geo<W>::STAGES, LDK = Geo<W>::LDK, LDT = Geo<W>::LDT, A_STAGE = Geo<W>::A_STAGE, STAGE = Geo<W>::STAGE;
+  constexpr bool LATE = Warps<W>::LATE;
+  constexpr int CHUNKS = 64 * BK / THREADS;                 // 16-byte cp.async per thread per operand per stage
   extern __shared__ __align__(16) double dsm[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int wm = warp >> 2, wn = warp & 3;                  // 2 x 4 warps
+  const int wm = warp / Warps<W>::WN, wn = warp % Warps<W>::WN;
   const int g = lane >> 2, q = lane & 3;                    // fragment row group / k (or column pair) index
 
   // tile order: groups of 8 M-blocks sweep N so that co-resident CTAs share A rows and B columns in L2
@@ -84,10 +110,10 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
     double* Bs = As + A_STAGE;
     const int k0 = kt * BK;
 #pragma unroll
-    for (int it = 0; it < 4; it++) {
+    for (int it = 0; it < CHUNKS; it++) {
       const int c = tid + it * THREADS;
       if (!TA) {
-        const int row = c >> 3, kc = (c & 7) * 2;
+        const int row = c / (BK / 2), kc = (c % (BK / 2)) * 2;
         const long long gr = m0 + row;
         const int bytes = gr < p.m ? clamp16((long long)(p.k - (k0 + kc)) * 8) : 0;
         cp_async16(As + row * LDK + kc, bytes ? p.a + gr * p.lda + (k0 + kc) : p.a, bytes);
@@ -98,7 +124,7 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
       }
     }
 #pragma unroll
-    for (int it = 0; it < 4; it++) {
+    for (int it = 0; it < CHUNKS; it++) {
       const int c = tid + it * THREADS;
       const int kr = c >> 6, nc = (c & 63) * 2;
       const int bytes = (k0 + kr) < p.k ? clamp16((long long)(p.n - (n0 + nc)) * 8) : 0;
@@ -106,14 +132,39 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
     }
   };
 
+  // Interior tiles (no edge in m, n; the k edge is tested per tile): every chunk is a full 16 bytes at base + it * step -- two
+  // pointers and no clamping instead of the generic path's per-chunk bounds arithmetic (~125 instructions per stage).
+  const bool full_mn = LATE && m0 + BM <= p.m && n0 + BN <= p.n;
+  const double* a_thr = TA ? p.a + (long long)(tid >> 6) * p.lda + (m0 + (tid & 63) * 2)
+                           : p.a + (long long)(m0 + tid / (BK / 2)) * p.lda + (tid % (BK / 2)) * 2;
+  const double* b_thr = p.b + (long long)(tid >> 6) * p.ldb + (n0 + (tid & 63) * 2);
+  const int a_dst = TA ? (tid >> 6) * LDT + (tid & 63) * 2 : (tid / (BK / 2)) * LDK + (tid % (BK / 2)) * 2;
+  const int b_dst = (tid >> 6) * LDT + (tid & 63) * 2;
+  auto load_stage_fast = [&](int kt, int slot) {
+    double* As = dsm + slot * STAGE;
+    double* Bs = As + A_STAGE;
+    const long long k0 = (long long)kt * BK;
+#pragma unroll
+    for (int it = 0; it < CHUNKS; it++) {
+      if (!TA) cp_async16(As + a_dst + it * (THREADS / (BK / 2)) * LDK, a_thr + (long long)it * (THREADS / (BK / 2)) * p.lda + k0, 16);
+      else cp_async16(As + a_dst + it * (THREADS / 64) * LDT, a_thr + (k0 + it * (THREADS / 64)) * p.lda, 16);
+    }
+#pragma unroll
+    for (int it = 0; it < CHUNKS; it++) cp_async16(Bs + b_dst + it * (THREADS / 64) * LDT, b_thr + (k0 + it * (THREADS / 64)) * p.ldb, 16);
+  };
+  auto load_any = [&](int kt, int slot) {
+    if (full_mn && (kt + 1) * BK <= p.k) load_stage_fast(kt, slot);
+    else load_stage(kt, slot);
+  };
+
   // ---- accumulators start from the beta-scaled C (the reference's separate pass, compute/dgemm.go:104-119) ----
-  double acc[8][4][2];
+  double acc[MF][NF][2];
 #pragma unroll
-  for (int mf = 0; mf < 8; mf++) {
-    const int row = m0 + wm * 64 + mf * 8 + g;
+  for (int mf = 0; mf < MF; mf++) {
+    const int row = m0 + wm * WROWS + mf * 8 + g;
 #pragma unroll
-    for (int nf = 0; nf < 4; nf++) {
-      const int col = n0 + wn * 32 + nf * 8 + q * 2;
+    for (int nf = 0; nf < NF; nf++) {
+      const int col = n0 + wn * WCOLS + nf * 8 + q * 2;
 #pragma unroll
       for (int e = 0; e < 2; e++) {
         double v = 0.0;
@@ -136,8 +187,10 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
   for (int kt = 0; kt < KT; kt++) {
     cp_async_wait<STAGES - 2>();
     __syncthreads();
-    if (kt + STAGES - 1 < KT) load_stage(kt + STAGES - 1, (kt + STAGES - 1) % STAGES);
-    cp_async_commit();
+    if (!LATE) {
+      if (kt + STAGES - 1 < KT) load_stage(kt + STAGES - 1, (kt + STAGES - 1) % STAGES);
+      cp_async_commit();
+    }
 
     const double* As = dsm + (kt % STAGES) * STAGE;
     const double* Bs = As + A_STAGE;
@@ -145,45 +198,52 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
 #pragma unroll
     for (int kk = 0; kk < BK / 4; kk++) {
       const int kb = k0 + kk * 4;
+      if (LATE && kk == 1) {          // the slot refilled here was read in the previous iteration; every warp is past this iteration's barrier
+        if (kt + STAGES - 1 < KT) load_any(kt + STAGES - 1, (kt + STAGES - 1) % STAGES);
+        cp_async_commit();
+      }
       if (kb + 4 <= p.k) {
-        double af[8], bf[4];
+        double af[MF], bf[NF];
 #pragma unroll
-        for (int mf = 0; mf < 8; mf++) {
-          const int ml = wm * 64 + mf * 8 + g;
+        for (int mf = 0; mf < MF; mf++) {
+          const int ml = wm * WROWS + mf * 8 + g;
           double v = TA ? As[(kk * 4 + q) * LDT + ml] : As[ml * LDK + kk * 4 + q];
           if (SCALE) v = __dmul_rn(p.alpha, v);
           if (SKIP) zero_a |= (v == 0.0);
           af[mf] = v;
         }
 #pragma unroll
-        for (int nf = 0; nf < 4; nf++) {
-          const double v = Bs[(kk * 4 + q) * LDT + wn * 32 + nf * 8 + g];
+        for (int nf = 0; nf < NF; nf++) {
+          const double v = Bs[(kk * 4 + q) * LDT + wn * WCOLS + nf * 8 + g];
           if (SKIP) nonfinite_b |= ((__double2hiint(v) & 0x7ff00000) == 0x7ff00000);
           bf[nf] = v;
         }
 #pragma unroll
-        for (int mf = 0; mf < 8; mf++)
+        for (int mf = 0; mf < MF; mf++)
 #pragma unroll
-          for (int nf = 0; nf < 4; nf++) dmma_8x8x4(acc[mf][nf], af[mf], bf[nf]);
+          for (int nf = 0; nf < NF; nf++) {
+            if (LATE) dmma_8x8x4_free(acc[mf][nf], af[mf], bf[nf]);
+            else dmma_8x8x4(acc[mf][nf], af[mf], bf[nf]);
+          }
       } else if (kb < p.k) {
         // K % 4 tail: scalar FMAs on the accumulator fragments, same order and the same zero test
         for (int l = kb; l < p.k; l++) {
           const int kl = l - k0;
-          double av[8];
+          double av[MF];
 #pragma unroll
-          for (int mf = 0; mf < 8; mf++) {
-            const int ml = wm * 64 + mf * 8 + g;
+          for (int mf = 0; mf < MF; mf++) {
+            const int ml = wm * WROWS + mf * 8 + g;
             double v = TA ? As[kl * LDT + ml] : As[ml * LDK + kl];
             if (SCALE) v = __dmul_rn(p.alpha, v);
             av[mf] = v;
           }
 #pragma unroll
-          for (int nf = 0; nf < 4; nf++) {
+          for (int nf = 0; nf < NF; nf++) {
 #pragma unroll
             for (int e = 0; e < 2; e++) {
-              const double bv = Bs[kl * LDT + wn * 32 + nf * 8 + q * 2 + e];
+              const double bv = Bs[kl * LDT + wn * WCOLS + nf * 8 + q * 2 + e];
 #pragma unroll
-              for (int mf = 0; mf < 8; mf++)
+              for (int mf = 0; mf < MF; mf++)
                 if (!SKIP || av[mf] != 0.0) acc[mf][nf][e] = __fma_rn(av[mf], bv, acc[mf][nf][e]);
             }
           }
@@ -197,9 +257,9 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
   if (SKIP) {
     bool zero_out = false;
 #pragma unroll
-    for (int mf = 0; mf < 8; mf++)
+    for (int mf = 0; mf < MF; mf++)
 #pragma unroll
-      for (int nf = 0; nf < 4; nf++) zero_out |= (acc[mf][nf][0] == 0.0) | (acc[mf][nf][1] == 0.0);
+      for (int nf = 0; nf < NF; nf++) zero_out |= (acc[mf][nf][0] == 0.0) | (acc[mf][nf][1] == 0.0);
     const int za = __syncthreads_or(zero_a);
     const int hz = __syncthreads_or(nonfinite_b | zero_out);
     if (za && hz) {
@@ -229,12 +289,12 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
   const bool vec_ok = ((p.ldc & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
   const int lim_m = p.m < p.edge_m ? p.m : p.edge_m, lim_n = p.n < p.edge_n ? p.n : p.edge_n;
 #pragma unroll
-  for (int mf = 0; mf < 8; mf++) {
-    const int row = m0 + wm * 64 + mf * 8 + g;
+  for (int mf = 0; mf < MF; mf++) {
+    const int row = m0 + wm * WROWS + mf * 8 + g;
     if (row >= lim_m) continue;
 #pragma unroll
-    for (int nf = 0; nf < 4; nf++) {
-      const int col = n0 + wn * 32 + nf * 8 + q * 2;
+    for (int nf = 0; nf < NF; nf++) {
+      const int col = n0 + wn * WCOLS + nf * 8 + q * 2;
       if (!SCAT || p.c) {
         double* dst = p.c + (long long)row * p.ldc + col;
         if (vec_ok && col + 1 < lim_n) {
@@ -260,16 +320,24 @@ __global__ void __launch_bounds__(dmma::THREADS, 1) dgemm_dmma_kernel(DmmaParams
   }
 }
 
-template <bool TA, bool SCALE, bool SKIP, bool SCAT>
-static int launch_dmma_s(const DmmaParams& p, const ScatterParams<double, SCAT>& sp, cudaStream_t s) {
-  auto kern = dgemm_dmma_kernel<TA, SCALE, SKIP, SCAT>;
+static int g_dmma_warps = [] { const char* e = getenv("GUDA_DMMA_WARPS"); return e ? atoi(e) : 2; }();
+template <bool TA, bool SCALE, bool SKIP, bool SCAT, int W>
+static int launch_dmma_w(const DmmaParams& p, const ScatterParams<double, SCAT>& sp, cudaStream_t s) {
+  auto kern = dgemm_dmma_kernel<TA, SCALE, SKIP, SCAT, W>;
   static bool attr_set = false;
   if (!attr_set) {
-    GUDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dmma::SMEM_BYTES));
+    GUDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dmma::Geo<W>::SMEM_BYTES));
     attr_set = true;
   }
-  kern<<<p.tiles_m * p.tiles_n, dmma::THREADS, dmma::SMEM_BYTES, s>>>(p, sp);
+  kern<<<p.tiles_m * p.tiles_n, dmma::Warps<W>::THREADS, dmma::Geo<W>::SMEM_BYTES, s>>>(p, sp);
   return check_launch("dgemm_dmma");
+}
+template <bool TA, bool SCALE, bool SKIP, bool SCAT>
+static int launch_dmma_s(const DmmaParams& p, const ScatterParams<double, SCAT>& sp, cudaStream_t s) {
+  switch (g_dmma_warps) {
+    case 0: return launch_dmma_w<TA, SCALE, SKIP, SCAT, 0>(p, sp, s);
+    default: return launch_dmma_w<TA, SCALE, SKIP, SCAT, 2>(p, sp, s);
+  }
 }
 template <bool TA, bool SCALE, bool SKIP>
 static int launch_dmma(const DmmaParams& p, cudaStream_t s, const ScatterArgsT<double>* sc) {

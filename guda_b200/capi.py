@@ -133,6 +133,7 @@ SIGNATURES = {
     "guda_multiply": (i, [vp, vp, vp, C.c_longlong, vp]),
     "guda_relu": (i, [vp, C.c_longlong, vp]),
     "guda_sigmoid": (i, [vp, C.c_longlong, vp]),
+    "guda_selftest_activations": (i, [vp, vp]),
     "guda_fused_execute": (i, [vp, C.POINTER(vp), i, C.c_longlong, C.POINTER(FusedOp), i, vp]),
     "guda_conv_set_route": (i, [i]),
     "guda_conv2d_direct": (i, [vp, vp, vp, vp, C.POINTER(ConvParams), vp]),

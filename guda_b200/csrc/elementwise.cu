@@ -7,18 +7,38 @@
 // Arithmetic: every Go statement on a float32 rounds once and GOAMD64=v1 does not contract `val += alpha*other`, so each
 // step is an explicit __fmul_rn / __fadd_rn / __fdiv_rn; ExpFloat32 and geluFloat32 are the restatements of gemm_simt.cuh.
 #include "gemm_simt.cuh"
+#ifndef GUDA_ACT_FAST
+#define GUDA_ACT_FAST true      // false: the kernels below use the plain div.rn forms (A/B timing arm, tools/time_activations.py)
+#endif
 
 namespace guda {
 
+template <bool FAST = true>
 __device__ __forceinline__ float sigmoid_f32_exact(float x) {      // activations.go:9-27
   if (x < -10.0f) return 0.0f;
   if (x > 10.0f) return 1.0f;
   if (x >= 0.0f) {
     const float e = gelu_exp_f32(-x);
-    return __fdiv_rn(1.0f, __fadd_rn(1.0f, e));
+    return FAST ? div_normal_rn(1.0f, __fadd_rn(1.0f, e)) : __fdiv_rn(1.0f, __fadd_rn(1.0f, e));
   }
-  const float e = gelu_exp_f32(x);                                 // also the NaN route (every comparison false)
-  return __fdiv_rn(e, __fadd_rn(1.0f, e));
+  const float e = gelu_exp_f32(x);                                 // also the NaN route (every comparison false): generic division
+  if (!FAST || x != x) return __fdiv_rn(e, __fadd_rn(1.0f, e));
+  return div_normal_rn(e, __fadd_rn(1.0f, e));
+}
+
+// All 2^32 inputs through both forms of each activation (see the comment above div_const_rn in gemm_simt.cuh)
+__global__ void __launch_bounds__(256) activation_selftest_kernel(unsigned long long* counts, unsigned int* first_bad) {
+  unsigned long long bad_g = 0, bad_s = 0;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < (1ull << 32); i += stride) {
+    const float x = __uint_as_float((unsigned)i);
+    const unsigned g1 = __float_as_uint(gelu_f32_exact<true>(x)), g0 = __float_as_uint(gelu_f32_exact<false>(x));
+    const unsigned s1 = __float_as_uint(sigmoid_f32_exact<true>(x)), s0 = __float_as_uint(sigmoid_f32_exact<false>(x));
+    if (g1 != g0) { bad_g++; atomicMin(first_bad, (unsigned)i); }
+    if (s1 != s0) { bad_s++; atomicMin(first_bad + 1, (unsigned)i); }
+  }
+  if (bad_g) atomicAdd(counts, bad_g);
+  if (bad_s) atomicAdd(counts + 1, bad_s);
 }
 
 enum { EW_ADD = 0, EW_MUL = 1, EW_RELU = 2, EW_SIGMOID = 3 };
@@ -33,7 +53,7 @@ __global__ void __launch_bounds__(256) ew_kernel(const float* __restrict__ a, co
     if (OP == EW_ADD) return __fadd_rn(x, y);
     if (OP == EW_MUL) return __fmul_rn(x, y);
     if (OP == EW_RELU) return x < 0.0f ? 0.0f : x;                 // math.go:240: NaN and -0 stay
-    return sigmoid_f32_exact(x);
+    return sigmoid_f32_exact<GUDA_ACT_FAST>(x);
   };
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
     const float4 x = reinterpret_cast<const float4*>(a)[i];
@@ -99,11 +119,11 @@ __device__ __forceinline__ void fused_apply(const FusedArgs& fa, float (&val)[NV
         break;
       case GUDA_FUSED_SIGMOID:
 #pragma unroll
-        for (int j = 0; j < NV; j++) val[j] = sigmoid_f32_exact(val[j]);
+        for (int j = 0; j < NV; j++) val[j] = sigmoid_f32_exact<GUDA_ACT_FAST>(val[j]);
         break;
       case GUDA_FUSED_GELU:
 #pragma unroll
-        for (int j = 0; j < NV; j++) val[j] = gelu_f32_exact(val[j]);
+        for (int j = 0; j < NV; j++) val[j] = gelu_f32_exact<GUDA_ACT_FAST>(val[j]);
         break;
       default: break;
     }
@@ -158,6 +178,26 @@ int guda_multiply(const float* a, const float* b, float* c, long long n, guda_st
 }
 int guda_relu(float* x, long long n, guda_stream_t stream) { return ew_launch<EW_RELU>(x, nullptr, x, n, stream, "ReLU"); }
 int guda_sigmoid(float* x, long long n, guda_stream_t stream) { return ew_launch<EW_SIGMOID>(x, nullptr, x, n, stream, "Sigmoid"); }
+// counts[0] / counts[1]: inputs (of all 2^32 bit patterns) on which the fast and the __fdiv_rn forms of geluFloat32 / SigmoidFloat32
+// disagree in any bit; first_bad[0] / [1]: the smallest such input.  Blocking.  The product kernels use the fast forms.
+int guda_selftest_activations(unsigned long long* counts, unsigned int* first_bad) {
+  if (!counts || !first_bad) return guda::set_error(GUDA_ERR_INVALID_ARG, "selftest_activations: null pointer");
+  int rc = guda::bind_device();
+  if (rc) return rc;
+  cudaStream_t s = guda::native(nullptr);
+  guda::PoolTemp buf;
+  if ((rc = buf.alloc(64, s))) return rc;
+  unsigned long long* d_counts = static_cast<unsigned long long*>(buf.p);
+  unsigned int* d_first = reinterpret_cast<unsigned int*>(d_counts + 2);
+  GUDA_CUDA(cudaMemsetAsync(d_counts, 0, 16, s));
+  GUDA_CUDA(cudaMemsetAsync(d_first, 0xFF, 8, s));
+  guda::activation_selftest_kernel<<<guda::sm_count() * 8, 256, 0, s>>>(d_counts, d_first);
+  if ((rc = guda::check_launch("selftest_activations"))) return rc;
+  GUDA_CUDA(cudaMemcpyAsync(counts, d_counts, 16, cudaMemcpyDeviceToHost, s));
+  GUDA_CUDA(cudaMemcpyAsync(first_bad, d_first, 8, cudaMemcpyDeviceToHost, s));
+  GUDA_CUDA(cudaStreamSynchronize(s));
+  return GUDA_OK;
+}
 
 int guda_fused_execute(float* x, const float* const* others, int n_others, long long n, const guda_fused_op_t* ops, int n_ops,
                        guda_stream_t stream) {

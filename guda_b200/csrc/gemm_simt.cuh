@@ -74,6 +74,30 @@ __device__ __forceinline__ float gelu_exp_f32(float x) {
   // the product rounds once from the same exact value (overflow to +Inf included) -- also covered by expcheck.c
   return __fmul_rn(e, __int_as_float((k + 127) << 23));
 }
+// ---- IEEE divisions of the activation functions without div.rn's generic sequence (~10 instructions + a slow-path call each) ----
+// The three divisions of geluFloat32 / the one of SigmoidFloat32 made these kernels issue-bound at 0.47 of HBM.  Each activation is a
+// function of ONE float, so a cheaper sequence is certified the brute-force way: guda_selftest_activations() evaluates the sequences
+// below and the plain __fdiv_rn restatement on all 2^32 inputs ON THE DEVICE and counts differing bit patterns (a -m gpu test
+// requires 0).  FAST = false selects the __fdiv_rn form (the other arm of that check).
+// q = RN(a / D), D a small integer constant: Markstein's correction with the correctly rounded reciprocal.
+template <int D> __device__ __forceinline__ float div_const_rn(float a) {
+  constexpr float d = (float)D, c = 1.0f / (float)D;
+  const float q0 = __fmul_rn(a, c);
+  const float r = __fmaf_rn(-d, q0, a);                 // exact remainder
+  return __fmaf_rn(r, c, q0);
+}
+// q = RN(a / b) for normal b well inside the exponent range and a / b normal: approximate reciprocal, one Newton step, quotient,
+// exact remainder, correction.
+__device__ __forceinline__ float div_normal_rn(float a, float b) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(b));
+  const float e = __fmaf_rn(-b, y, 1.0f);
+  y = __fmaf_rn(y, e, y);
+  const float q0 = __fmul_rn(a, y);
+  const float r = __fmaf_rn(-b, q0, a);
+  return __fmaf_rn(r, y, q0);
+}
+template <bool FAST = true>
 __device__ __forceinline__ float gelu_tanh_f32(float x) {
   if (x != x) return x;
   float ax = fabsf(x);
@@ -81,20 +105,22 @@ __device__ __forceinline__ float gelu_tanh_f32(float x) {
   if (ax > 10.0f) r = 1.0f;
   else if (ax < 0.5f) {
     float x2 = __fmul_rn(ax, ax);
-    float b = __fsub_rn(1.0f, __fdiv_rn(x2, 3.0f));
-    float c = __fdiv_rn(__fmul_rn(__fmul_rn(2.0f, x2), x2), 15.0f);
+    float b = __fsub_rn(1.0f, FAST ? div_const_rn<3>(x2) : __fdiv_rn(x2, 3.0f));
+    float n15 = __fmul_rn(__fmul_rn(2.0f, x2), x2);
+    float c = FAST ? div_const_rn<15>(n15) : __fdiv_rn(n15, 15.0f);
     r = __fmul_rn(ax, __fadd_rn(b, c));
   } else {
     float e = gelu_exp_f32(__fmul_rn(2.0f, ax));
-    r = __fdiv_rn(__fsub_rn(e, 1.0f), __fadd_rn(e, 1.0f));
+    r = FAST ? div_normal_rn(__fsub_rn(e, 1.0f), __fadd_rn(e, 1.0f)) : __fdiv_rn(__fsub_rn(e, 1.0f), __fadd_rn(e, 1.0f));
   }
   return x < 0 ? -r : r;
 }
+template <bool FAST = true>
 __device__ __forceinline__ float gelu_f32_exact(float x) {
   float x3 = __fmul_rn(__fmul_rn(x, x), x);
   float inner = __fadd_rn(x, __fmul_rn(0.044715f, x3));
   float arg = __fmul_rn(0.7978845608028653559f, inner);
-  float t = gelu_tanh_f32(arg);
+  float t = gelu_tanh_f32<FAST>(arg);
   return __fmul_rn(__fmul_rn(0.5f, x), __fadd_rn(1.0f, t));
 }
 
@@ -103,7 +129,7 @@ __device__ __forceinline__ T apply_epilogue(T acc, T bias) {
   if (EPI == EPI_NONE) return acc;
   T v = g_add(acc, bias);
   if (EPI == EPI_BIAS_RELU) return v < T(0) ? T(0) : v;          // fused.go:362-365 (NaN stays NaN)
-  return (T)gelu_f32_exact((float)v);
+  return (T)gelu_f32_exact<true>((float)v);
 }
 
 template <typename T>

@@ -238,6 +238,11 @@ int guda_add(const float* a, const float* b, float* c, long long n, guda_stream_
 int guda_multiply(const float* a, const float* b, float* c, long long n, guda_stream_t stream);
 int guda_relu(float* x, long long n, guda_stream_t stream);
 int guda_sigmoid(float* x, long long n, guda_stream_t stream);
+/* Test support: geluFloat32 and SigmoidFloat32 are functions of one float, and the kernels replace their IEEE divisions by
+ * shorter correctly-rounding sequences (csrc/gemm_simt.cuh div_const_rn / div_normal_rn).  This call evaluates the sequences and
+ * the plain div.rn restatement of fused_gelu.go:44-56 / activations.go:9-27 on ALL 2^32 inputs on the device; counts[0] / [1] =
+ * inputs whose results differ in any bit (GELU / Sigmoid), first_bad[0] / [1] = the smallest such input.  Blocking. */
+int guda_selftest_activations(unsigned long long counts[2], unsigned int first_bad[2]);
 /* fused.go:18-216 FusedKernel: x[idx] is read once, the ops are applied to the value in order, and it is written once.
  * Types follow fused.go:34-42 (FusedCustom is available for the one function the reference passes to it, geluFloat32,
  * fused.go:261-267).  A binary op (Add: val += alpha * other, Mul: val *= other) consumes the next `others` pointer and is

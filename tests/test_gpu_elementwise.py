@@ -178,3 +178,14 @@ def test_topk_leading_nan_and_errors(g, O):
         g.TopK(dx, 5, 0)
     assert "invalid parameter" in e.value.message
     g.Free(dx)
+
+
+def test_fast_division_sequences_agree_with_div_rn_on_every_float32_input(g):
+    """geluFloat32 / SigmoidFloat32 are functions of one float: the kernels' shortened division sequences (gemm_simt.cuh div_const_rn,
+    div_normal_rn) and the plain div.rn restatement are evaluated on all 2^32 bit patterns on the device; not one bit may differ."""
+    import ctypes as C
+    counts = (C.c_ulonglong * 2)()
+    first = (C.c_uint * 2)()
+    g.capi.check(g.load().guda_selftest_activations(counts, first), "SelftestActivations")
+    assert (counts[0], counts[1]) == (0, 0), "GELU differs on %d inputs (first 0x%08x), Sigmoid on %d (first 0x%08x)" % (
+        counts[0], first[0], counts[1], first[1])

@@ -95,6 +95,7 @@ SIGNATURES = {
     "guda_get_sgemm_mode": (i, [ip]),
     "guda_sgemm": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
     "guda_sgemm_host": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, vp]),
+    "guda_host_gemm_schedule": (i, [i, i, vp, i, vp, vp]),
     "guda_dgemm": (i, [i, i, i, i, i, d, vp, i, vp, i, d, vp, i, vp]),
     "guda_sgemm_scatter": (i, [i, i, i, i, i, f, vp, i, vp, i, f, vp, i, C.POINTER(vp), i, i, i, i, vp]),
     "guda_dgemm_scatter": (i, [i, i, i, i, i, d, vp, i, vp, i, d, vp, i, C.POINTER(vp), i, i, i, i, vp]),

@@ -178,3 +178,16 @@ extern "C" int guda_sgemm_host(int ta, int tb, int m, int n, int k, float alpha,
   buf.done = true;
   return GUDA_OK;
 }
+
+// Test support (host logic only, no device call): the K-chunk schedule and the row-panel count of the host-operand GEMMs.
+// bounds[0..*count-1] receives 0 = b0 < b1 < ... = k; returns GUDA_ERR_INVALID_ARG if `cap` is too small.
+extern "C" int guda_host_gemm_schedule(int k, int m, int* bounds, int cap, int* count, int* panels) {
+  if (k < 1 || !bounds || !count) return guda::set_error(GUDA_ERR_INVALID_ARG, "host_gemm_schedule: bad arguments");
+  std::vector<int> kb;
+  guda::host_k_chunks(k, kb);
+  if ((int)kb.size() > cap) return guda::set_error(GUDA_ERR_INVALID_ARG, "host_gemm_schedule: %d bounds do not fit %d slots", (int)kb.size(), cap);
+  for (size_t i = 0; i < kb.size(); i++) bounds[i] = kb[i];
+  *count = (int)kb.size();
+  if (panels) *panels = guda::host_c_panels(m);
+  return GUDA_OK;
+}

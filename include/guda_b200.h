@@ -182,6 +182,10 @@ int guda_add_bias_relu(float* x, const float* bias, int n, int bias_len, guda_st
  * panel computes.  Blocks until C is on the host.  Bit-identical to guda_sgemm on device-resident copies of the same operands. */
 int guda_sgemm_host(int trans_a, int trans_b, int m, int n, int k, float alpha, const float* host_a, int lda, const float* host_b, int ldb,
                     float beta, float* host_c, int ldc, guda_stream_t stream);
+/* Test support, host logic only (no device call): the K-chunk schedule guda_sgemm_host / guda_sgemm_sharded_host walk for depth k
+ * (bounds[0] = 0 < ... < bounds[*count-1] = k: a short first chunk, doubling depths, 8192-deep blocks, a two-block last chunk -- the
+ * only one the download of C can hide under) and the number of row panels the last chunk of an m-row block is cut into. */
+int guda_host_gemm_schedule(int k, int m, int* bounds, int cap, int* count, int* panels);
 
 /* ---- Level 2: compute/level2float32.go:244-308 Sgemv, :24-65 Sger (row-major; lda = row stride);
  * kernels compute/asm/f32/gemv.go:12-91 (GemvN / GemvT) and compute/asm/f32/ge_amd64.s (Ger).  trans: 0 = NoTrans,

@@ -96,3 +96,37 @@ def test_product_package_never_imports_the_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, fn)).read()
                 assert "oracle" not in text.replace("the oracle", "").replace("oracle's", "").replace("oracle checks", ""), os.path.join(dirpath, fn)
+
+
+def _schedule(k, m=65536):
+    from guda_b200 import capi
+    L = capi.load()
+    bounds, count, panels = (C.c_int * 64)(), C.c_int(0), C.c_int(0)
+    capi.check(L.guda_host_gemm_schedule(k, m, bounds, 64, C.byref(count), C.byref(panels)), "HostGemmSchedule")
+    return list(bounds[:count.value]), panels.value
+
+
+@pytest.mark.parametrize("k", [1, 100, 8192, 8193, 9000, 16384, 20000, 24576, 32768, 65536, 131072])
+def test_host_gemm_k_chunk_schedule(k):
+    """Host logic of guda_sgemm_host / guda_sgemm_sharded_host (no device call): the chunk bounds cover [0, k) in order; up to one 8192
+    block there is a single chunk; beyond it the depths start at 512 and at most double from chunk to chunk (chunk j+1 uploads under
+    chunk j's GEMM), every interior bound keeps the 16-byte / TMA alignment, and from three blocks up the last chunk is more than one block (at most two) deep
+    (the download of C hides under the last chunk only)."""
+    b, _ = _schedule(k)
+    assert b[0] == 0 and b[-1] == k and all(x < y for x, y in zip(b, b[1:]))
+    depth = [y - x for x, y in zip(b, b[1:])]
+    if k <= 8192:
+        assert depth == [k]
+        return
+    assert depth[0] == 512
+    assert all(x % 512 == 0 for x in b[1:-1])
+    body = depth[:-1]
+    assert all(d2 <= 2 * d1 for d1, d2 in zip(body, body[1:]))
+    assert max(depth[:-1], default=0) <= 8192
+    assert depth[-1] <= 2 * 8192
+    if k >= 3 * 8192:
+        assert depth[-1] > 8192
+
+
+def test_host_gemm_row_panels():
+    assert _schedule(100, 1024)[1] == 1 and _schedule(100, 2048)[1] == 8 and _schedule(100, 32768)[1] == 16

@@ -10,6 +10,7 @@
 // Exposed transfer time is one chunk in and one panel out instead of the whole of A, B and C.
 // Results are bit-identical to guda_sgemm on device-resident operands (tests/test_gpu_host_gemm.py).
 #include "common.cuh"
+#include <mutex>
 #include <vector>
 
 namespace guda {
@@ -19,15 +20,17 @@ constexpr int HG_KC = 8192;          // = the device path's K block (gemm.cu KCh
 struct HgStreams { cudaStream_t in = nullptr, in2 = nullptr, out = nullptr; };
 static int hg_streams(HgStreams** o) {
   static HgStreams st;
-  if (!st.in) {
+  static std::mutex mu;                    // first use may come from several host threads at once
+  std::lock_guard<std::mutex> lk(mu);
+  if (!st.out) {                           // `out` is created last: a failed attempt is simply repeated by the next call
     // Highest priority: what runs on these streams besides copies is the NVLink broadcast of the sharded host step (an NCCL kernel).
     // The GEMM launches fill every SM (4 CTAs x 126 registers x 128 threads), and at equal priority a waiting kernel only gets CTA
     // slots when the running grid has none left to issue -- one broadcast per GEMM launch boundary, which starved the upload
     // pipeline at 8 GPUs.  At higher priority its few CTAs take the first slots a retiring GEMM CTA frees (every ~0.1 ms).
     int least = 0, greatest = 0;
     GUDA_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
-    GUDA_CUDA(cudaStreamCreateWithPriority(&st.in, cudaStreamNonBlocking, greatest));
-    GUDA_CUDA(cudaStreamCreateWithPriority(&st.in2, cudaStreamNonBlocking, greatest));
+    if (!st.in) GUDA_CUDA(cudaStreamCreateWithPriority(&st.in, cudaStreamNonBlocking, greatest));
+    if (!st.in2) GUDA_CUDA(cudaStreamCreateWithPriority(&st.in2, cudaStreamNonBlocking, greatest));
     GUDA_CUDA(cudaStreamCreateWithPriority(&st.out, cudaStreamNonBlocking, greatest));
   }
   *o = &st;

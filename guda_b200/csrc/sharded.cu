@@ -382,7 +382,11 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
   if (rc) return rc;
   cudaStream_t s = native(stream), s_in, s_in2, s_out;             // s_in carries the A chunks, s_in2 the B chunks
   if ((rc = aux_copy_streams(&s_in, &s_out, &s_in2))) return rc;
-  std::vector<cudaEvent_t> evs;
+  struct EventBag {                       // destroyed on every return path (an early error return used to leak the step's events);
+    std::vector<cudaEvent_t> v;            // destroying an event that queued work still references is legal: CUDA defers the release
+    ~EventBag() { for (cudaEvent_t e : v) cudaEventDestroy(e); }
+    void push_back(cudaEvent_t e) { v.push_back(e); }
+  } evs;
   // GUDA_HOST_STEP_TRACE=1: events carry timestamps and every rank prints, per K chunk, when its operands were on the device and when
   // its GEMM finished (ms from the start of the step) -- the tool that shows whether the GEMM ever waits for the upload pipeline
   static const bool trace = [] { const char* e = getenv("GUDA_HOST_STEP_TRACE"); return e && atoi(e) != 0; }();
@@ -531,7 +535,6 @@ int guda_sgemm_sharded_host(guda_comm_t comm, int pr, int pc, int m_total, int n
       fprintf(stderr, "%s end %.1f\n", line.c_str(), t_end);
     }
   }
-  for (cudaEvent_t e : evs) cudaEventDestroy(e);
   return rc;
 }
 

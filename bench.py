@@ -331,7 +331,7 @@ def suite(dev, peaks, ffma_peak, dfma_peak, dmma_peak):
     ea, eb, ec = g.Malloc(ne * 4), g.Malloc(ne * 4), g.Malloc(ne * 4)
     g.FillUniform(ea, 1, ne, ne, 700); g.FillUniform(eb, 1, ne, ne, 701)
     for key, fn, bpe in (("add_64M", lambda: g.Add(ea, eb, ec, ne), 12.0), ("linear_relu_64M", lambda: g.LinearReLU(ec, 1.01, 0.1, ne), 8.0),
-                         ("gelu_64M", lambda: g.GELU(ec, ne), 8.0)):
+                         ("gelu_64M", lambda: g.GELU(ec, ne), 8.0), ("sigmoid_64M", lambda: g.Sigmoid(ec, ne), 8.0)):
         for _ in range(3):
             fn()
         ms = dev.time_ms(fn, 20)
